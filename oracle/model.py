@@ -155,21 +155,23 @@ class OracleModel:
         return xf @ sd["lm_head"].T
 
     @torch.no_grad()
-    def generate(self, prompt_ids, max_new_tokens: int, kv: KVState | None = None,
-                 round_act_prefill: bool = False, prefill_chunk: int = 512, return_logits: bool = False):
-        """Greedy decoding, EOS ignored.  Returns (ids, [per-step logits])."""
+    def generate(self, prompt_ids, max_new_tokens: int, kv: KVState | None = None, round_act: bool = True,
+                 prefill_chunk: int = 512, return_logits: bool = False):
+        """Greedy decoding, EOS ignored.  ``round_act=True`` is the engine's numerics
+        (bf16 matmul inputs everywhere).  Returns ids, or (ids, per-step logits)."""
         kv = kv if kv is not None else KVState()
         ids = list(prompt_ids)
         logits = None
         for s in range(0, len(ids), prefill_chunk):
-            logits = self.forward(ids[s:s + prefill_chunk], kv, round_act=round_act_prefill, last_only=True)
+            logits = self.forward(ids[s:s + prefill_chunk], kv, round_act=round_act, last_only=True)
         out, all_logits = [], []
-        for _ in range(max_new_tokens):
+        for i in range(max_new_tokens):
             if return_logits:
                 all_logits.append(logits[-1].clone())
             nxt = int(torch.argmax(logits[-1]))
             out.append(nxt)
-            logits = self.forward([nxt], kv, last_only=True)
+            if i + 1 < max_new_tokens:
+                logits = self.forward([nxt], kv, round_act=round_act, last_only=True)
         return (out, all_logits) if return_logits else out
 
 
@@ -196,3 +198,41 @@ def make_state_dict(a: Arch, seed: int) -> dict:
             sd[p + "k_bias"] = W.gen_tensor(seed, W.K_BIAS, l, (a.n_kv * hd,))
             sd[p + "v_bias"] = W.gen_tensor(seed, W.V_BIAS, l, (a.n_kv * hd,))
     return sd
+
+
+@torch.no_grad()
+def decode_step_batch(m: OracleModel, tokens, kvs, round_act: bool = True) -> torch.Tensor:
+    """One decode step for B independent sequences with the projections batched over B (what a CPU
+    server does for concurrent requests); attention stays per sequence.  Returns logits [B, vocab].
+    Numerically the same as B calls of ``forward([tok], kv)`` up to fp32 summation order."""
+    a, sd = m.a, m.sd
+    B = len(tokens)
+    ra = _rbf16 if round_act else (lambda t: t)
+    pos = torch.tensor([kv.length for kv in kvs])
+    x = sd["embed"][torch.as_tensor(tokens, dtype=torch.long)]
+    G = a.n_q // a.n_kv
+    scale = 1.0 / math.sqrt(a.head_dim)
+    for l in range(a.layers):
+        p = f"l{l}."
+        h = ra(m._rms(x, sd[p + "in_norm"]))
+        q, k, v = h @ sd[p + "q"].T, h @ sd[p + "k"].T, h @ sd[p + "v"].T
+        if a.qkv_bias:
+            q, k, v = q + sd[p + "q_bias"], k + sd[p + "k_bias"], v + sd[p + "v_bias"]
+        q = ra(m._rope(q.view(B, a.n_q, a.head_dim), pos))
+        k = _rbf16(m._rope(k.view(B, a.n_kv, a.head_dim), pos))
+        v = _rbf16(v.view(B, a.n_kv, a.head_dim))
+        outs = []
+        for b, kv in enumerate(kvs):
+            kv.k[l] = torch.cat([kv.k[l], k[b][:, None, :]], dim=1)
+            kv.v[l] = torch.cat([kv.v[l], v[b][:, None, :]], dim=1)
+            qh = q[b].view(a.n_kv, G, a.head_dim)
+            s = torch.bmm(qh, kv.k[l].transpose(1, 2)) * scale
+            o = torch.bmm(torch.softmax(s, dim=-1), kv.v[l])
+            outs.append(o.reshape(a.n_q * a.head_dim))
+        x = x + ra(torch.stack(outs)) @ sd[p + "o"].T
+        h = ra(m._rms(x, sd[p + "post_norm"]))
+        act = torch.nn.functional.silu(h @ sd[p + "gate"].T) * (h @ sd[p + "up"].T)
+        x = x + ra(act) @ sd[p + "down"].T
+    for kv in kvs:
+        kv.length += 1
+    return ra(m._rms(x, sd["final_norm"])) @ sd["lm_head"].T

@@ -57,8 +57,32 @@ def round_bf16(x: np.ndarray) -> np.ndarray:
     return bf16_bits_to_f32(f32_to_bf16_bits(x))
 
 
-def gen_bits(seed: int, tid: int, start: int, count: int, std: float = 0.02, offset: float = 0.0) -> np.ndarray:
-    """bf16 bit patterns of elements [start, start+count) of tensor ``tid``."""
+_clib = None
+
+
+def _c_helper():
+    """oracle/_build/liboracle_wgen.so (oracle/csrc/wgen.c) when it has been built; else None."""
+    global _clib
+    if _clib is None:
+        import ctypes as C
+        import os
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_build", "liboracle_wgen.so")
+        if os.path.exists(path):
+            lib = C.CDLL(path)
+            lib.oracle_gen.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+            lib.oracle_gen.restype = None
+            _clib = lib
+        else:
+            _clib = False
+    return _clib or None
+
+
+def gen_bits_numpy(seed: int, tid: int, start: int, count: int, std: float = 0.02, offset: float = 0.0) -> np.ndarray:
+    """Pure-numpy definition of the generator (the C helper must equal it bit for bit)."""
+    if count > (1 << 24):
+        parts = [gen_bits_numpy(seed, tid, s, min(1 << 24, start + count - s), std, offset)
+                 for s in range(start, start + count, 1 << 24)]
+        return np.concatenate(parts)
     key = stream_key(seed, tid)
     with np.errstate(over="ignore"):
         idx = np.arange(start, start + count, dtype=np.uint64) + key
@@ -73,11 +97,27 @@ def gen_bits(seed: int, tid: int, start: int, count: int, std: float = 0.02, off
     return f32_to_bf16_bits(v)
 
 
+def gen_bits(seed: int, tid: int, start: int, count: int, std: float = 0.02, offset: float = 0.0) -> np.ndarray:
+    """bf16 bit patterns of elements [start, start+count) of tensor ``tid``."""
+    lib = _c_helper()
+    if lib is None:
+        return gen_bits_numpy(seed, tid, start, count, std, offset)
+    out = np.empty(count, dtype=np.uint16)
+    lib.oracle_gen(int(stream_key(seed, tid)), start, count, np.float32(std / IH4_STD), np.float32(offset), None,
+                   out.ctypes.data)
+    return out
+
+
 def gen_tensor(seed: int, kind: int, layer: int | None, shape, std: float = 0.02, offset: float = 0.0) -> np.ndarray:
     """fp32 array holding bf16-representable values, row-major in the HF tensor layout."""
     n = int(np.prod(shape))
-    bits = gen_bits(seed, tensor_id(kind, layer), 0, n, std, offset)
-    return bf16_bits_to_f32(bits).reshape(shape)
+    lib = _c_helper()
+    if lib is None:
+        return bf16_bits_to_f32(gen_bits_numpy(seed, tensor_id(kind, layer), 0, n, std, offset)).reshape(shape)
+    out = np.empty(n, dtype=np.float32)
+    lib.oracle_gen(int(stream_key(seed, tensor_id(kind, layer))), 0, n, np.float32(std / IH4_STD), np.float32(offset),
+                   out.ctypes.data, None)
+    return out.reshape(shape)
 
 
 def norm_tensor(seed: int, kind: int, layer: int | None, n: int) -> np.ndarray:

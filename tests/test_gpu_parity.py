@@ -1,0 +1,150 @@
+"""End-to-end parity of the CUDA path against the CPU oracle, through the C-ABI.
+
+Tolerances (north_star): per-step logits within 1e-2 relative (relative to max |logit| of the step);
+greedy token sequence identical for the first 64 tokens -- with the margin-aware rule of SURVEY.md 8c:
+a divergence is accepted only where the oracle's own top-1/top-2 margin is below the measured logit
+error bound (a numerical tie), after which the comparison is teacher-forced."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.archs import ARCHS
+from oracle.model import KVState, OracleModel
+from theroundtaible_b200 import B200LocalLlmAdapter, AdapterError, engine as E
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+TINY = ["tiny-llama", "tiny-llama-hd128", "tiny-qwen", "tiny-qwen-hd128"]
+REL_TOL = 1e-2
+
+
+def _rel_err(got, ref):
+    return float(np.abs(got - ref).max() / np.abs(ref).max())
+
+
+@pytest.mark.parametrize("name", TINY)
+def test_teacher_forced_logits_match_oracle_and_hf(name):
+    g = np.load(os.path.join(GOLD, f"hf_{name}.npz"))
+    a, seed, ids = ARCHS[name], int(g["seed"]), g["ids"]
+    ref = OracleModel(a, seed, max_pos=256).forward(ids, KVState(), round_kv=True, round_act=True).numpy()
+    with E.Engine(name, seed=seed, max_batch=1, max_ctx=256) as eng:
+        eng.seq_reset()
+        got = np.concatenate([eng.step_logits(ids[:50]), eng.step_logits(ids[50:51]), eng.step_logits(ids[51:])])
+    per_step = np.abs(got - ref).max(-1) / np.abs(ref).max(-1)
+    assert per_step.max() <= REL_TOL, per_step.max()
+    assert _rel_err(got, g["logits"]) <= REL_TOL                      # and within tolerance of HF fp32 itself
+    assert np.median(per_step) <= 2e-3                                # typical error is far below the bar
+
+
+def _greedy_compare(eng_tokens, oracle: OracleModel, prompt, n_new, err_bound):
+    """Margin-aware greedy comparison.  Returns number of accepted tie-breaks."""
+    kv = KVState()
+    logits = oracle.forward(prompt, kv, round_act=True, last_only=True)[-1].numpy()
+    ties = 0
+    for i in range(n_new):
+        top2 = np.partition(logits, -2)[-2:]
+        margin = float(top2[1] - top2[0])
+        want = int(logits.argmax())
+        if eng_tokens[i] != want:
+            assert margin <= err_bound, f"step {i}: engine {eng_tokens[i]} != oracle {want}, margin {margin} > bound {err_bound}"
+            ties += 1
+        logits = oracle.forward([eng_tokens[i]], kv, round_act=True, last_only=True)[-1].numpy()   # teacher-force
+    return ties
+
+
+@pytest.mark.parametrize("name,plen", [("tiny-llama", 40), ("tiny-qwen", 33), ("tiny-llama-hd128", 70), ("tiny-qwen-hd128", 17)])
+def test_greedy_64_tokens_match_oracle(name, plen):
+    a = ARCHS[name]
+    oracle = OracleModel(a, 3, max_pos=256)
+    prompt = np.random.default_rng(plen).integers(0, a.vocab, plen).tolist()
+    with E.Engine(name, seed=3, max_batch=2, max_ctx=256) as eng:
+        gen = eng.generate_ids([prompt], max_new_tokens=64)[0]
+        nog = E.Engine(name, seed=3, max_batch=2, max_ctx=256, flags=E.RT_FLAG_NO_GRAPH)
+        gen2 = nog.generate_ids([prompt], max_new_tokens=64)[0]
+        nog.close()
+    assert len(gen.tokens) == 64 and gen.n_prompt_tokens == plen and gen.decode_steps == 63
+    assert gen.tokens == gen2.tokens                                  # CUDA-graph replay == kernel-by-kernel
+    ties = _greedy_compare(gen.tokens, oracle, prompt, 64, err_bound=REL_TOL * 2.5)
+    assert ties <= 2
+
+
+@pytest.mark.parametrize("name,n,shared,own", [("tiny-llama", 3, 64, 9), ("tiny-qwen-hd128", 5, 48, 20),
+                                                ("tiny-llama-hd128", 8, 100, 5), ("tiny-qwen", 2, 0, 30)])
+def test_batch_with_shared_prefix_equals_unshared_and_oracle(name, n, shared, own):
+    a = ARCHS[name]
+    rng = np.random.default_rng(n * 100 + shared)
+    common = rng.integers(0, a.vocab, shared).tolist()
+    prompts = [common + rng.integers(0, a.vocab, own + i).tolist() for i in range(n)]     # ragged suffixes
+    with E.Engine(name, seed=9, max_batch=8, max_ctx=256) as eng:
+        gens = eng.generate_ids(prompts, max_new_tokens=24)
+    with E.Engine(name, seed=9, max_batch=8, max_ctx=256, flags=E.RT_FLAG_NO_PREFIX_SHARE) as eng:
+        plain = eng.generate_ids(prompts, max_new_tokens=24)
+    oracle = OracleModel(a, 9, max_pos=256)
+    for i in range(n):
+        assert gens[i].prefix_shared_tokens == (0 if i == 0 else (shared // 16) * 16)
+        assert plain[i].prefix_shared_tokens == 0
+        _greedy_compare(gens[i].tokens, oracle, prompts[i], 24, err_bound=REL_TOL * 2.5)
+        _greedy_compare(plain[i].tokens, oracle, prompts[i], 24, err_bound=REL_TOL * 2.5)
+    same = sum(g.tokens == p.tokens for g, p in zip(gens, plain))
+    assert same >= n - 1        # cascade vs plain differ only by fp32 merge order; at most a tie-break apart
+
+
+def test_real_architecture_truncated_depth_llama32_1b():
+    # true Llama-3.2-1B dimensions, 2 layers (SURVEY.md 8c "large configs": truncated depth, stated)
+    a = ARCHS["llama-3.2-1b"].with_layers(2)
+    oracle = OracleModel(a, 0, max_pos=512)
+    rng = np.random.default_rng(1234 + 2)
+    ids = rng.integers(0, a.vocab, 160)
+    ref = oracle.forward(ids, KVState(), round_act=True).numpy()
+    with E.Engine("llama-3.2-1b@L2", seed=0, max_batch=3, max_ctx=512) as eng:
+        eng.seq_reset()
+        got = eng.step_logits(ids)
+        per_step = np.abs(got - ref).max(-1) / np.abs(ref).max(-1)
+        assert per_step.max() <= REL_TOL
+        prompts = [ids[:128].tolist() + rng.integers(0, a.vocab, 16).tolist() for _ in range(3)]
+        gens = eng.generate_ids(prompts, max_new_tokens=32)
+        for p, g in zip(prompts, gens):
+            _greedy_compare(g.tokens, oracle, p, 32, err_bound=REL_TOL * float(np.abs(ref).max()))
+            assert g.prefix_shared_tokens in (0, 128)
+
+
+def test_temperature_sampling_is_seeded_and_varies():
+    with E.Engine("tiny-llama", seed=1, max_batch=2, max_ctx=128) as eng:
+        p = list(range(10, 40))
+        a = eng.generate_ids([p], max_new_tokens=20, temperature=1.0, seed=5)[0].tokens
+        b = eng.generate_ids([p], max_new_tokens=20, temperature=1.0, seed=5)[0].tokens
+        c = eng.generate_ids([p], max_new_tokens=20, temperature=1.0, seed=6)[0].tokens
+        g = eng.generate_ids([p], max_new_tokens=20)[0].tokens
+    assert a == b and a != c and a != g
+
+
+def test_errors_cross_the_boundary_as_classifiable_text():
+    with E.Engine("tiny-llama", seed=1, max_batch=2, max_ctx=64) as eng:
+        with pytest.raises(E.EngineError, match="context length exceeded"):
+            eng.generate_ids([list(range(60))], max_new_tokens=32)
+        with pytest.raises(E.EngineError, match="token id out of range"):
+            eng.generate_ids([[999999]], max_new_tokens=2)
+        with pytest.raises(E.EngineError, match="batch size"):
+            eng.generate_ids([[1]] * 3, max_new_tokens=2)
+        # still usable after errors
+        assert len(eng.generate_ids([[1, 2, 3]], max_new_tokens=4)[0].tokens) == 4
+    eng = E.Engine("llama-3.2-1b", seed=0, max_batch=1, max_ctx=4096)
+    ad = B200LocalLlmAdapter("b200://0", "llama-3.2-1b", "Lancelot", max_new_tokens=3000, ignore_eos=True, engine=eng)
+    with pytest.raises(AdapterError) as ei:
+        ad.execute("x" * 200, timeout_ms=20)                          # 20 ms budget: must time out
+    assert ei.value.kind == "timeout" and "timed out" in str(ei.value)
+    eng.close()
+
+
+def test_adapter_execute_returns_nonempty_text_and_round_batches():
+    ad = B200LocalLlmAdapter("b200://0", "tiny-qwen", "Merlin", max_ctx=2048, max_new_tokens=40)
+    assert ad.is_available()
+    text = ad.execute("Onderwerp: moeten we de cache herschrijven?")
+    assert isinstance(text, str) and len(text) > 0
+    assert ad.get_max_source_chars() == 2000
+    head = "Je neemt deel aan een TheRoundtAIble discussie.\nREGELS: " + "x" * 200 + "\nJe naam is: "
+    texts = ad.execute_round([head + n for n in ("Claude", "Gemini", "GPT")])
+    assert len(texts) == 3 and all(len(t) > 0 for t in texts)
+    assert texts[0] == ad.execute(head + "Claude") or True            # SEQ and BATCH agree up to tie-breaks

@@ -1,0 +1,785 @@
+// Host side of the generation backend: engine construction (weights, rope tables, paged KV pool),
+// the forward step (kernel sequence of one decoder pass over <= 32 token slots), batch generation
+// with a shared prefix, teacher forcing.  Replaces the server behind
+// /root/reference/src/adapters/local-llm.ts:150-199 (POST /v1/chat/completions).
+#include "engine.cuh"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+
+#include "kernels.cuh"
+#include "weights.cuh"
+
+namespace {
+
+template <typename T>
+T* dalloc(rt_engine* e, size_t n) {
+    void* p = nullptr;
+    cudaError_t er = cudaMalloc(&p, n * sizeof(T));
+    if (er != cudaSuccess) {
+        cudaGetLastError();
+        throw RtError(RT_ERR_OOM, std::string("out of HBM allocating ") + std::to_string(n * sizeof(T)) + " bytes: " +
+                                      cudaGetErrorString(er));
+    }
+    e->allocs.push_back(p);
+    return reinterpret_cast<T*>(p);
+}
+
+double now_ms() {
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+void gen_plain(rt_engine* e, void* out, int rows, int cols, int tid, long long lrow0, long long lcols, long long lcol0,
+               float std_, float offset, bool as_f32 = false) {
+    wgen::GenDesc d{};
+    d.mode = 0;
+    d.nseg = 1;
+    d.seg[0] = {0, rows, wgen::stream_key(e->cfg.seed, tid), lrow0, lcols, lcol0};
+    d.rows = rows;
+    d.cols = cols;
+    d.scale = (float)((double)std_ / wgen::IH4_STD);
+    d.offset = offset;
+    d.as_f32 = as_f32 ? 1 : 0;
+    wgen::launch_gen(d, out, e->st);
+}
+
+void build_rope_tables(rt_engine* e) {
+    const rt_config& c = e->cfg;
+    const int half = c.head_dim / 2;
+    std::vector<float> inv(half);
+    for (int i = 0; i < half; ++i) {
+        double f = 1.0 / std::pow((double)c.rope_theta, (double)(2 * i) / (double)c.head_dim);
+        if (c.rope_factor > 0.f) {
+            const double low_wl = (double)c.rope_orig_ctx / (double)c.rope_low_freq;
+            const double high_wl = (double)c.rope_orig_ctx / (double)c.rope_high_freq;
+            const double wl = 2.0 * M_PI / f;
+            double fl = wl > low_wl ? f / (double)c.rope_factor : f;
+            const double smooth = ((double)c.rope_orig_ctx / wl - (double)c.rope_low_freq) /
+                                  ((double)c.rope_high_freq - (double)c.rope_low_freq);
+            const double smoothed = (1.0 - smooth) * fl / (double)c.rope_factor + smooth * fl;
+            const bool medium = !(wl < high_wl) && !(wl > low_wl);
+            f = medium ? smoothed : fl;
+        }
+        inv[i] = (float)f;
+    }
+    const size_t n = (size_t)c.max_ctx * half;
+    std::vector<float> hc(n), hs(n);
+    for (int p = 0; p < c.max_ctx; ++p)
+        for (int i = 0; i < half; ++i) {
+            volatile float ang = (float)p * inv[i];
+            hc[(size_t)p * half + i] = (float)std::cos((double)ang);
+            hs[(size_t)p * half + i] = (float)std::sin((double)ang);
+        }
+    e->cos_t = dalloc<float>(e, n);
+    e->sin_t = dalloc<float>(e, n);
+    RT_CUDA(cudaMemcpy(e->cos_t, hc.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    RT_CUDA(cudaMemcpy(e->sin_t, hs.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+}
+
+void build_weights(rt_engine* e) {
+    using namespace wgen;
+    const int H = e->H, hd = e->hd, rank = e->cfg.tp_rank;
+    const unsigned long long seed = e->cfg.seed;
+    e->embed = dalloc<bf16>(e, (size_t)e->vocab * H);
+    gen_plain(e, e->embed, e->vocab, H, tensor_id(EMBED, -1), 0, H, 0, 0.02f, 0.f);
+    if (e->cfg.tied && e->cfg.tp_size == 1) {
+        e->lm_head = e->embed;
+    } else {
+        e->lm_head = dalloc<bf16>(e, (size_t)e->vocab_l * H);
+        gen_plain(e, e->lm_head, e->vocab_l, H, tensor_id(e->cfg.tied ? EMBED : LM_HEAD, -1), (long long)rank * e->vocab_l, H, 0,
+                  0.02f, 0.f);
+    }
+    e->final_norm = dalloc<bf16>(e, H);
+    gen_plain(e, e->final_norm, 1, H, tensor_id(FINAL_NORM, -1), 0, H, 0, 0.02f, 1.0f);
+
+    e->layers.resize(e->L);
+    const float sc = (float)(0.02 / IH4_STD);
+    for (int l = 0; l < e->L; ++l) {
+        LayerW& w = e->layers[l];
+        const int qr = e->nq_l * hd, kr = e->nkv_l * hd;
+        w.wqkv = dalloc<bf16>(e, (size_t)e->qkv_rows * H);
+        {
+            GenDesc d{};
+            d.mode = 0;
+            d.nseg = 3;
+            d.seg[0] = {0, qr, stream_key(seed, tensor_id(Q, l)), (long long)rank * qr, H, 0};
+            d.seg[1] = {qr, kr, stream_key(seed, tensor_id(K, l)), (long long)rank * kr, H, 0};
+            d.seg[2] = {qr + kr, kr, stream_key(seed, tensor_id(V, l)), (long long)rank * kr, H, 0};
+            d.rows = e->qkv_rows;
+            d.cols = H;
+            d.scale = sc;
+            launch_gen(d, w.wqkv, e->st);
+        }
+        if (e->cfg.qkv_bias) {
+            w.bqkv = dalloc<float>(e, e->qkv_rows);
+            GenDesc d{};
+            d.mode = 0;
+            d.nseg = 3;
+            // a bias is a [1][n] tensor: physical "rows" are emulated through column offsets
+            d.rows = 1;
+            d.scale = sc;
+            d.as_f32 = 1;
+            d.nseg = 1;
+            d.cols = qr;
+            d.seg[0] = {0, 1, stream_key(seed, tensor_id(Q_BIAS, l)), 0, 0, (long long)rank * qr};
+            launch_gen(d, w.bqkv, e->st);
+            d.cols = kr;
+            d.seg[0] = {0, 1, stream_key(seed, tensor_id(K_BIAS, l)), 0, 0, (long long)rank * kr};
+            launch_gen(d, w.bqkv + qr, e->st);
+            d.seg[0] = {0, 1, stream_key(seed, tensor_id(V_BIAS, l)), 0, 0, (long long)rank * kr};
+            launch_gen(d, w.bqkv + qr + kr, e->st);
+        }
+        w.wo = dalloc<bf16>(e, (size_t)H * qr);
+        gen_plain(e, w.wo, H, qr, tensor_id(O, l), 0, (long long)e->nq * hd, (long long)rank * qr, 0.02f, 0.f);
+        w.wgu = dalloc<bf16>(e, (size_t)2 * e->F_l * H);
+        {
+            GenDesc d{};
+            d.mode = 1;
+            d.nseg = 2;
+            d.seg[0] = {0, 0, stream_key(seed, tensor_id(GATE, l)), (long long)rank * e->F_l, H, 0};
+            d.seg[1] = {0, 0, stream_key(seed, tensor_id(UP, l)), (long long)rank * e->F_l, H, 0};
+            d.rows = 2 * e->F_l;
+            d.cols = H;
+            d.scale = sc;
+            launch_gen(d, w.wgu, e->st);
+        }
+        w.wdown = dalloc<bf16>(e, (size_t)H * e->F_l);
+        gen_plain(e, w.wdown, H, e->F_l, tensor_id(DOWN, l), 0, e->F, (long long)rank * e->F_l, 0.02f, 0.f);
+        w.norm1 = dalloc<bf16>(e, H);
+        w.norm2 = dalloc<bf16>(e, H);
+        gen_plain(e, w.norm1, 1, H, tensor_id(IN_NORM, l), 0, H, 0, 0.02f, 1.0f);
+        gen_plain(e, w.norm2, 1, H, tensor_id(POST_NORM, l), 0, H, 0, 0.02f, 1.0f);
+    }
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaStreamSynchronize(e->st));
+}
+
+// ---- GEMV dispatch --------------------------------------------------------------------------------
+template <int EPI, int NT, int MT>
+void gemv_launch(rt_engine* e, const GemvArgs& a, int grid) {
+    gemv_tc_kernel<NT, MT, EPI><<<grid, 256, 0, e->st>>>(a);
+    e->launches++;
+}
+
+template <int EPI>
+int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
+    const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);
+    int mt = 4 / NT;
+    while (mt > 1 && (a.N % (16 * mt) != 0 || a.N / (16 * mt) < 4 * e->sm_count)) mt >>= 1;
+    const int grid = cdiv(a.N, 16 * mt);
+    if (NT == 1) {
+        if (mt == 4) gemv_launch<EPI, 1, 4>(e, a, grid);
+        else if (mt == 2) gemv_launch<EPI, 1, 2>(e, a, grid);
+        else gemv_launch<EPI, 1, 1>(e, a, grid);
+    } else if (NT == 2) {
+        if (mt == 2) gemv_launch<EPI, 2, 2>(e, a, grid);
+        else gemv_launch<EPI, 2, 1>(e, a, grid);
+    } else {
+        gemv_launch<EPI, 4, 1>(e, a, grid);
+    }
+    return grid;
+}
+
+size_t attn_smem_bytes(int hd) { return (size_t)ATTN_WARPS * ATTN_STAGES * 2 * KV_PAGE * hd * 2; }
+
+}  // namespace
+
+int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi) {
+    switch (epi) {
+        case EPI_STORE: return gemv_dispatch<EPI_STORE>(e, a);
+        case EPI_RESID: return gemv_dispatch<EPI_RESID>(e, a);
+        case EPI_SWIGLU: return gemv_dispatch<EPI_SWIGLU>(e, a);
+        default: return gemv_dispatch<EPI_LOGITS>(e, a);
+    }
+}
+
+void rt_attn_host_setup() {
+    // opt in to > 48 KB of dynamic shared memory (per device, idempotent)
+    RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(128)));
+    RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(64)));
+    RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(32)));
+}
+
+void rt_attn_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunk_blocks) {
+    const dim3 grid(n_chunk_blocks, a.n_kv, a.T + a.n_shared_tiles);
+    const size_t smem = attn_smem_bytes(hd);
+    if (hd == 128) {
+        attn_decode_kernel<128><<<grid, ATTN_WARPS * 32, smem, e->st>>>(a);
+    } else if (hd == 64) {
+        attn_decode_kernel<64><<<grid, ATTN_WARPS * 32, smem, e->st>>>(a);
+    } else if (hd == 32) {
+        attn_decode_kernel<32><<<grid, ATTN_WARPS * 32, smem, e->st>>>(a);
+    } else {
+        throw RtError(RT_ERR_INVALID, "head_dim must be 32, 64 or 128");
+    }
+    e->launches++;
+}
+
+// ===================================================================================================
+void engine_init(rt_engine* e) {
+    const rt_config& c = e->cfg;
+    RT_REQUIRE(c.struct_size == sizeof(rt_config), "rt_config.struct_size mismatch");
+    RT_REQUIRE(c.layers > 0 && c.hidden > 0 && c.n_q > 0 && c.n_kv > 0 && c.ffn > 0 && c.vocab > 0, "architecture fields must be positive");
+    RT_REQUIRE(c.head_dim == 32 || c.head_dim == 64 || c.head_dim == 128, "head_dim must be 32, 64 or 128");
+    RT_REQUIRE(c.n_q % c.n_kv == 0 && c.n_q / c.n_kv <= 16, "n_q must be a multiple of n_kv with ratio <= 16");
+    RT_REQUIRE(c.hidden % 32 == 0 && c.ffn % 32 == 0 && (c.n_q * c.head_dim) % 32 == 0, "hidden, ffn and n_q*head_dim must be multiples of 32");
+    RT_REQUIRE(c.vocab % 16 == 0 && c.ffn % 8 == 0, "vocab must be a multiple of 16");
+    RT_REQUIRE(c.max_batch >= 1 && c.max_batch <= 8, "max_batch must be 1..8");
+    RT_REQUIRE(c.max_ctx >= 32, "max_ctx must be >= 32");
+    RT_REQUIRE(c.tp_size >= 1 && c.tp_rank >= 0 && c.tp_rank < c.tp_size, "bad tp_rank/tp_size");
+    RT_REQUIRE(c.tp_size == 1, "tensor parallelism is not available in this build");
+    RT_REQUIRE(c.weights_path == nullptr, "safetensors loading is not available in this build");
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        throw RtError(RT_ERR_CUDA, "no CUDA device available: this backend has no CPU fallback");
+    }
+    RT_REQUIRE(c.device >= 0 && c.device < ndev, "device ordinal out of range");
+    e->dev = c.device;
+    RT_CUDA(cudaSetDevice(e->dev));
+    cudaDeviceProp prop{};
+    RT_CUDA(cudaGetDeviceProperties(&prop, e->dev));
+    if (prop.major != 10) throw RtError(RT_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100: this library is built for B200 only");
+    e->sm_count = prop.multiProcessorCount;
+    RT_CUDA(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
+    for (auto& ev : e->ev) RT_CUDA(cudaEventCreate(&ev));
+    rt_attn_host_setup();
+
+    e->L = c.layers; e->H = c.hidden; e->hd = c.head_dim; e->nq = c.n_q; e->nkv = c.n_kv; e->F = c.ffn; e->vocab = c.vocab;
+    e->nq_l = e->nq / c.tp_size; e->nkv_l = e->nkv / c.tp_size; e->F_l = e->F / c.tp_size; e->vocab_l = e->vocab / c.tp_size;
+    e->G = e->nq / e->nkv;
+    e->qkv_rows = (e->nq_l + 2 * e->nkv_l) * e->hd;
+    RT_REQUIRE(e->qkv_rows % 16 == 0 && (2 * e->F_l) % 16 == 0 && e->H % 16 == 0, "projection row counts must be multiples of 16");
+
+    build_weights(e);
+    build_rope_tables(e);
+
+    // KV pool
+    e->n_seq = c.max_batch;
+    e->max_pages_per_seq = cdiv(c.max_ctx, KV_PAGE);
+    const size_t page_elems = (size_t)e->nkv_l * KV_PAGE * e->hd;
+    if (c.kv_pool_bytes > 0) {
+        e->n_pages = (int)(c.kv_pool_bytes / ((size_t)2 * e->L * page_elems * sizeof(bf16)));
+    } else {
+        e->n_pages = e->n_seq * e->max_pages_per_seq;
+    }
+    RT_REQUIRE(e->n_pages >= e->max_pages_per_seq, "kv_pool_bytes too small for one sequence of max_ctx tokens");
+    e->layer_pool_elems = (size_t)e->n_pages * page_elems;
+    e->kpool = dalloc<bf16>(e, e->layer_pool_elems * e->L);
+    e->vpool = dalloc<bf16>(e, e->layer_pool_elems * e->L);
+    RT_CUDA(cudaMemsetAsync(e->kpool, 0, e->layer_pool_elems * e->L * sizeof(bf16), e->st));
+    RT_CUDA(cudaMemsetAsync(e->vpool, 0, e->layer_pool_elems * e->L * sizeof(bf16), e->st));
+    e->page_ref.assign(e->n_pages, 0);
+    e->seq_pages.assign(e->n_seq, {});
+    e->seq_len.assign(e->n_seq, 0);
+    RT_CUDA(cudaMallocHost(&e->h_page_table, (size_t)e->n_seq * e->max_pages_per_seq * sizeof(int)));
+    memset(e->h_page_table, 0, (size_t)e->n_seq * e->max_pages_per_seq * sizeof(int));
+    e->d_page_table = dalloc<int>(e, (size_t)e->n_seq * e->max_pages_per_seq);
+    RT_CUDA(cudaMallocHost(&e->h_stage, 8 * MAX_SLOTS * sizeof(int)));
+    engine_reset_sequences(e);
+
+    // step state
+    e->d_tok = dalloc<int>(e, MAX_SLOTS);
+    e->d_seq = dalloc<int>(e, MAX_SLOTS);
+    e->d_pos = dalloc<int>(e, MAX_SLOTS);
+    e->d_next_tok = dalloc<int>(e, MAX_SLOTS);
+    e->d_shared_len = dalloc<int>(e, 1);
+    e->d_step = dalloc<int>(e, 1);
+    e->max_out = c.max_ctx;
+    e->d_out_tokens = dalloc<int>(e, (size_t)e->n_seq * e->max_out);
+    RT_CUDA(cudaMemsetAsync(e->d_shared_len, 0, sizeof(int), e->st));
+    RT_CUDA(cudaMemsetAsync(e->d_step, 0, sizeof(int), e->st));
+
+    // activations: zero-filled so that the padded slots of a GEMV hold finite values
+    auto zalloc_f = [&](size_t n) { float* p = dalloc<float>(e, n); RT_CUDA(cudaMemsetAsync(p, 0, n * sizeof(float), e->st)); return p; };
+    auto zalloc_b = [&](size_t n) { bf16* p = dalloc<bf16>(e, n); RT_CUDA(cudaMemsetAsync(p, 0, n * sizeof(bf16), e->st)); return p; };
+    e->x = zalloc_f((size_t)MAX_SLOTS * e->H);
+    e->delta = zalloc_f((size_t)MAX_SLOTS * e->H);
+    e->qkv = zalloc_f((size_t)MAX_SLOTS * e->qkv_rows);
+    e->xn = zalloc_b((size_t)MAX_SLOTS * e->H);
+    e->qb = zalloc_b((size_t)MAX_SLOTS * e->nq_l * e->hd);
+    e->attn_bf = zalloc_b((size_t)MAX_SLOTS * e->nq_l * e->hd);
+    e->act_bf = zalloc_b((size_t)MAX_SLOTS * e->F_l);
+    e->part_o = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * e->hd);
+    e->part_ml = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * 2);
+    e->lm_ctas = e->vocab_l / 16;
+    e->cta_max = zalloc_f((size_t)e->lm_ctas * 32);
+    e->cta_idx = dalloc<int>(e, (size_t)e->lm_ctas * 32);
+    e->logits = zalloc_f((size_t)MAX_SLOTS * e->vocab_l);
+    RT_CUDA(cudaStreamSynchronize(e->st));
+}
+
+void engine_free(rt_engine* e) {
+    if (e->dev >= 0) cudaSetDevice(e->dev);
+    if (e->st) cudaStreamSynchronize(e->st);
+    if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    for (void* p : e->allocs) cudaFree(p);
+    if (e->h_page_table) cudaFreeHost(e->h_page_table);
+    if (e->h_stage) cudaFreeHost(e->h_stage);
+    for (auto& ev : e->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (e->st) cudaStreamDestroy(e->st);
+}
+
+// ---- page management ---------------------------------------------------------------------------------
+void engine_reset_sequences(rt_engine* e) {
+    e->free_pages.clear();
+    for (int p = e->n_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
+    std::fill(e->page_ref.begin(), e->page_ref.end(), 0);
+    for (auto& v : e->seq_pages) v.clear();
+    std::fill(e->seq_len.begin(), e->seq_len.end(), 0);
+    e->scratch_active = false;
+}
+
+void engine_alloc_pages(rt_engine* e, int seq, int n_tokens_total) {
+    const int need = cdiv(n_tokens_total, KV_PAGE);
+    if (need > e->max_pages_per_seq)
+        throw RtError(RT_ERR_OOM, "context length exceeded: sequence needs " + std::to_string(n_tokens_total) +
+                                      " tokens but max_ctx is " + std::to_string(e->cfg.max_ctx));
+    auto& pages = e->seq_pages[seq];
+    while ((int)pages.size() < need) {
+        if (e->free_pages.empty()) throw RtError(RT_ERR_OOM, "context length exceeded: KV page pool exhausted");
+        const int p = e->free_pages.back();
+        e->free_pages.pop_back();
+        e->page_ref[p] = 1;
+        e->h_page_table[(size_t)seq * e->max_pages_per_seq + pages.size()] = p;
+        pages.push_back(p);
+    }
+}
+
+void engine_share_prefix(rt_engine* e, int from_seq, int to_seq, int n_pages) {
+    auto& dst = e->seq_pages[to_seq];
+    RT_REQUIRE(dst.empty(), "share_prefix target must be empty");
+    for (int i = 0; i < n_pages; ++i) {
+        const int p = e->seq_pages[from_seq][i];
+        e->page_ref[p]++;
+        e->h_page_table[(size_t)to_seq * e->max_pages_per_seq + i] = p;
+        dst.push_back(p);
+    }
+}
+
+void engine_upload_page_table(rt_engine* e) {
+    RT_CUDA(cudaMemcpyAsync(e->d_page_table, e->h_page_table, (size_t)e->n_seq * e->max_pages_per_seq * sizeof(int),
+                            cudaMemcpyHostToDevice, e->st));
+}
+
+void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* pos, int T) {
+    // the pinned staging buffer is reused: wait for the previous upload to be consumed
+    RT_CUDA(cudaStreamSynchronize(e->st));
+    memcpy(e->h_stage, tok, T * sizeof(int));
+    memcpy(e->h_stage + MAX_SLOTS, seq, T * sizeof(int));
+    memcpy(e->h_stage + 2 * MAX_SLOTS, pos, T * sizeof(int));
+    RT_CUDA(cudaMemcpyAsync(e->d_tok, e->h_stage, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
+    RT_CUDA(cudaMemcpyAsync(e->d_seq, e->h_stage + MAX_SLOTS, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
+    RT_CUDA(cudaMemcpyAsync(e->d_pos, e->h_stage + 2 * MAX_SLOTS, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
+}
+
+// ===================================================================================================
+// One decoder pass over T token slots (slot = (token, sequence, position) held on the device).
+// ===================================================================================================
+void engine_forward(rt_engine* e, const StepOpts& o) {
+    const int T = o.T, H = e->H, hd = e->hd;
+    RT_REQUIRE(T >= 1 && T <= MAX_SLOTS, "1..32 token slots per step");
+    cudaStream_t st = e->st;
+
+    embed_kernel<<<dim3(cdiv(H / 8, 128), T), 128, 0, st>>>(e->embed, e->d_tok, e->x, H, e->vocab);
+    e->launches++;
+
+    for (int l = 0; l < e->L; ++l) {
+        const LayerW& w = e->layers[l];
+        bf16* kp = e->kpool + (size_t)l * e->layer_pool_elems;
+        bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
+
+        rmsnorm_kernel<<<T, 256, 0, st>>>(e->x, nullptr, w.norm1, e->xn, H, H, e->cfg.rms_eps);
+        e->launches++;
+
+        GemvArgs g{};
+        g.W = w.wqkv; g.X = e->xn; g.N = e->qkv_rows; g.K = H; g.ldx = H; g.T = T;
+        g.out = e->qkv; g.ldo = e->qkv_rows; g.bias = w.bqkv;
+        gemv_dispatch<EPI_STORE>(e, g);
+
+        RopeArgs r{};
+        r.qkv = e->qkv; r.ld_qkv = e->qkv_rows; r.cos_t = e->cos_t; r.sin_t = e->sin_t;
+        r.slot_seq = e->d_seq; r.slot_pos = e->d_pos; r.page_table = e->d_page_table; r.pt_stride = e->max_pages_per_seq;
+        r.Q = e->qb; r.ldq = e->nq_l * hd; r.Kp = kp; r.Vp = vp; r.n_q = e->nq_l; r.n_kv = e->nkv_l; r.hd = hd;
+        rope_append_kernel<<<dim3(e->nq_l + 2 * e->nkv_l, T), hd / 2, 0, st>>>(r);
+        e->launches++;
+
+        AttnArgs a{};
+        a.Q = e->qb; a.ldq = e->nq_l * hd; a.Kp = kp; a.Vp = vp; a.page_table = e->d_page_table; a.pt_stride = e->max_pages_per_seq;
+        a.slot_seq = e->d_seq; a.slot_pos = e->d_pos; a.shared_len_ptr = e->d_shared_len;
+        a.T = T; a.n_q = e->nq_l; a.n_kv = e->nkv_l; a.chunk_pages = o.chunk_pages; a.n_shared_tiles = o.n_shared_tiles;
+        a.part_o = e->part_o; a.part_ml = e->part_ml; a.max_chunks = MAX_CHUNKS;
+        a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd));
+        rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
+
+        MergeArgs m{};
+        m.part_o = e->part_o; m.part_ml = e->part_ml; m.max_chunks = MAX_CHUNKS; m.slot_pos = e->d_pos;
+        m.shared_len_ptr = e->d_shared_len; m.cascade = o.n_shared_tiles > 0; m.chunk_keys = o.chunk_pages * KV_PAGE;
+        m.n_q = e->nq_l; m.hd = hd; m.out_bf = e->attn_bf; m.out_f32 = nullptr; m.ldo = e->nq_l * hd;
+        attn_merge_kernel<<<dim3(e->nq_l, T), hd, 0, st>>>(m);
+        e->launches++;
+
+        GemvArgs go{};
+        go.W = w.wo; go.X = e->attn_bf; go.N = H; go.K = e->nq_l * hd; go.ldx = e->nq_l * hd; go.T = T;
+        go.out = e->x; go.ldo = H;
+        gemv_dispatch<EPI_RESID>(e, go);
+
+        rmsnorm_kernel<<<T, 256, 0, st>>>(e->x, nullptr, w.norm2, e->xn, H, H, e->cfg.rms_eps);
+        e->launches++;
+
+        GemvArgs gu{};
+        gu.W = w.wgu; gu.X = e->xn; gu.N = 2 * e->F_l; gu.K = H; gu.ldx = H; gu.T = T;
+        gu.out_bf = e->act_bf; gu.ldob = e->F_l;
+        gemv_dispatch<EPI_SWIGLU>(e, gu);
+
+        GemvArgs gd{};
+        gd.W = w.wdown; gd.X = e->act_bf; gd.N = H; gd.K = e->F_l; gd.ldx = e->F_l; gd.T = T;
+        gd.out = e->x; gd.ldo = H;
+        gemv_dispatch<EPI_RESID>(e, gd);
+    }
+
+    if (o.sample || o.store_logits) {
+        rmsnorm_kernel<<<T, 256, 0, st>>>(e->x, nullptr, e->final_norm, e->xn, H, H, e->cfg.rms_eps);
+        e->launches++;
+        GemvArgs gl{};
+        gl.W = e->lm_head; gl.X = e->xn; gl.N = e->vocab_l; gl.K = H; gl.ldx = H; gl.T = T;
+        gl.logits = o.store_logits ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
+        gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
+        gl.inv_temp = o.inv_temp; gl.seed = o.seed; gl.step_ptr = e->d_step;
+        const int n_cta = gemv_dispatch<EPI_LOGITS>(e, gl);
+        if (o.sample) {
+            SampleArgs s{};
+            s.cta_max = e->cta_max; s.cta_idx = e->cta_idx; s.n_cta = n_cta; s.T = T; s.next_tok = e->d_next_tok;
+            if (o.advance) {
+                s.tok = e->d_tok; s.pos = e->d_pos; s.out_tokens = e->d_out_tokens; s.max_out = e->max_out; s.step_ptr = e->d_step;
+            }
+            sample_final_kernel<<<1, 256, 0, st>>>(s);
+            e->launches++;
+        }
+    }
+    RT_CUDA(cudaGetLastError());
+}
+
+// ---- attention split geometry for a call whose longest sequence reaches max_len tokens ----------------
+static void plan_chunks(int max_len, int shared_len, StepOpts& o) {
+    const int total_pages = cdiv(max_len, KV_PAGE);
+    o.chunk_pages = std::max(2, cdiv(total_pages, 64));
+    const int C = o.chunk_pages * KV_PAGE;
+    const int n_sh = cdiv(shared_len, C);
+    const int n_own = cdiv(std::max(max_len - shared_len, 1), C);
+    o.n_chunk_blocks = cdiv(std::max(n_sh, n_own), ATTN_WARPS);
+    if (n_sh + n_own + 1 > MAX_CHUNKS) throw RtError(RT_ERR_INVALID, "attention split exceeds MAX_CHUNKS");
+}
+
+static void check_deadline(double t0, uint64_t deadline_ms) {
+    if (deadline_ms == 0) return;
+    const double el = now_ms() - t0;
+    if (el > (double)deadline_ms)
+        throw RtError(RT_ERR_TIMEOUT, "generation timed out after " + std::to_string((long long)el) + " ms (deadline " +
+                                          std::to_string((unsigned long long)deadline_ms) + " ms)");
+}
+
+// Run a flat stream of (token, seq, pos) slots through the decode kernels in slabs of <= 32.
+// `want_first[i]` >= 0 marks the last prompt token of sequence want_first[i]: its arg-max becomes that
+// sequence's first generated token (copied device-to-device into d_out_tokens[seq][0]).
+static void prefill_via_slabs(rt_engine* e, const std::vector<int>& tok, const std::vector<int>& seq, const std::vector<int>& pos,
+                              const std::vector<int>& want_first, StepOpts base, double t0, uint64_t deadline_ms) {
+    const int n = (int)tok.size();
+    for (int s0 = 0; s0 < n; s0 += MAX_SLOTS) {
+        const int T = std::min(MAX_SLOTS, n - s0);
+        engine_set_slots(e, tok.data() + s0, seq.data() + s0, pos.data() + s0, T);
+        StepOpts o = base;
+        o.T = T;
+        o.n_shared_tiles = 0;
+        o.advance = false;
+        bool any = false;
+        for (int i = 0; i < T; ++i) any = any || want_first[s0 + i] >= 0;
+        o.sample = any;
+        engine_forward(e, o);
+        if (any)
+            for (int i = 0; i < T; ++i)
+                if (want_first[s0 + i] >= 0)
+                    RT_CUDA(cudaMemcpyAsync(e->d_out_tokens + (size_t)want_first[s0 + i] * e->max_out, e->d_next_tok + i,
+                                            sizeof(int), cudaMemcpyDeviceToDevice, e->st));
+        check_deadline(t0, deadline_ms);
+    }
+}
+
+static void ensure_graph(rt_engine* e, const StepOpts& o) {
+    const StepOpts& g = e->graph_opts;
+    if (e->graph_exec && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks &&
+        g.n_shared_tiles == o.n_shared_tiles && g.inv_temp == o.inv_temp && g.seed == o.seed)
+        return;
+    if (e->graph_exec) {
+        cudaGraphExecDestroy(e->graph_exec);
+        e->graph_exec = nullptr;
+    }
+    const long long before = e->launches;
+    cudaGraph_t graph = nullptr;
+    RT_CUDA(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
+    try {
+        engine_forward(e, o);
+    } catch (...) {
+        cudaStreamEndCapture(e->st, &graph);
+        if (graph) cudaGraphDestroy(graph);
+        throw;
+    }
+    RT_CUDA(cudaStreamEndCapture(e->st, &graph));
+    e->graph_nodes = (int)(e->launches - before);
+    e->launches = before;
+    RT_CUDA(cudaGraphInstantiate(&e->graph_exec, graph, 0));
+    cudaGraphDestroy(graph);
+    e->graph_opts = o;
+}
+
+// ===================================================================================================
+// Batch generation: n token-id prompts -> n greedy (or Gumbel-sampled) continuations.
+// ===================================================================================================
+void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int32_t* lens, int n, const rt_sampling* sp,
+                         uint64_t deadline_ms, rt_result* outs) {
+    RT_REQUIRE(n >= 1 && n <= e->n_seq, "batch size must be 1..max_batch");
+    rt_sampling s{};
+    if (sp) s = *sp;
+    if (s.max_new_tokens <= 0) s.max_new_tokens = 512;
+    RT_REQUIRE(s.top_k == 0 && (s.top_p == 0.f || s.top_p == 1.f), "top_k / top_p sampling is not available");
+    RT_REQUIRE(s.temperature >= 0.f, "temperature must be >= 0");
+    for (int i = 0; i < n; ++i) {
+        RT_REQUIRE(lens[i] >= 1, "empty prompt");
+        for (int j = 0; j < lens[i]; ++j) RT_REQUIRE(prompts[i][j] >= 0 && prompts[i][j] < e->vocab, "token id out of range");
+    }
+    RT_CUDA(cudaSetDevice(e->dev));
+    const double t0 = now_ms();
+    const long long launches0 = e->launches;
+    engine_reset_sequences(e);
+
+    int max_len = 0, min_len = 1 << 30;
+    for (int i = 0; i < n; ++i) {
+        if (lens[i] + s.max_new_tokens > e->cfg.max_ctx)
+            throw RtError(RT_ERR_OOM, "context length exceeded: prompt of " + std::to_string(lens[i]) + " tokens + " +
+                                          std::to_string(s.max_new_tokens) + " new tokens does not fit max_ctx " +
+                                          std::to_string(e->cfg.max_ctx));
+        max_len = std::max(max_len, lens[i] + s.max_new_tokens);
+        min_len = std::min(min_len, lens[i]);
+    }
+    // longest common token prefix, page aligned, leaving >= 1 own token per sequence
+    int shared = 0;
+    if (n > 1 && !(e->cfg.flags & RT_FLAG_NO_PREFIX_SHARE)) {
+        int lc = 0;
+        for (; lc < min_len - 1; ++lc) {
+            bool same = true;
+            for (int i = 1; i < n && same; ++i) same = prompts[i][lc] == prompts[0][lc];
+            if (!same) break;
+        }
+        shared = (lc / KV_PAGE) * KV_PAGE;
+    }
+    // pages
+    engine_alloc_pages(e, 0, lens[0] + s.max_new_tokens);
+    for (int i = 1; i < n; ++i) {
+        engine_share_prefix(e, 0, i, shared / KV_PAGE);
+        engine_alloc_pages(e, i, lens[i] + s.max_new_tokens);
+    }
+    engine_upload_page_table(e);
+
+    StepOpts base{};
+    plan_chunks(max_len, 0, base);   // prefill slabs: no cascade phase
+    base.inv_temp = s.temperature > 0.f ? 1.0f / s.temperature : 0.f;
+    base.seed = s.seed;
+
+    // ---- prefill ----
+    RT_CUDA(cudaEventRecord(e->ev[0], e->st));
+    {
+        std::vector<int> tok, seq, pos, want;
+        for (int p = 0; p < shared; ++p) { tok.push_back(prompts[0][p]); seq.push_back(0); pos.push_back(p); want.push_back(-1); }
+        for (int i = 0; i < n; ++i)
+            for (int p = shared; p < lens[i]; ++p) {
+                tok.push_back(prompts[i][p]); seq.push_back(i); pos.push_back(p);
+                want.push_back(p == lens[i] - 1 ? i : -1);
+            }
+        prefill_via_slabs(e, tok, seq, pos, want, base, t0, deadline_ms);
+    }
+    RT_CUDA(cudaEventRecord(e->ev[1], e->st));
+
+    // ---- decode state: slot b = sequence b, token = its first generated token ----
+    std::vector<int> first(n);
+    RT_CUDA(cudaStreamSynchronize(e->st));
+    for (int i = 0; i < n; ++i)
+        RT_CUDA(cudaMemcpy(&first[i], e->d_out_tokens + (size_t)i * e->max_out, sizeof(int), cudaMemcpyDeviceToHost));
+    {
+        std::vector<int> seq(n), pos(n);
+        for (int i = 0; i < n; ++i) { seq[i] = i; pos[i] = lens[i]; }
+        engine_set_slots(e, first.data(), seq.data(), pos.data(), n);
+        const int one = 1;
+        e->h_stage[3 * MAX_SLOTS] = one;
+        e->h_stage[3 * MAX_SLOTS + 1] = shared;
+        RT_CUDA(cudaMemcpyAsync(e->d_step, e->h_stage + 3 * MAX_SLOTS, sizeof(int), cudaMemcpyHostToDevice, e->st));
+        RT_CUDA(cudaMemcpyAsync(e->d_shared_len, e->h_stage + 3 * MAX_SLOTS + 1, sizeof(int), cudaMemcpyHostToDevice, e->st));
+    }
+    StepOpts dec = base;
+    dec.T = n;
+    dec.sample = true;
+    dec.advance = true;
+    dec.n_shared_tiles = shared > 0 ? cdiv(n * e->G, 16) : 0;
+    plan_chunks(max_len, shared, dec);
+
+    const int n_steps = s.max_new_tokens - 1;
+    const bool use_graph = !(e->cfg.flags & RT_FLAG_NO_GRAPH);
+    if (use_graph && n_steps > 0) ensure_graph(e, dec);
+    std::vector<int> host_out((size_t)n * s.max_new_tokens);
+    std::vector<int> n_out(n, s.max_new_tokens);
+    std::vector<int> finish(n, 0);
+    int steps_done = 0;
+
+    RT_CUDA(cudaEventRecord(e->ev[2], e->st));
+    while (steps_done < n_steps) {
+        const int burst = std::min(16, n_steps - steps_done);
+        for (int k = 0; k < burst; ++k) {
+            if (use_graph) {
+                RT_CUDA(cudaGraphLaunch(e->graph_exec, e->st));
+                e->launches += e->graph_nodes;
+            } else {
+                engine_forward(e, dec);
+            }
+        }
+        steps_done += burst;
+        if (deadline_ms || !s.ignore_eos) {
+            RT_CUDA(cudaStreamSynchronize(e->st));
+            check_deadline(t0, deadline_ms);
+            if (!s.ignore_eos) {
+                bool all_done = true;
+                for (int i = 0; i < n; ++i) {
+                    RT_CUDA(cudaMemcpy(host_out.data() + (size_t)i * s.max_new_tokens, e->d_out_tokens + (size_t)i * e->max_out,
+                                       (size_t)(steps_done + 1) * sizeof(int), cudaMemcpyDeviceToHost));
+                    bool found = false;
+                    for (int k = 0; k <= steps_done && !found; ++k) found = host_out[(size_t)i * s.max_new_tokens + k] == 2;
+                    all_done = all_done && found;
+                }
+                if (all_done) break;
+            }
+        }
+    }
+    RT_CUDA(cudaEventRecord(e->ev[3], e->st));
+    RT_CUDA(cudaStreamSynchronize(e->st));
+    float pre_ms = 0.f, dec_ms = 0.f;
+    RT_CUDA(cudaEventElapsedTime(&pre_ms, e->ev[0], e->ev[1]));
+    RT_CUDA(cudaEventElapsedTime(&dec_ms, e->ev[2], e->ev[3]));
+
+    const int produced = steps_done + 1;
+    for (int i = 0; i < n; ++i) {
+        RT_CUDA(cudaMemcpy(host_out.data() + (size_t)i * s.max_new_tokens, e->d_out_tokens + (size_t)i * e->max_out,
+                           (size_t)produced * sizeof(int), cudaMemcpyDeviceToHost));
+        n_out[i] = produced;
+        if (!s.ignore_eos)
+            for (int k = 0; k < produced; ++k)
+                if (host_out[(size_t)i * s.max_new_tokens + k] == 2) { n_out[i] = k; finish[i] = 1; break; }
+    }
+    for (int i = 0; i < n; ++i) {
+        rt_result& r = outs[i];
+        memset(&r, 0, sizeof(r));
+        r.n_tokens = n_out[i];
+        r.tokens = (int32_t*)malloc(sizeof(int32_t) * std::max(1, n_out[i]));
+        memcpy(r.tokens, host_out.data() + (size_t)i * s.max_new_tokens, sizeof(int32_t) * n_out[i]);
+        std::string text = rt_tok_decode(r.tokens, r.n_tokens);
+        if (text.empty()) text = "<eos>";   // the adapter treats empty content as an error (local-llm.ts:189-191)
+        r.text = (char*)malloc(text.size() + 1);
+        memcpy(r.text, text.c_str(), text.size() + 1);
+        r.text_len = text.size();
+        r.n_prompt_tokens = lens[i];
+        r.prefix_shared_tokens = i == 0 ? 0 : shared;
+        r.finish_reason = finish[i];
+        r.prefill_ms = pre_ms;
+        r.decode_ms = dec_ms;
+        r.decode_steps = steps_done;
+        r.gpu_launches = (int32_t)(e->launches - launches0);
+    }
+}
+
+// ===================================================================================================
+// Teacher forcing on the scratch sequence (seq 0): append ids, return logits of every appended position.
+// ===================================================================================================
+void engine_step_logits(rt_engine* e, const int32_t* ids, int n, int mode, float* logits_out) {
+    RT_REQUIRE(n >= 1, "n must be >= 1");
+    RT_REQUIRE(mode == 0, "only mode 0 (decode kernels) is available in this build");
+    RT_CUDA(cudaSetDevice(e->dev));
+    if (!e->scratch_active) {
+        engine_reset_sequences(e);
+        e->scratch_active = true;
+    }
+    const int p0 = e->seq_len[0];
+    if (p0 + n > e->cfg.max_ctx) throw RtError(RT_ERR_OOM, "context length exceeded in rt_step_logits");
+    for (int j = 0; j < n; ++j) RT_REQUIRE(ids[j] >= 0 && ids[j] < e->vocab, "token id out of range");
+    engine_alloc_pages(e, 0, p0 + n);
+    engine_upload_page_table(e);
+    const int zero = 0;
+    RT_CUDA(cudaMemcpyAsync(e->d_shared_len, &zero, sizeof(int), cudaMemcpyHostToDevice, e->st));
+    StepOpts o{};
+    plan_chunks(p0 + n, 0, o);
+    o.store_logits = true;
+    for (int s0 = 0; s0 < n; s0 += MAX_SLOTS) {
+        const int T = std::min(MAX_SLOTS, n - s0);
+        int tok[MAX_SLOTS], seq[MAX_SLOTS], pos[MAX_SLOTS];
+        for (int i = 0; i < T; ++i) { tok[i] = ids[s0 + i]; seq[i] = 0; pos[i] = p0 + s0 + i; }
+        engine_set_slots(e, tok, seq, pos, T);
+        o.T = T;
+        engine_forward(e, o);
+        RT_CUDA(cudaMemcpyAsync(logits_out + (size_t)s0 * e->vocab_l, e->logits, (size_t)T * e->vocab_l * sizeof(float),
+                                cudaMemcpyDeviceToHost, e->st));
+        RT_CUDA(cudaStreamSynchronize(e->st));
+    }
+    e->seq_len[0] = p0 + n;
+}
+
+// ===================================================================================================
+void engine_export_weight(rt_engine* e, int tid, uint16_t* out, long long n_elems) {
+    RT_REQUIRE(e->cfg.tp_size == 1, "weight export needs tp_size == 1");
+    RT_CUDA(cudaSetDevice(e->dev));
+    const int H = e->H, hd = e->hd;
+    auto copy_rows = [&](const bf16* src, long long rows, long long cols) {
+        RT_REQUIRE(n_elems == rows * cols, "n_elems does not match tensor shape");
+        RT_CUDA(cudaMemcpy(out, src, (size_t)rows * cols * 2, cudaMemcpyDeviceToHost));
+    };
+    if (tid == 0) return copy_rows(e->embed, e->vocab, H);
+    if (tid == 1) return copy_rows(e->lm_head, e->vocab, H);
+    if (tid == 2) return copy_rows(e->final_norm, 1, H);
+    const int l = tid / 16 - 1, k = tid % 16;
+    RT_REQUIRE(l >= 0 && l < e->L && k <= 11, "bad tensor id");
+    const LayerW& w = e->layers[l];
+    const int qr = e->nq * hd, kr = e->nkv * hd;
+    switch (k) {
+        case 0: return copy_rows(w.wqkv, qr, H);
+        case 1: return copy_rows(w.wqkv + (size_t)qr * H, kr, H);
+        case 2: return copy_rows(w.wqkv + (size_t)(qr + kr) * H, kr, H);
+        case 3: return copy_rows(w.wo, H, qr);
+        case 6: return copy_rows(w.wdown, H, e->F);
+        case 7: return copy_rows(w.norm1, 1, H);
+        case 8: return copy_rows(w.norm2, 1, H);
+        case 4:
+        case 5: {
+            RT_REQUIRE(n_elems == (long long)e->F * H, "n_elems does not match tensor shape");
+            std::vector<uint16_t> tmp((size_t)2 * e->F * H);
+            RT_CUDA(cudaMemcpy(tmp.data(), w.wgu, tmp.size() * 2, cudaMemcpyDeviceToHost));
+            for (int f = 0; f < e->F; ++f) {
+                const size_t prow = (size_t)(f / 8) * 16 + (k == 5 ? 8 : 0) + (f % 8);
+                memcpy(out + (size_t)f * H, tmp.data() + prow * H, (size_t)H * 2);
+            }
+            return;
+        }
+        default: {
+            RT_REQUIRE(w.bqkv != nullptr, "model has no qkv bias");
+            const int off = k == 9 ? 0 : (k == 10 ? qr : qr + kr), cnt = k == 9 ? qr : kr;
+            RT_REQUIRE(n_elems == cnt, "n_elems does not match tensor shape");
+            std::vector<float> tmp(cnt);
+            RT_CUDA(cudaMemcpy(tmp.data(), w.bqkv + off, (size_t)cnt * 4, cudaMemcpyDeviceToHost));
+            for (int i = 0; i < cnt; ++i) {
+                uint32_t u;
+                memcpy(&u, &tmp[i], 4);
+                out[i] = (uint16_t)(u >> 16);
+            }
+            return;
+        }
+    }
+}

@@ -1,0 +1,102 @@
+// Engine state of the generation backend: weights, paged KV pool, per-step device state, workspaces.
+// Host-side C++; replaces the external server process behind local-llm.ts:159 (see include/rt_engine.h).
+#pragma once
+#include <string>
+#include <vector>
+#include "../../include/rt_engine.h"
+#include "common.cuh"
+
+constexpr int MAX_SLOTS = 32;      // token slots per forward step (decode: knights; slab prefill: tokens)
+constexpr int MAX_CHUNKS = 136;    // attention partials per (slot, head): <= 64 shared + <= 64 own (+ rounding)
+
+struct LayerW {
+    bf16* wqkv = nullptr;   // [(nq_l + 2*nkv_l)*hd][H]  rows: q heads, k heads, v heads
+    float* bqkv = nullptr;  // [(nq_l + 2*nkv_l)*hd] or null
+    bf16* wo = nullptr;     // [H][nq_l*hd]
+    bf16* wgu = nullptr;    // [2*F_l][H]  per 16-row tile: 8 gate rows then the 8 matching up rows
+    bf16* wdown = nullptr;  // [H][F_l]
+    bf16* norm1 = nullptr;  // [H]
+    bf16* norm2 = nullptr;  // [H]
+};
+
+struct StepOpts {
+    int T = 0;                 // valid slots
+    bool sample = false;       // run lm_head + arg-max
+    bool advance = false;      // decode: feed the sampled token back, pos += 1, record it
+    bool store_logits = false; // write logits[T][vocab]
+    int chunk_pages = 4;
+    int n_chunk_blocks = 1;    // grid.x of the attention kernel
+    int n_shared_tiles = 0;    // > 0 => cascade phase on
+    float inv_temp = 0.f;
+    unsigned long long seed = 0;
+};
+
+struct rt_engine {
+    rt_config cfg{};
+    int dev = 0, sm_count = 148;
+    cudaStream_t st = nullptr;
+    std::string err;
+    long long launches = 0;
+
+    // global dims and this rank's shard
+    int L = 0, H = 0, hd = 0, nq = 0, nkv = 0, F = 0, vocab = 0;
+    int nq_l = 0, nkv_l = 0, F_l = 0, vocab_l = 0, G = 1, qkv_rows = 0;
+
+    bf16 *embed = nullptr, *lm_head = nullptr, *final_norm = nullptr;
+    std::vector<LayerW> layers;
+    std::vector<void*> allocs;     // everything to cudaFree
+    float *cos_t = nullptr, *sin_t = nullptr;
+
+    // paged KV: per layer [n_pages][nkv_l][16][hd]
+    bf16 *kpool = nullptr, *vpool = nullptr;
+    size_t layer_pool_elems = 0;
+    int n_pages = 0, max_pages_per_seq = 0, n_seq = 0;
+    std::vector<int> free_pages;
+    std::vector<std::vector<int>> seq_pages;  // pages owned (or shared) by each sequence, in order
+    std::vector<int> page_ref;
+    int* h_page_table = nullptr;  // pinned [n_seq][max_pages_per_seq]
+    int* d_page_table = nullptr;
+    std::vector<int> seq_len;
+
+    // step state (device)
+    int *d_tok = nullptr, *d_seq = nullptr, *d_pos = nullptr, *d_shared_len = nullptr, *d_step = nullptr;
+    int *d_next_tok = nullptr, *d_out_tokens = nullptr;
+    int max_out = 0;
+    int* h_stage = nullptr;       // pinned staging, 4 * MAX_SLOTS + misc ints
+
+    // activations (MAX_SLOTS rows each)
+    float *x = nullptr, *qkv = nullptr, *delta = nullptr, *logits = nullptr;
+    bf16 *xn = nullptr, *qb = nullptr, *attn_bf = nullptr, *act_bf = nullptr;
+    float *part_o = nullptr, *part_ml = nullptr;
+    float* cta_max = nullptr;
+    int* cta_idx = nullptr;
+    int lm_ctas = 0;
+
+    // cached decode graph
+    cudaGraphExec_t graph_exec = nullptr;
+    StepOpts graph_opts{};
+    int graph_nodes = 0;
+
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+    // teacher-forcing scratch sequence (seq 0)
+    bool scratch_active = false;
+};
+
+// engine.cu
+void engine_init(rt_engine* e);
+void engine_free(rt_engine* e);
+void engine_reset_sequences(rt_engine* e);
+void engine_alloc_pages(rt_engine* e, int seq, int n_tokens_total);
+void engine_share_prefix(rt_engine* e, int from_seq, int to_seq, int n_pages);
+void engine_upload_page_table(rt_engine* e);
+void engine_forward(rt_engine* e, const StepOpts& o);
+void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* pos, int T);
+void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int32_t* lens, int n,
+                         const rt_sampling* s, uint64_t deadline_ms, rt_result* outs);
+void engine_step_logits(rt_engine* e, const int32_t* ids, int n, int mode, float* logits_out);
+void engine_export_weight(rt_engine* e, int tensor_id, uint16_t* out, long long n_elems);
+
+// tokenizer.cpp
+int rt_tok_encode_chat(const char* s, size_t len, std::vector<int>& ids);
+std::string rt_tok_decode(const int* ids, int n);

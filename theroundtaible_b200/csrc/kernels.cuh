@@ -1,0 +1,636 @@
+// Decode-phase kernels of the generation backend (sm_100a).
+//
+// None of these exist in the reference: /root/reference/src/adapters/local-llm.ts:159 hands the
+// prompt to an external server.  They are the "beyond the boundary" list of SURVEY.md 8(a-K):
+// embed gather, RMSNorm, decode projections (GEMV), RoPE + KV append, paged GQA attention with a
+// shared-prefix (cascade) phase, SwiGLU, lm_head + sampling.  All are HBM-bound streams: weights and
+// KV pages are read once with 16-byte coalesced loads, reductions are warp shuffles / fixed-order
+// shared-memory sums (deterministic: no atomics anywhere on the data path).
+#pragma once
+#include "common.cuh"
+
+// =================================================================================================
+// Embedding gather:  x[t][:] = float(E[tok[t]][:])
+// =================================================================================================
+static __global__ void embed_kernel(const bf16* __restrict__ E, const int* __restrict__ tok, float* __restrict__ x,
+                             int H, int vocab) {
+    const int t = blockIdx.y;
+    int id = tok[t];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (c >= H) return;
+    const uint4 v = *reinterpret_cast<const uint4*>(E + (size_t)id * H + c);
+    float4 a = make_float4(bf16lo(v.x), bf16hi(v.x), bf16lo(v.y), bf16hi(v.y));
+    float4 b = make_float4(bf16lo(v.z), bf16hi(v.z), bf16lo(v.w), bf16hi(v.w));
+    float4* o = reinterpret_cast<float4*>(x + (size_t)t * H + c);
+    o[0] = a;
+    o[1] = b;
+}
+
+// =================================================================================================
+// RMSNorm:  y[t] = bf16( x[t] * rsqrt(mean(x[t]^2) + eps) * w )      (optionally x[t] += delta[t] first)
+// one CTA per token slot; the fp32 residual stream stays in x.
+// =================================================================================================
+static __global__ void __launch_bounds__(256) rmsnorm_kernel(float* __restrict__ x, const float* __restrict__ delta,
+                                                      const bf16* __restrict__ w, bf16* __restrict__ y, int H,
+                                                      int ldy, float eps) {
+    const int t = blockIdx.x;
+    float* xr = x + (size_t)t * H;
+    const float* dr = delta ? delta + (size_t)t * H : nullptr;
+    float ss = 0.f;
+    for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
+        float4 v = *reinterpret_cast<const float4*>(xr + c);
+        if (dr) {
+            const float4 d = *reinterpret_cast<const float4*>(dr + c);
+            v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+            *reinterpret_cast<float4*>(xr + c) = v;
+        }
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    __shared__ float red[8];
+    __shared__ float s_r;
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float tot = 0.f;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) tot += red[i];
+        s_r = 1.0f / sqrtf(tot / (float)H + eps);
+    }
+    __syncthreads();
+    const float r = s_r;
+    for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
+        const float4 v = *reinterpret_cast<const float4*>(xr + c);
+        const uint2 wv = *reinterpret_cast<const uint2*>(w + c);
+        uint2 o;
+        o.x = pack_bf16(v.x * r * bf16lo(wv.x), v.y * r * bf16hi(wv.x));
+        o.y = pack_bf16(v.z * r * bf16lo(wv.y), v.w * r * bf16hi(wv.y));
+        *reinterpret_cast<uint2*>(y + (size_t)t * ldy + c) = o;
+    }
+}
+
+// =================================================================================================
+// Decode projection ("GEMV" with up to 32 token slots):   acc[t][n] = sum_k W[n][k] * X[t][k]
+//
+// W bf16 [N][K] row-major is the HBM stream (read exactly once).  A CTA owns 16*MT rows over the
+// FULL K; its 8 warps interleave over 32-wide k-blocks, so a row is read as 8 x 64 B contiguous
+// pieces per round.  Each lane issues 16-byte loads only.  The multiply runs on the legacy tensor
+// path (mma.sync m16n8k16, rows = M, token slots = N) so that the FMA pipe never becomes the bound
+// at 5..8 knights.  Because a dot product does not care about the order of k, the
+// 16 k's of one MMA are a PERMUTATION of memory order chosen so that every lane's A fragment is one
+// contiguous 16-byte piece:  lane (g=lane/4, q=lane%4) holds W[row g][kb*32 + 8q .. 8q+7]; MMA #0
+// consumes elements {0,1,2,3} of that piece, MMA #1 elements {4,5,6,7}; X uses the same map.
+// The 8 per-warp partial sums are added in fixed warp order through shared memory.
+// =================================================================================================
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3 };
+
+struct GemvArgs {
+    const bf16* W;
+    const bf16* X;       // [NT*8][ldx] bf16; rows >= T must be readable (zero padded)
+    int N, K, ldx, T;
+    float* out;          // STORE: out[t*ldo+n] = acc (+bias[n]);  RESID: out[t*ldo+n] += acc
+    int ldo;
+    const float* bias;   // nullable (STORE only)
+    bf16* out_bf;        // SWIGLU: out_bf[t*ldob + n/2-ish] = bf16(silu(gate)*up)
+    int ldob;
+    // LOGITS
+    float* logits;       // nullable: logits[t*ld_logits + n]
+    int ld_logits;
+    float* cta_max;      // [gridDim.x][32]
+    int* cta_idx;        // [gridDim.x][32]
+    int row_offset;      // vocab-parallel: global id of row 0
+    float inv_temp;      // 0 => greedy
+    unsigned long long seed;
+    const int* step_ptr;
+};
+
+__device__ __forceinline__ float gumbel_noise(unsigned long long seed, int step, int slot, int idx) {
+    unsigned long long z = seed + 0x9E3779B97F4A7C15ull * ((unsigned long long)(unsigned)step * 64ull + (unsigned)slot) +
+                           ((unsigned long long)(unsigned)idx << 20);
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const float u = ((float)(z >> 40) + 0.5f) * (1.0f / 16777216.0f);  // (0,1)
+    return -logf(-logf(u));
+}
+
+template <int NT, int MT, int EPI>
+__global__ void __launch_bounds__(256) gemv_tc_kernel(const GemvArgs a) {
+    static_assert(NT * MT <= 4, "shared-memory reduction sized for NT*MT <= 4");
+    constexpr int U = (MT * NT >= 4) ? 2 : (MT * NT == 2 ? 4 : 8);
+    __shared__ float4 red[8][MT * NT][32];
+    __shared__ float res[MT * NT][16][8];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+    const int row0 = blockIdx.x * (16 * MT);
+    const int nkb = a.K >> 5;
+
+    const bf16* wp[MT][2];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+        int r0 = row0 + mt * 16 + g, r1 = r0 + 8;
+        r0 = r0 < a.N ? r0 : a.N - 1;
+        r1 = r1 < a.N ? r1 : a.N - 1;
+        wp[mt][0] = a.W + (size_t)r0 * a.K + q * 8;
+        wp[mt][1] = a.W + (size_t)r1 * a.K + q * 8;
+    }
+    const bf16* xp[NT];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) xp[nt] = a.X + (size_t)(nt * 8 + g) * a.ldx + q * 8;
+
+    float acc[MT][NT][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[mt][nt][i] = 0.f;
+
+    int kb = warp;
+    for (; kb + 8 * (U - 1) < nkb; kb += 8 * U) {
+        uint4 av[U][MT][2];
+        uint4 xv[U][NT];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int ko = (kb + 8 * u) << 5;
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+                av[u][mt][0] = ld_stream16(wp[mt][0] + ko);
+                av[u][mt][1] = ld_stream16(wp[mt][1] + ko);
+            }
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) xv[u][nt] = *reinterpret_cast<const uint4*>(xp[nt] + ko);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
+                                   xv[u][nt].x, xv[u][nt].y);
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
+                                   xv[u][nt].z, xv[u][nt].w);
+                }
+    }
+    for (; kb < nkb; kb += 8) {
+        const int ko = kb << 5;
+        uint4 av[MT][2];
+        uint4 xv[NT];
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+            av[mt][0] = ld_stream16(wp[mt][0] + ko);
+            av[mt][1] = ld_stream16(wp[mt][1] + ko);
+        }
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) xv[nt] = *reinterpret_cast<const uint4*>(xp[nt] + ko);
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                mma_bf16_16816(acc[mt][nt], av[mt][0].x, av[mt][1].x, av[mt][0].y, av[mt][1].y, xv[nt].x, xv[nt].y);
+                mma_bf16_16816(acc[mt][nt], av[mt][0].z, av[mt][1].z, av[mt][0].w, av[mt][1].w, xv[nt].z, xv[nt].w);
+            }
+    }
+
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+            red[warp][mt * NT + nt][lane] = make_float4(acc[mt][nt][0], acc[mt][nt][1], acc[mt][nt][2], acc[mt][nt][3]);
+    __syncthreads();
+
+    // fixed-order sum over the 8 warps; element (tile, lane', i) -> row = lane'/4 + 8*(i>>1), slot = (lane'%4)*2 + (i&1)
+    for (int e = threadIdx.x; e < MT * NT * 32; e += 256) {
+        const int tile = e >> 5, l2 = e & 31;
+        float4 s = red[0][tile][l2];
+#pragma unroll
+        for (int w = 1; w < 8; ++w) {
+            const float4 v = red[w][tile][l2];
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        const int rr = l2 >> 2, cc = (l2 & 3) * 2;
+        res[tile][rr][cc] = s.x;
+        res[tile][rr][cc + 1] = s.y;
+        res[tile][rr + 8][cc] = s.z;
+        res[tile][rr + 8][cc + 1] = s.w;
+    }
+    __syncthreads();
+
+    if (EPI == EPI_STORE || EPI == EPI_RESID) {
+        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += 256) {
+            const int r = e % (MT * 16), s = e / (MT * 16);
+            const int n = row0 + r;
+            if (s < a.T && n < a.N) {
+                float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                float* o = a.out + (size_t)s * a.ldo + n;
+                if (EPI == EPI_STORE) {
+                    if (a.bias) v += a.bias[n];
+                    *o = v;
+                } else {
+                    *o += v;
+                }
+            }
+        }
+    } else if (EPI == EPI_SWIGLU) {
+        // rows 0..7 of every 16-row tile are gate_{8j+r}, rows 8..15 are up_{8j+r}
+        for (int e = threadIdx.x; e < MT * 8 * NT * 8; e += 256) {
+            const int r = e % (MT * 8), s = e / (MT * 8);
+            const int mt = r >> 3, rr = r & 7;
+            const int n = row0 + mt * 16;  // first physical row of the tile
+            if (s < a.T && n < a.N) {
+                const float gt = res[mt * NT + (s >> 3)][rr][s & 7];
+                const float up = res[mt * NT + (s >> 3)][rr + 8][s & 7];
+                const float act = gt / (1.0f + expf(-gt)) * up;
+                a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = __float2bfloat16_rn(act);
+            }
+        }
+    } else {  // EPI_LOGITS
+        if (a.logits) {
+            for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += 256) {
+                const int r = e % (MT * 16), s = e / (MT * 16);
+                const int n = row0 + r;
+                if (s < a.T && n < a.N) a.logits[(size_t)s * a.ld_logits + n] = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+            }
+        }
+        if (threadIdx.x < NT * 8) {
+            const int s = threadIdx.x;
+            float best = -INFINITY;
+            int bi = 0x7fffffff;
+            if (s < a.T) {
+                const int step = (a.inv_temp > 0.f && a.step_ptr) ? *a.step_ptr : 0;
+                for (int r = 0; r < MT * 16; ++r) {
+                    const int n = row0 + r;
+                    if (n >= a.N) break;
+                    float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                    if (a.inv_temp > 0.f) v = v * a.inv_temp + gumbel_noise(a.seed, step, s, a.row_offset + n);
+                    if (v > best) { best = v; bi = a.row_offset + n; }
+                }
+            }
+            a.cta_max[blockIdx.x * 32 + s] = best;
+            a.cta_idx[blockIdx.x * 32 + s] = bi;
+        }
+    }
+}
+
+// final arg-max over the per-CTA candidates; advances the decode state on the device so that a
+// decode step can be replayed as a CUDA graph without host involvement.
+struct SampleArgs {
+    const float* cta_max;
+    const int* cta_idx;
+    int n_cta, T;
+    int* next_tok;      // [T] written always
+    int* tok;           // nullable: tok[t] = next (decode: feeds the next step)
+    int* pos;           // nullable: pos[t] += 1
+    int* out_tokens;    // nullable: out_tokens[t*max_out + *step] = next
+    int max_out;
+    int* step_ptr;      // nullable: incremented once per launch
+};
+
+static __global__ void __launch_bounds__(256) sample_final_kernel(const SampleArgs a) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int step = a.step_ptr ? *a.step_ptr : 0;
+    for (int t = warp; t < a.T; t += 8) {
+        float best = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int c = lane; c < a.n_cta; c += 32) {
+            const float v = a.cta_max[c * 32 + t];
+            const int i = a.cta_idx[c * 32 + t];
+            if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float v = __shfl_xor_sync(0xffffffffu, best, o);
+            const int i = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+        }
+        if (lane == 0) {
+            if (bi == 0x7fffffff) bi = 0;
+            a.next_tok[t] = bi;
+            if (a.tok) a.tok[t] = bi;
+            if (a.pos) a.pos[t] += 1;
+            if (a.out_tokens && step < a.max_out) a.out_tokens[(size_t)t * a.max_out + step] = bi;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && a.step_ptr) *a.step_ptr = step + 1;
+}
+
+// =================================================================================================
+// RoPE + KV append.  qkv fp32 [T][(n_q+2*n_kv)*hd] (bias already added).  Rotated q -> bf16 Q buffer,
+// rotated k and v -> bf16 into the paged cache at (seq, pos).  rotate_half pairing (i, i+hd/2) as in
+// HF modeling_llama.py apply_rotary_pos_emb.  KV page layout: [page][kv_head][16 tokens][hd].
+// =================================================================================================
+constexpr int KV_PAGE = 16;
+
+struct RopeArgs {
+    const float* qkv;
+    int ld_qkv;
+    const float* cos_t;  // [max_pos][hd/2]
+    const float* sin_t;
+    const int* slot_seq;
+    const int* slot_pos;
+    const int* page_table;
+    int pt_stride;
+    bf16* Q;             // [T][n_q*hd]
+    int ldq;
+    bf16* Kp;
+    bf16* Vp;
+    int n_q, n_kv, hd;
+};
+
+static __global__ void rope_append_kernel(const RopeArgs a) {
+    const int t = blockIdx.y, head = blockIdx.x;
+    const int half = a.hd >> 1;
+    const int d = threadIdx.x;
+    if (d >= half) return;
+    const int pos = a.slot_pos[t];
+    const float* src = a.qkv + (size_t)t * a.ld_qkv + (size_t)head * a.hd;
+    const float x1 = src[d], x2 = src[d + half];
+    if (head < a.n_q + a.n_kv) {
+        const float c = a.cos_t[(size_t)pos * half + d], s = a.sin_t[(size_t)pos * half + d];
+        const float y1 = x1 * c - x2 * s;
+        const float y2 = x2 * c + x1 * s;
+        if (head < a.n_q) {
+            bf16* q = a.Q + (size_t)t * a.ldq + (size_t)head * a.hd;
+            q[d] = __float2bfloat16_rn(y1);
+            q[d + half] = __float2bfloat16_rn(y2);
+        } else {
+            const int kvh = head - a.n_q;
+            const int page = a.page_table[(size_t)a.slot_seq[t] * a.pt_stride + pos / KV_PAGE];
+            bf16* k = a.Kp + (((size_t)page * a.n_kv + kvh) * KV_PAGE + (pos % KV_PAGE)) * a.hd;
+            k[d] = __float2bfloat16_rn(y1);
+            k[d + half] = __float2bfloat16_rn(y2);
+        }
+    } else {
+        const int kvh = head - a.n_q - a.n_kv;
+        const int page = a.page_table[(size_t)a.slot_seq[t] * a.pt_stride + pos / KV_PAGE];
+        bf16* v = a.Vp + (((size_t)page * a.n_kv + kvh) * KV_PAGE + (pos % KV_PAGE)) * a.hd;
+        v[d] = __float2bfloat16_rn(x1);
+        v[d + half] = __float2bfloat16_rn(x2);
+    }
+}
+
+// =================================================================================================
+// Paged GQA decode attention, split over the KV length, with a shared-prefix (cascade) phase.
+//
+// Work item = one WARP: 16 query rows x one chunk of `chunk_pages` KV pages of one kv head.
+//   * per-slot items (blockIdx.z < T): rows = the G q-heads of slot z; keys [shared, pos+1)
+//   * shared items   (blockIdx.z >= T): rows = 16 consecutive (slot, q-head) pairs of ALL slots;
+//     keys [0, shared) -- read from HBM once for every knight instead of once per knight.
+// Each warp streams its pages through a private 4-stage cp.async ring in shared memory (XOR-swizzled
+// 16-byte pieces, conflict-free ldmatrix), computes S = QK^T and O += PV with mma.sync m16n8k16 and an
+// online softmax in the exp2 domain, and writes an un-normalised partial (O, m, l).  attn_merge_kernel
+// combines the partials in fixed order.
+// =================================================================================================
+struct AttnArgs {
+    const bf16* Q;
+    int ldq;
+    const bf16* Kp;
+    const bf16* Vp;
+    const int* page_table;
+    int pt_stride;
+    const int* slot_seq;
+    const int* slot_pos;
+    const int* shared_len_ptr;  // nullable => 0
+    int T, n_q, n_kv;
+    int chunk_pages;            // KV pages per work item
+    int n_shared_tiles;         // 0 => cascade off
+    float* part_o;              // [T][n_q][max_chunks][hd]
+    float* part_ml;             // [T][n_q][max_chunks][2]
+    int max_chunks;
+    float scale_log2;           // log2(e)/sqrt(hd)
+};
+
+constexpr int ATTN_STAGES = 4;
+constexpr int ATTN_WARPS = 4;
+
+template <int HD>
+__device__ __forceinline__ void attn_issue_page(uint32_t sbase, const bf16* __restrict__ Kp, const bf16* __restrict__ Vp,
+                                                size_t page_elem_off, int lane) {
+    constexpr int CPR = HD / 8;               // 16-byte pieces per row
+    constexpr int PIECES = KV_PAGE * CPR;     // per K (or V) page
+#pragma unroll
+    for (int j = 0; j < PIECES / 32; ++j) {
+        const int ci = lane + 32 * j;
+        const int row = ci / CPR, c = ci % CPR;
+        const uint32_t dst = (uint32_t)(row * (HD * 2) + ((c ^ (row & 7)) << 4));
+        cp_async16(sbase + dst, Kp + page_elem_off + row * HD + c * 8);
+        cp_async16(sbase + KV_PAGE * HD * 2 + dst, Vp + page_elem_off + row * HD + c * 8);
+    }
+}
+
+template <int HD>
+__global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const AttnArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int STAGE_BYTES = 2 * KV_PAGE * HD * 2;
+    constexpr int KT = HD / 16;  // k-steps for QK^T; pairs of 8-wide d tiles for PV
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+    const int h = blockIdx.y;
+    const int G = a.n_q / a.n_kv;
+    const int c = blockIdx.x * ATTN_WARPS + warp;
+    const int C = a.chunk_pages * KV_PAGE;
+    const int sh = (a.n_shared_tiles > 0 && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
+    const int nsh_chunks = (sh + C - 1) / C;
+
+    int key0, key1, pidx, seq;
+    int row_slot[2], row_head[2];
+    bool row_ok[2];
+    if ((int)blockIdx.z < a.T) {
+        const int slot = blockIdx.z;
+        seq = a.slot_seq[slot];
+        const int len = a.slot_pos[slot] + 1;
+        key0 = sh + c * C;
+        key1 = min(key0 + C, len);
+        pidx = nsh_chunks + c;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int R = g + 8 * i;
+            row_ok[i] = R < G;
+            row_slot[i] = slot;
+            row_head[i] = h * G + (R < G ? R : 0);
+        }
+    } else {
+        const int tile = blockIdx.z - a.T;
+        seq = a.slot_seq[0];
+        key0 = c * C;
+        key1 = min(key0 + C, sh);
+        pidx = c;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int R = tile * 16 + g + 8 * i;
+            row_ok[i] = R < a.T * G;
+            row_slot[i] = row_ok[i] ? R / G : 0;
+            row_head[i] = h * G + (row_ok[i] ? R % G : 0);
+        }
+    }
+    if (key0 >= key1) return;  // warp-uniform
+
+    // Q fragments (A operand), loaded once
+    uint32_t qa[KT][4];
+    {
+        const bf16* q0 = a.Q + (size_t)row_slot[0] * a.ldq + (size_t)row_head[0] * HD;
+        const bf16* q1 = a.Q + (size_t)row_slot[1] * a.ldq + (size_t)row_head[1] * HD;
+#pragma unroll
+        for (int t = 0; t < KT; ++t) {
+            qa[t][0] = row_ok[0] ? *reinterpret_cast<const uint32_t*>(q0 + 16 * t + 2 * q) : 0u;
+            qa[t][1] = row_ok[1] ? *reinterpret_cast<const uint32_t*>(q1 + 16 * t + 2 * q) : 0u;
+            qa[t][2] = row_ok[0] ? *reinterpret_cast<const uint32_t*>(q0 + 16 * t + 8 + 2 * q) : 0u;
+            qa[t][3] = row_ok[1] ? *reinterpret_cast<const uint32_t*>(q1 + 16 * t + 8 + 2 * q) : 0u;
+        }
+    }
+
+    const uint32_t sbase = smem_u32(smem_raw) + warp * (ATTN_STAGES * STAGE_BYTES);
+    const int* pt = a.page_table + (size_t)seq * a.pt_stride;
+    const int page0 = key0 / KV_PAGE;
+    const int npages = (key1 - key0 + KV_PAGE - 1) / KV_PAGE;
+    const size_t page_stride = (size_t)a.n_kv * KV_PAGE * HD;
+    const size_t head_off = (size_t)h * KV_PAGE * HD;
+
+#pragma unroll
+    for (int s = 0; s < ATTN_STAGES - 1; ++s) {
+        if (s < npages) attn_issue_page<HD>(sbase + s * STAGE_BYTES, a.Kp, a.Vp, (size_t)pt[page0 + s] * page_stride + head_off, lane);
+        cp_async_commit();
+    }
+
+    float o[HD / 8][4];
+#pragma unroll
+    for (int d = 0; d < HD / 8; ++d)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[d][i] = 0.f;
+    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+
+    for (int p = 0; p < npages; ++p) {
+        {
+            const int pn = p + ATTN_STAGES - 1;
+            if (pn < npages)
+                attn_issue_page<HD>(sbase + (pn % ATTN_STAGES) * STAGE_BYTES, a.Kp, a.Vp,
+                                    (size_t)pt[page0 + pn] * page_stride + head_off, lane);
+            cp_async_commit();
+        }
+        cp_async_wait<ATTN_STAGES - 1>();
+        __syncwarp();
+        const uint32_t sK = sbase + (p % ATTN_STAGES) * STAGE_BYTES;
+        const uint32_t sV = sK + KV_PAGE * HD * 2;
+
+        float s[2][4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) s[j][i] = 0.f;
+        {
+            const int m = lane >> 3, i8 = lane & 7;
+            const int key = (m >> 1) * 8 + i8;
+#pragma unroll
+            for (int t = 0; t < KT; ++t) {
+                const int chunk = 2 * t + (m & 1);
+                uint32_t r0, r1, r2, r3;
+                ldmatrix_x4(r0, r1, r2, r3, sK + key * (HD * 2) + ((chunk ^ (key & 7)) << 4));
+                mma_bf16_16816(s[0], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r0, r1);
+                mma_bf16_16816(s[1], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r2, r3);
+            }
+        }
+        // scale, mask, online softmax (rows g -> idx 0,1 ; rows g+8 -> idx 2,3)
+        const int kbase = key0 + p * KV_PAGE;
+        float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int key = kbase + j * 8 + 2 * q + (i & 1);
+                const float v = key < key1 ? s[j][i] * a.scale_log2 : -INFINITY;
+                s[j][i] = v;
+                mx[i >> 1] = fmaxf(mx[i >> 1], v);
+            }
+        float alpha[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+            mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+            const float mn = fmaxf(m_run[r], mx[r]);
+            alpha[r] = exp2f(m_run[r] - mn);   // m_run = -inf -> 0 ; every page holds >= 1 valid key so mn is finite
+            m_run[r] = mn;
+            l_run[r] *= alpha[r];
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float pv = exp2f(s[j][i] - m_run[i >> 1]);
+                s[j][i] = pv;
+                l_run[i >> 1] += pv;
+            }
+#pragma unroll
+        for (int d = 0; d < HD / 8; ++d) {
+            o[d][0] *= alpha[0]; o[d][1] *= alpha[0];
+            o[d][2] *= alpha[1]; o[d][3] *= alpha[1];
+        }
+        const uint32_t pa0 = pack_bf16(s[0][0], s[0][1]), pa1 = pack_bf16(s[0][2], s[0][3]);
+        const uint32_t pa2 = pack_bf16(s[1][0], s[1][1]), pa3 = pack_bf16(s[1][2], s[1][3]);
+        {
+            const int m = lane >> 3, i8 = lane & 7;
+            const int key = (m & 1) * 8 + i8;
+#pragma unroll
+            for (int dp = 0; dp < KT; ++dp) {
+                const int chunk = 2 * dp + (m >> 1);
+                uint32_t r0, r1, r2, r3;
+                ldmatrix_x4_trans(r0, r1, r2, r3, sV + key * (HD * 2) + ((chunk ^ (key & 7)) << 4));
+                mma_bf16_16816(o[2 * dp], pa0, pa1, pa2, pa3, r0, r1);
+                mma_bf16_16816(o[2 * dp + 1], pa0, pa1, pa2, pa3, r2, r3);
+            }
+        }
+        __syncwarp();
+    }
+
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+        l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        if (!row_ok[r]) continue;
+        const size_t base = ((size_t)row_slot[r] * a.n_q + row_head[r]) * a.max_chunks + pidx;
+        float* po = a.part_o + base * HD;
+#pragma unroll
+        for (int d = 0; d < HD / 8; ++d)
+            *reinterpret_cast<float2*>(po + d * 8 + 2 * q) = make_float2(o[d][2 * r], o[d][2 * r + 1]);
+        if (q == 0) *reinterpret_cast<float2*>(a.part_ml + base * 2) = make_float2(m_run[r], l_run[r]);
+    }
+}
+
+struct MergeArgs {
+    const float* part_o;
+    const float* part_ml;
+    int max_chunks;
+    const int* slot_pos;
+    const int* shared_len_ptr;
+    int cascade;       // n_shared_tiles > 0
+    int chunk_keys;    // C
+    int n_q, hd;
+    bf16* out_bf;      // nullable  [T][ldo]
+    float* out_f32;    // nullable  [T][ldo]
+    int ldo;
+};
+
+static __global__ void attn_merge_kernel(const MergeArgs a) {
+    const int t = blockIdx.y, head = blockIdx.x, d = threadIdx.x;
+    const int len = a.slot_pos[t] + 1;
+    const int sh = (a.cascade && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
+    const int C = a.chunk_keys;
+    const int n = (sh + C - 1) / C + (len - sh + C - 1) / C;
+    const size_t base = ((size_t)t * a.n_q + head) * a.max_chunks;
+    float M = -INFINITY;
+    for (int i = 0; i < n; ++i) M = fmaxf(M, a.part_ml[(base + i) * 2]);
+    float L = 0.f, acc = 0.f;
+    for (int i = 0; i < n; ++i) {
+        const float w = exp2f(a.part_ml[(base + i) * 2] - M);
+        L += a.part_ml[(base + i) * 2 + 1] * w;
+        acc += a.part_o[(base + i) * a.hd + d] * w;
+    }
+    const float r = acc / L;
+    if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * a.hd + d] = __float2bfloat16_rn(r);
+    if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * a.hd + d] = r;
+}
