@@ -8,6 +8,8 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
+#include <cuda_profiler_api.h>
 
 #include "kernels.cuh"
 #include "weights.cuh"
@@ -584,6 +586,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
         engine_alloc_pages(e, i, lens[i] + s.max_new_tokens);
     }
     engine_upload_page_table(e);
+    RT_CUDA(cudaMemsetAsync(e->d_step, 0, sizeof(int), e->st));   // sampling noise is keyed on the step counter
 
     StepOpts base{};
     plan_chunks(max_len, 0, base);   // prefill slabs: no cascade phase
@@ -634,6 +637,8 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     std::vector<int> finish(n, 0);
     int steps_done = 0;
 
+    const bool prof = getenv("RT_PROFILE_DECODE") != nullptr;   // ncu --profile-from-start off: decode steps only
+    if (prof) cudaProfilerStart();
     RT_CUDA(cudaEventRecord(e->ev[2], e->st));
     while (steps_done < n_steps) {
         const int burst = std::min(16, n_steps - steps_done);
@@ -664,6 +669,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     }
     RT_CUDA(cudaEventRecord(e->ev[3], e->st));
     RT_CUDA(cudaStreamSynchronize(e->st));
+    if (prof) cudaProfilerStop();
     float pre_ms = 0.f, dec_ms = 0.f;
     RT_CUDA(cudaEventElapsedTime(&pre_ms, e->ev[0], e->ev[1]));
     RT_CUDA(cudaEventElapsedTime(&dec_ms, e->ev[2], e->ev[3]));

@@ -406,6 +406,11 @@ struct AttnArgs {
 constexpr int ATTN_STAGES = 4;
 constexpr int ATTN_WARPS = 4;
 
+// XOR swizzle of the 16-byte piece index inside a shared-memory row of HD bf16, chosen so that the 8 rows an
+// ldmatrix touches land in 8 different bank groups: rows are 64 B (HD=32), 128 B (HD=64) or 256 B (HD=128).
+template <int HD>
+__device__ __forceinline__ int attn_swz(int row) { return HD >= 64 ? (row & 7) : ((row >> 1) & 3); }
+
 template <int HD>
 __device__ __forceinline__ void attn_issue_page(uint32_t sbase, const bf16* __restrict__ Kp, const bf16* __restrict__ Vp,
                                                 size_t page_elem_off, int lane) {
@@ -415,7 +420,7 @@ __device__ __forceinline__ void attn_issue_page(uint32_t sbase, const bf16* __re
     for (int j = 0; j < PIECES / 32; ++j) {
         const int ci = lane + 32 * j;
         const int row = ci / CPR, c = ci % CPR;
-        const uint32_t dst = (uint32_t)(row * (HD * 2) + ((c ^ (row & 7)) << 4));
+        const uint32_t dst = (uint32_t)(row * (HD * 2) + ((c ^ attn_swz<HD>(row)) << 4));
         cp_async16(sbase + dst, Kp + page_elem_off + row * HD + c * 8);
         cp_async16(sbase + KV_PAGE * HD * 2 + dst, Vp + page_elem_off + row * HD + c * 8);
     }
@@ -527,7 +532,7 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const Attn
             for (int t = 0; t < KT; ++t) {
                 const int chunk = 2 * t + (m & 1);
                 uint32_t r0, r1, r2, r3;
-                ldmatrix_x4(r0, r1, r2, r3, sK + key * (HD * 2) + ((chunk ^ (key & 7)) << 4));
+                ldmatrix_x4(r0, r1, r2, r3, sK + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
                 mma_bf16_16816(s[0], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r0, r1);
                 mma_bf16_16816(s[1], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r2, r3);
             }
@@ -567,8 +572,14 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const Attn
             o[d][0] *= alpha[0]; o[d][1] *= alpha[0];
             o[d][2] *= alpha[1]; o[d][3] *= alpha[1];
         }
+        // P as bf16 hi + bf16 lo (two MMAs): the decode kernel is HBM-bound, so the second MMA is free and
+        // the softmax weights keep ~16 bits instead of 8
         const uint32_t pa0 = pack_bf16(s[0][0], s[0][1]), pa1 = pack_bf16(s[0][2], s[0][3]);
         const uint32_t pa2 = pack_bf16(s[1][0], s[1][1]), pa3 = pack_bf16(s[1][2], s[1][3]);
+        const uint32_t pl0 = pack_bf16(s[0][0] - bf16lo(pa0), s[0][1] - bf16hi(pa0));
+        const uint32_t pl1 = pack_bf16(s[0][2] - bf16lo(pa1), s[0][3] - bf16hi(pa1));
+        const uint32_t pl2 = pack_bf16(s[1][0] - bf16lo(pa2), s[1][1] - bf16hi(pa2));
+        const uint32_t pl3 = pack_bf16(s[1][2] - bf16lo(pa3), s[1][3] - bf16hi(pa3));
         {
             const int m = lane >> 3, i8 = lane & 7;
             const int key = (m & 1) * 8 + i8;
@@ -576,9 +587,11 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const Attn
             for (int dp = 0; dp < KT; ++dp) {
                 const int chunk = 2 * dp + (m >> 1);
                 uint32_t r0, r1, r2, r3;
-                ldmatrix_x4_trans(r0, r1, r2, r3, sV + key * (HD * 2) + ((chunk ^ (key & 7)) << 4));
+                ldmatrix_x4_trans(r0, r1, r2, r3, sV + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
                 mma_bf16_16816(o[2 * dp], pa0, pa1, pa2, pa3, r0, r1);
+                mma_bf16_16816(o[2 * dp], pl0, pl1, pl2, pl3, r0, r1);
                 mma_bf16_16816(o[2 * dp + 1], pa0, pa1, pa2, pa3, r2, r3);
+                mma_bf16_16816(o[2 * dp + 1], pl0, pl1, pl2, pl3, r2, r3);
             }
         }
         __syncwarp();
