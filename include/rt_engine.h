@@ -190,6 +190,34 @@ RT_API int rt_k_attention(const uint16_t* q, const uint16_t* k, const uint16_t* 
  * from HBM (rotating over enough copies to exceed L2); returns mean ms per launch. */
 RT_API int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t device, double* ms_out);
 
+/* Paged GQA decode attention for callers that must not allocate.  It has no counterpart in the
+ * reference.  It exists for two kinds of caller: a process that has already given (almost) all of
+ * HBM to its own pool allocator -- a serving framework embedding this library -- where a cudaMalloc
+ * made inside the library would fail or fragment that pool; and a latency-critical token loop that
+ * cannot afford the device-wide synchronisation cudaMalloc / cudaFree imply.  Everything is passed as
+ * DEVICE pointers the caller owns:
+ *   q_dev          bf16 [T][n_q][hd]           one query token per sequence, RoPE already applied
+ *   kpool_dev/vpool_dev  bf16 [pages][n_kv][16][hd]   the paged KV pool (page = 16 tokens)
+ *   page_table_dev int32 [T][pt_stride]        page ids of sequence t, in order
+ *   query_pos_dev  int32 [T]                   position of query t = number of earlier tokens; it attends keys 0..pos
+ *   out_dev        fp32 [T][n_q][hd]
+ * max_len is an upper bound of query_pos+1 over the batch; chunk (multiple of 16) is the split-KV
+ * granularity.  The launch is asynchronous on `stream` (a cudaStream_t; NULL = default stream), and
+ * `device` must be the calling thread's current device.
+ * The split-KV partial results go to a 4.25 MiB scratch array built into the library (every GPU that
+ * loads the library keeps it until exit).  Limit: T * n_q * ceil(max_len/chunk) * hd <= 1,048,576
+ * floats, else RT_ERR_INVALID with an explanatory rt_last_error(NULL).  No cudaMalloc, cudaFree or
+ * other allocating call is made.  The first call on each device resolves the scratch address
+ * (cudaGetSymbolAddress) and sets kernel attributes: make that first call before starting any stream
+ * capture.  All calls share the one scratch array, and it keeps the previous call's contents: nothing
+ * in it needs to start at zero (each call overwrites every partial it later reads), but two calls
+ * whose kernels overlap on the GPU (different streams, or different host threads) race on it -- keep
+ * calls on one device ordered. */
+RT_API int rt_k_attention_noalloc(const void* q_dev, const void* kpool_dev, const void* vpool_dev,
+                                  const int32_t* page_table_dev, int32_t pt_stride, const int32_t* query_pos_dev,
+                                  float* out_dev, int32_t T, int32_t max_len, int32_t n_q, int32_t n_kv, int32_t hd,
+                                  int32_t chunk, int32_t device, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

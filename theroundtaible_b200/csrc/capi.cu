@@ -53,6 +53,8 @@ const ArchRow kArchs[] = {
 };
 }  // namespace
 
+void rt_internal_set_error(const std::string& msg) { g_err = msg; }
+
 extern "C" {
 
 int rt_arch_by_name(const char* name, rt_config* cfg) {

@@ -54,7 +54,7 @@ class RtModelInfo(C.Structure):
 EXPORTS = ("rt_arch_by_name", "rt_engine_create", "rt_engine_destroy", "rt_last_error", "rt_model_info_get",
            "rt_generate", "rt_generate_batch", "rt_generate_ids", "rt_seq_reset", "rt_step_logits", "rt_result_free",
            "rt_tokenize_chat", "rt_detokenize", "rt_nccl_unique_id", "rt_weights_export", "rt_k_gemv", "rt_k_rmsnorm",
-           "rt_k_attention", "rt_k_gemv_bench")
+           "rt_k_attention", "rt_k_gemv_bench", "rt_k_attention_noalloc")
 
 _lib = None
 
@@ -104,6 +104,7 @@ def load_library():
                                  C.c_float, i32]
     lib.rt_k_attention.argtypes = [C.POINTER(C.c_uint16)] * 3 + [C.POINTER(i32), C.POINTER(C.c_float)] + [i32] * 8
     lib.rt_k_gemv_bench.argtypes = [i32, i32, i32, i32, i32, C.POINTER(C.c_double)]
+    lib.rt_k_attention_noalloc.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     _lib = lib
     return lib
 
@@ -286,3 +287,14 @@ def k_gemv_bench(N: int, K: int, T: int, iters: int = 50, device: int = 0) -> fl
     ms = C.c_double()
     _check(load_library().rt_k_gemv_bench(N, K, T, iters, device, C.byref(ms)))
     return ms.value
+
+
+def k_attention_noalloc(q_ptr: int, kpool_ptr: int, vpool_ptr: int, page_table_ptr: int, pt_stride: int, query_pos_ptr: int,
+                        out_ptr: int, T: int, max_len: int, n_q: int, n_kv: int, hd: int, chunk: int, device: int = 0,
+                        stream: int = 0) -> None:
+    """rt_k_attention_noalloc on raw DEVICE addresses (ints).  For hosts that must not allocate: an embedding
+    framework that owns all of HBM through its own pool, or a token loop that cannot take cudaMalloc's
+    device-wide synchronisation.  Asynchronous on ``stream``; raises EngineError when the built-in 4 MiB
+    split-KV scratch would not suffice."""
+    _check(load_library().rt_k_attention_noalloc(q_ptr, kpool_ptr, vpool_ptr, page_table_ptr, pt_stride, query_pos_ptr,
+                                                 out_ptr, T, max_len, n_q, n_kv, hd, chunk, device, stream or None))
