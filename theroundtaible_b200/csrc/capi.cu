@@ -1,4 +1,5 @@
 // extern "C" boundary of the generation backend (include/rt_engine.h).  No exception crosses it.
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -6,6 +7,7 @@
 
 #include "engine.cuh"
 #include "kernels.cuh"
+#include "weights.cuh"
 
 int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi);
 void rt_attn_host_setup();
@@ -269,7 +271,9 @@ int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t
         bf16* dw = s.alloc<bf16>((size_t)N * K, false);
         bf16* dx = s.alloc<bf16>((size_t)MAX_SLOTS * K);
         float* dy = s.alloc<float>((size_t)MAX_SLOTS * N);
-        RT_CUDA(cudaMemcpyAsync(dw, w, (size_t)N * K * 2, cudaMemcpyHostToDevice, s.e.st));
+        std::vector<uint16_t> cm((size_t)N * K);
+        wgen::rowmajor_to_cm(w, cm.data(), N, K);     // the kernel streams the core-matrix-major layout (gemv.cuh)
+        RT_CUDA(cudaMemcpyAsync(dw, cm.data(), (size_t)N * K * 2, cudaMemcpyHostToDevice, s.e.st));
         RT_CUDA(cudaMemcpyAsync(dx, x, (size_t)T * K * 2, cudaMemcpyHostToDevice, s.e.st));
         GemvArgs a{};
         a.W = dw; a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N;
@@ -365,6 +369,22 @@ int rt_k_attention(const uint16_t* q, const uint16_t* k, const uint16_t* v, cons
         a.part_o = po; a.part_ml = pml; a.max_chunks = MAX_CHUNKS;
         a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd));
         rt_attn_host_launch(&s.e, a, hd, cdiv(std::max(n_sh, n_own), ATTN_WARPS));
+        if (const char* it = getenv("RT_ATTN_BENCH_ITERS")) {   // profiling aid: time the partials kernel alone
+            const int iters = atoi(it);
+            cudaEvent_t e0, e1;
+            RT_CUDA(cudaEventCreate(&e0));
+            RT_CUDA(cudaEventCreate(&e1));
+            RT_CUDA(cudaEventRecord(e0, st));
+            for (int i = 0; i < iters; ++i) rt_attn_host_launch(&s.e, a, hd, cdiv(std::max(n_sh, n_own), ATTN_WARPS));
+            RT_CUDA(cudaEventRecord(e1, st));
+            RT_CUDA(cudaStreamSynchronize(st));
+            float ms = 0.f;
+            RT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            fprintf(stderr, "[attn bench] T=%d n_q=%d n_kv=%d hd=%d max_len=%d shared=%d chunk=%d: %.2f us per launch\n", T, n_q, n_kv, hd,
+                    max_len, shared, chunk, 1e3 * ms / iters);
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+        }
         MergeArgs m{};
         m.part_o = po; m.part_ml = pml; m.max_chunks = MAX_CHUNKS; m.slot_pos = dpos; m.shared_len_ptr = dsh;
         m.cascade = shared > 0; m.chunk_keys = chunk; m.n_q = n_q; m.hd = hd; m.out_f32 = dout; m.ldo = n_q * hd;

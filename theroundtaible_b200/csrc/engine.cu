@@ -35,13 +35,14 @@ double now_ms() {
 }
 
 void gen_plain(rt_engine* e, void* out, int rows, int cols, int tid, long long lrow0, long long lcols, long long lcol0,
-               float std_, float offset, bool as_f32 = false) {
+               float std_, float offset, bool cm, bool as_f32 = false) {
     wgen::GenDesc d{};
-    d.mode = 0;
+    d.map = 0;
     d.nseg = 1;
     d.seg[0] = {0, rows, wgen::stream_key(e->cfg.seed, tid), lrow0, lcols, lcol0};
     d.rows = rows;
     d.cols = cols;
+    d.cm = cm ? 1 : 0;
     d.scale = (float)((double)std_ / wgen::IH4_STD);
     d.offset = offset;
     d.as_f32 = as_f32 ? 1 : 0;
@@ -81,21 +82,22 @@ void build_rope_tables(rt_engine* e) {
     RT_CUDA(cudaMemcpy(e->sin_t, hs.data(), n * sizeof(float), cudaMemcpyHostToDevice));
 }
 
+// All projection matrices live in the CM layout of gemv.cuh (one copy serves decode and prefill).
 void build_weights(rt_engine* e) {
     using namespace wgen;
     const int H = e->H, hd = e->hd, rank = e->cfg.tp_rank;
     const unsigned long long seed = e->cfg.seed;
     e->embed = dalloc<bf16>(e, (size_t)e->vocab * H);
-    gen_plain(e, e->embed, e->vocab, H, tensor_id(EMBED, -1), 0, H, 0, 0.02f, 0.f);
+    gen_plain(e, e->embed, e->vocab, H, tensor_id(EMBED, -1), 0, H, 0, 0.02f, 0.f, true);
     if (e->cfg.tied && e->cfg.tp_size == 1) {
         e->lm_head = e->embed;
     } else {
         e->lm_head = dalloc<bf16>(e, (size_t)e->vocab_l * H);
         gen_plain(e, e->lm_head, e->vocab_l, H, tensor_id(e->cfg.tied ? EMBED : LM_HEAD, -1), (long long)rank * e->vocab_l, H, 0,
-                  0.02f, 0.f);
+                  0.02f, 0.f, true);
     }
     e->final_norm = dalloc<bf16>(e, H);
-    gen_plain(e, e->final_norm, 1, H, tensor_id(FINAL_NORM, -1), 0, H, 0, 0.02f, 1.0f);
+    gen_plain(e, e->final_norm, 1, H, tensor_id(FINAL_NORM, -1), 0, H, 0, 0.02f, 1.0f, false);
 
     e->layers.resize(e->L);
     const float sc = (float)(0.02 / IH4_STD);
@@ -105,7 +107,9 @@ void build_weights(rt_engine* e) {
         w.wqkv = dalloc<bf16>(e, (size_t)e->qkv_rows * H);
         {
             GenDesc d{};
-            d.mode = 0;
+            d.map = 2;
+            d.hd = hd;
+            d.cm = 1;
             d.nseg = 3;
             d.seg[0] = {0, qr, stream_key(seed, tensor_id(Q, l)), (long long)rank * qr, H, 0};
             d.seg[1] = {qr, kr, stream_key(seed, tensor_id(K, l)), (long long)rank * kr, H, 0};
@@ -116,30 +120,33 @@ void build_weights(rt_engine* e) {
             launch_gen(d, w.wqkv, e->st);
         }
         if (e->cfg.qkv_bias) {
+            // bias as a [rows][8] fp32 matrix whose row map equals wqkv's; column 0 is the value (lcols = 1 makes the
+            // logical index the row itself), compacted below
             w.bqkv = dalloc<float>(e, e->qkv_rows);
+            float* tmp = dalloc<float>(e, (size_t)e->qkv_rows * 8);
             GenDesc d{};
-            d.mode = 0;
+            d.map = 2;
+            d.hd = hd;
+            d.cm = 0;
             d.nseg = 3;
-            // a bias is a [1][n] tensor: physical "rows" are emulated through column offsets
-            d.rows = 1;
+            d.seg[0] = {0, qr, stream_key(seed, tensor_id(Q_BIAS, l)), (long long)rank * qr, 1, 0};
+            d.seg[1] = {qr, kr, stream_key(seed, tensor_id(K_BIAS, l)), (long long)rank * kr, 1, 0};
+            d.seg[2] = {qr + kr, kr, stream_key(seed, tensor_id(V_BIAS, l)), (long long)rank * kr, 1, 0};
+            d.rows = e->qkv_rows;
+            d.cols = 8;
             d.scale = sc;
             d.as_f32 = 1;
-            d.nseg = 1;
-            d.cols = qr;
-            d.seg[0] = {0, 1, stream_key(seed, tensor_id(Q_BIAS, l)), 0, 0, (long long)rank * qr};
-            launch_gen(d, w.bqkv, e->st);
-            d.cols = kr;
-            d.seg[0] = {0, 1, stream_key(seed, tensor_id(K_BIAS, l)), 0, 0, (long long)rank * kr};
-            launch_gen(d, w.bqkv + qr, e->st);
-            d.seg[0] = {0, 1, stream_key(seed, tensor_id(V_BIAS, l)), 0, 0, (long long)rank * kr};
-            launch_gen(d, w.bqkv + qr + kr, e->st);
+            launch_gen(d, tmp, e->st);
+            RT_CUDA(cudaMemcpy2DAsync(w.bqkv, sizeof(float), tmp, 8 * sizeof(float), sizeof(float), e->qkv_rows,
+                                      cudaMemcpyDeviceToDevice, e->st));
         }
         w.wo = dalloc<bf16>(e, (size_t)H * qr);
-        gen_plain(e, w.wo, H, qr, tensor_id(O, l), 0, (long long)e->nq * hd, (long long)rank * qr, 0.02f, 0.f);
+        gen_plain(e, w.wo, H, qr, tensor_id(O, l), 0, (long long)e->nq * hd, (long long)rank * qr, 0.02f, 0.f, true);
         w.wgu = dalloc<bf16>(e, (size_t)2 * e->F_l * H);
         {
             GenDesc d{};
-            d.mode = 1;
+            d.map = 1;
+            d.cm = 1;
             d.nseg = 2;
             d.seg[0] = {0, 0, stream_key(seed, tensor_id(GATE, l)), (long long)rank * e->F_l, H, 0};
             d.seg[1] = {0, 0, stream_key(seed, tensor_id(UP, l)), (long long)rank * e->F_l, H, 0};
@@ -149,38 +156,73 @@ void build_weights(rt_engine* e) {
             launch_gen(d, w.wgu, e->st);
         }
         w.wdown = dalloc<bf16>(e, (size_t)H * e->F_l);
-        gen_plain(e, w.wdown, H, e->F_l, tensor_id(DOWN, l), 0, e->F, (long long)rank * e->F_l, 0.02f, 0.f);
+        gen_plain(e, w.wdown, H, e->F_l, tensor_id(DOWN, l), 0, e->F, (long long)rank * e->F_l, 0.02f, 0.f, true);
         w.norm1 = dalloc<bf16>(e, H);
         w.norm2 = dalloc<bf16>(e, H);
-        gen_plain(e, w.norm1, 1, H, tensor_id(IN_NORM, l), 0, H, 0, 0.02f, 1.0f);
-        gen_plain(e, w.norm2, 1, H, tensor_id(POST_NORM, l), 0, H, 0, 0.02f, 1.0f);
+        gen_plain(e, w.norm1, 1, H, tensor_id(IN_NORM, l), 0, H, 0, 0.02f, 1.0f, false);
+        gen_plain(e, w.norm2, 1, H, tensor_id(POST_NORM, l), 0, H, 0, 0.02f, 1.0f, false);
     }
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaStreamSynchronize(e->st));
 }
 
-// ---- GEMV dispatch --------------------------------------------------------------------------------
-template <int EPI, int NT, int MT>
-void gemv_launch(rt_engine* e, const GemvArgs& a, int grid) {
-    gemv_tc_kernel<NT, MT, EPI><<<grid, 256, 0, e->st>>>(a);
+// ---- launch helpers -----------------------------------------------------------------------------------
+// Every kernel of the step is launched with the programmatic-stream-serialization attribute (PDL): its CTAs may
+// become resident while the previous kernel drains, issue their first weight loads, and block in
+// griddepcontrol.wait until the previous kernel's writes are visible.
+template <typename... KArgs, typename... Args>
+void launch_pdl(rt_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = e->st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = e->use_pdl ? 1 : 0;
+    RT_CUDA(cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...));
     e->launches++;
+}
+
+template <int EPI, int NT, int MT, int NW>
+void gemv_launch(rt_engine* e, const GemvArgs& a, int grid) {
+    launch_pdl(e, gemv_kernel<NT, MT, EPI, NW>, dim3(grid), dim3(NW * 32), 0, a);
+}
+
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
+template <int EPI, int NT, int MT>
+void gemv_pick_warps(rt_engine* e, const GemvArgs& a, int grid) {
+    // long rows (down-projection, K = FFN) get 16 warps so that each warp still has only 1-2 batches of loads
+    static const int force = env_int("RT_GEMV_NW", 0);
+    const int nw = force ? force : (a.K >= 4096 ? 16 : 8);
+    if (nw == 16) gemv_launch<EPI, NT, MT, 16>(e, a, grid);
+    else gemv_launch<EPI, NT, MT, 8>(e, a, grid);
 }
 
 template <int EPI>
 int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
+    static const int force_mt = env_int("RT_GEMV_MT", 0);
     const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);
     int mt = 4 / NT;
-    while (mt > 1 && (a.N % (16 * mt) != 0 || a.N / (16 * mt) < 4 * e->sm_count)) mt >>= 1;
+    // measured on B200 (scripts/gemv_tune.py): 64-row CTAs win once they still give >= 1.5 CTAs per SM
+    while (mt > 1 && (a.N % (16 * mt) != 0 || a.N / (16 * mt) < (3 * e->sm_count) / 2)) mt >>= 1;
+    if (force_mt && force_mt * NT <= 4 && a.N % (16 * force_mt) == 0) mt = force_mt;
     const int grid = cdiv(a.N, 16 * mt);
     if (NT == 1) {
-        if (mt == 4) gemv_launch<EPI, 1, 4>(e, a, grid);
-        else if (mt == 2) gemv_launch<EPI, 1, 2>(e, a, grid);
-        else gemv_launch<EPI, 1, 1>(e, a, grid);
+        if (mt == 4) gemv_pick_warps<EPI, 1, 4>(e, a, grid);
+        else if (mt == 2) gemv_pick_warps<EPI, 1, 2>(e, a, grid);
+        else gemv_pick_warps<EPI, 1, 1>(e, a, grid);
     } else if (NT == 2) {
-        if (mt == 2) gemv_launch<EPI, 2, 2>(e, a, grid);
-        else gemv_launch<EPI, 2, 1>(e, a, grid);
+        if (mt == 2) gemv_pick_warps<EPI, 2, 2>(e, a, grid);
+        else gemv_pick_warps<EPI, 2, 1>(e, a, grid);
     } else {
-        gemv_launch<EPI, 4, 1>(e, a, grid);
+        gemv_pick_warps<EPI, 4, 1>(e, a, grid);
     }
     return grid;
 }
@@ -194,7 +236,7 @@ int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi) {
         case EPI_STORE: return gemv_dispatch<EPI_STORE>(e, a);
         case EPI_RESID: return gemv_dispatch<EPI_RESID>(e, a);
         case EPI_SWIGLU: return gemv_dispatch<EPI_SWIGLU>(e, a);
-        default: return gemv_dispatch<EPI_LOGITS>(e, a);
+        default: throw RtError(RT_ERR_INVALID, "unsupported epilogue for the test hook");
     }
 }
 
@@ -208,16 +250,10 @@ void rt_attn_host_setup() {
 void rt_attn_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunk_blocks) {
     const dim3 grid(n_chunk_blocks, a.n_kv, a.T + a.n_shared_tiles);
     const size_t smem = attn_smem_bytes(hd);
-    if (hd == 128) {
-        attn_decode_kernel<128><<<grid, ATTN_WARPS * 32, smem, e->st>>>(a);
-    } else if (hd == 64) {
-        attn_decode_kernel<64><<<grid, ATTN_WARPS * 32, smem, e->st>>>(a);
-    } else if (hd == 32) {
-        attn_decode_kernel<32><<<grid, ATTN_WARPS * 32, smem, e->st>>>(a);
-    } else {
-        throw RtError(RT_ERR_INVALID, "head_dim must be 32, 64 or 128");
-    }
-    e->launches++;
+    if (hd == 128) launch_pdl(e, attn_decode_kernel<128>, grid, dim3(ATTN_WARPS * 32), smem, a);
+    else if (hd == 64) launch_pdl(e, attn_decode_kernel<64>, grid, dim3(ATTN_WARPS * 32), smem, a);
+    else if (hd == 32) launch_pdl(e, attn_decode_kernel<32>, grid, dim3(ATTN_WARPS * 32), smem, a);
+    else throw RtError(RT_ERR_INVALID, "head_dim must be 32, 64 or 128");
 }
 
 // ===================================================================================================
@@ -308,6 +344,9 @@ void engine_init(rt_engine* e) {
     e->act_bf = zalloc_b((size_t)MAX_SLOTS * e->F_l);
     e->part_o = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * e->hd);
     e->part_ml = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * 2);
+    e->done_counter = dalloc<int>(e, 1);
+    RT_CUDA(cudaMemsetAsync(e->done_counter, 0, sizeof(int), e->st));
+    e->use_pdl = getenv("RT_NO_PDL") == nullptr;
     e->lm_ctas = e->vocab_l / 16;
     e->cta_max = zalloc_f((size_t)e->lm_ctas * 32);
     e->cta_idx = dalloc<int>(e, (size_t)e->lm_ctas * 32);
@@ -382,34 +421,30 @@ void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* p
 
 // ===================================================================================================
 // One decoder pass over T token slots (slot = (token, sequence, position) held on the device).
+// 5 kernels per layer:  [norm + QKV + bias + RoPE + KV append] -> [attention + merge] -> [O-proj + residual]
+//                       -> [norm + gate/up + SwiGLU] -> [down-proj + residual]
 // ===================================================================================================
 void engine_forward(rt_engine* e, const StepOpts& o) {
     const int T = o.T, H = e->H, hd = e->hd;
     RT_REQUIRE(T >= 1 && T <= MAX_SLOTS, "1..32 token slots per step");
-    cudaStream_t st = e->st;
+    // RT_SKIP_MASK (profiling only, results are then wrong): leave kernel classes out of the step to measure their
+    // marginal cost in the dependent chain: 2 qkv, 4 attention, 8 o-proj, 16 gate/up, 32 down, 64 lm_head, 128 sampler
+    static const int skip = env_int("RT_SKIP_MASK", 0);
 
-    embed_kernel<<<dim3(cdiv(H / 8, 128), T), 128, 0, st>>>(e->embed, e->d_tok, e->x, H, e->vocab);
-    e->launches++;
+    launch_pdl(e, embed_norm_kernel, dim3(T), dim3(256), 0, (const bf16*)e->embed, (const int*)e->d_tok, e->x,
+               (const bf16*)e->layers[0].norm1, e->xn, H, e->vocab, e->cfg.rms_eps);
 
     for (int l = 0; l < e->L; ++l) {
         const LayerW& w = e->layers[l];
         bf16* kp = e->kpool + (size_t)l * e->layer_pool_elems;
         bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
 
-        rmsnorm_kernel<<<T, 256, 0, st>>>(e->x, nullptr, w.norm1, e->xn, H, H, e->cfg.rms_eps);
-        e->launches++;
-
         GemvArgs g{};
-        g.W = w.wqkv; g.X = e->xn; g.N = e->qkv_rows; g.K = H; g.ldx = H; g.T = T;
-        g.out = e->qkv; g.ldo = e->qkv_rows; g.bias = w.bqkv;
-        gemv_dispatch<EPI_STORE>(e, g);
-
-        RopeArgs r{};
-        r.qkv = e->qkv; r.ld_qkv = e->qkv_rows; r.cos_t = e->cos_t; r.sin_t = e->sin_t;
-        r.slot_seq = e->d_seq; r.slot_pos = e->d_pos; r.page_table = e->d_page_table; r.pt_stride = e->max_pages_per_seq;
-        r.Q = e->qb; r.ldq = e->nq_l * hd; r.Kp = kp; r.Vp = vp; r.n_q = e->nq_l; r.n_kv = e->nkv_l; r.hd = hd;
-        rope_append_kernel<<<dim3(e->nq_l + 2 * e->nkv_l, T), hd / 2, 0, st>>>(r);
-        e->launches++;
+        g.W = w.wqkv; g.N = e->qkv_rows; g.K = H; g.T = T; g.X = e->xn; g.ldx = H;
+        g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t; g.slot_seq = e->d_seq; g.slot_pos = e->d_pos;
+        g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq; g.Q = e->qb; g.Kp = kp; g.Vp = vp;
+        g.n_q = e->nq_l; g.n_kv = e->nkv_l; g.hd = hd;
+        if (!(skip & 2)) gemv_dispatch<EPI_QKV>(e, g);
 
         AttnArgs a{};
         a.Q = e->qb; a.ldq = e->nq_l * hd; a.Kp = kp; a.Vp = vp; a.page_table = e->d_page_table; a.pt_stride = e->max_pages_per_seq;
@@ -417,52 +452,50 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         a.T = T; a.n_q = e->nq_l; a.n_kv = e->nkv_l; a.chunk_pages = o.chunk_pages; a.n_shared_tiles = o.n_shared_tiles;
         a.part_o = e->part_o; a.part_ml = e->part_ml; a.max_chunks = MAX_CHUNKS;
         a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd));
-        rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
-
-        MergeArgs m{};
-        m.part_o = e->part_o; m.part_ml = e->part_ml; m.max_chunks = MAX_CHUNKS; m.slot_pos = e->d_pos;
-        m.shared_len_ptr = e->d_shared_len; m.cascade = o.n_shared_tiles > 0; m.chunk_keys = o.chunk_pages * KV_PAGE;
-        m.n_q = e->nq_l; m.hd = hd; m.out_bf = e->attn_bf; m.out_f32 = nullptr; m.ldo = e->nq_l * hd;
-        attn_merge_kernel<<<dim3(e->nq_l, T), hd, 0, st>>>(m);
-        e->launches++;
+        if (!(skip & 4)) {
+            rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
+            MergeArgs m{};
+            m.part_o = e->part_o; m.part_ml = e->part_ml; m.max_chunks = MAX_CHUNKS; m.slot_pos = e->d_pos;
+            m.shared_len_ptr = e->d_shared_len; m.cascade = o.n_shared_tiles > 0; m.chunk_keys = o.chunk_pages * KV_PAGE;
+            m.n_q = e->nq_l; m.hd = hd; m.out_bf = e->attn_bf; m.out_f32 = nullptr; m.ldo = e->nq_l * hd;
+            const dim3 mg(e->nq_l, T);
+            if (hd == 128) launch_pdl(e, attn_merge2_kernel<128>, mg, dim3(128), 0, m);
+            else if (hd == 64) launch_pdl(e, attn_merge2_kernel<64>, mg, dim3(128), 0, m);
+            else launch_pdl(e, attn_merge2_kernel<32>, mg, dim3(128), 0, m);
+        }
 
         GemvArgs go{};
         go.W = w.wo; go.X = e->attn_bf; go.N = H; go.K = e->nq_l * hd; go.ldx = e->nq_l * hd; go.T = T;
         go.out = e->x; go.ldo = H;
-        gemv_dispatch<EPI_RESID>(e, go);
-
-        rmsnorm_kernel<<<T, 256, 0, st>>>(e->x, nullptr, w.norm2, e->xn, H, H, e->cfg.rms_eps);
-        e->launches++;
+        go.norm_w = w.norm2; go.xn_out = e->xn; go.done_counter = e->done_counter; go.eps = e->cfg.rms_eps;
+        if (!(skip & 8)) gemv_dispatch<EPI_RESID>(e, go);
 
         GemvArgs gu{};
-        gu.W = w.wgu; gu.X = e->xn; gu.N = 2 * e->F_l; gu.K = H; gu.ldx = H; gu.T = T;
+        gu.W = w.wgu; gu.N = 2 * e->F_l; gu.K = H; gu.T = T; gu.X = e->xn; gu.ldx = H;
         gu.out_bf = e->act_bf; gu.ldob = e->F_l;
-        gemv_dispatch<EPI_SWIGLU>(e, gu);
+        if (!(skip & 16)) gemv_dispatch<EPI_SWIGLU>(e, gu);
 
         GemvArgs gd{};
         gd.W = w.wdown; gd.X = e->act_bf; gd.N = H; gd.K = e->F_l; gd.ldx = e->F_l; gd.T = T;
         gd.out = e->x; gd.ldo = H;
-        gemv_dispatch<EPI_RESID>(e, gd);
+        gd.norm_w = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;   // feeds the next layer's QKV, or the lm_head
+        gd.xn_out = e->xn; gd.done_counter = e->done_counter; gd.eps = e->cfg.rms_eps;
+        if (!(skip & 32)) gemv_dispatch<EPI_RESID>(e, gd);
     }
 
     if (o.sample || o.store_logits) {
-        rmsnorm_kernel<<<T, 256, 0, st>>>(e->x, nullptr, e->final_norm, e->xn, H, H, e->cfg.rms_eps);
-        e->launches++;
         GemvArgs gl{};
-        gl.W = e->lm_head; gl.X = e->xn; gl.N = e->vocab_l; gl.K = H; gl.ldx = H; gl.T = T;
+        gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = H; gl.T = T; gl.X = e->xn; gl.ldx = H;
         gl.logits = o.store_logits ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
         gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
         gl.inv_temp = o.inv_temp; gl.seed = o.seed; gl.step_ptr = e->d_step;
-        const int n_cta = gemv_dispatch<EPI_LOGITS>(e, gl);
         if (o.sample) {
-            SampleArgs s{};
-            s.cta_max = e->cta_max; s.cta_idx = e->cta_idx; s.n_cta = n_cta; s.T = T; s.next_tok = e->d_next_tok;
+            gl.next_tok = e->d_next_tok; gl.done_counter = e->done_counter;
             if (o.advance) {
-                s.tok = e->d_tok; s.pos = e->d_pos; s.out_tokens = e->d_out_tokens; s.max_out = e->max_out; s.step_ptr = e->d_step;
+                gl.tok = e->d_tok; gl.pos = e->d_pos; gl.out_tokens = e->d_out_tokens; gl.max_out = e->max_out; gl.step_w = e->d_step;
             }
-            sample_final_kernel<<<1, 256, 0, st>>>(s);
-            e->launches++;
         }
+        if (!(skip & 64)) gemv_dispatch<EPI_LOGITS>(e, gl);
     }
     RT_CUDA(cudaGetLastError());
 }
@@ -470,12 +503,13 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
 // ---- attention split geometry for a call whose longest sequence reaches max_len tokens ----------------
 static void plan_chunks(int max_len, int shared_len, StepOpts& o) {
     const int total_pages = cdiv(max_len, KV_PAGE);
-    o.chunk_pages = std::max(2, cdiv(total_pages, 64));
+    o.chunk_pages = std::max(env_int("RT_ATTN_MIN_CHUNK_PAGES", 4), cdiv(total_pages, 64));
     const int C = o.chunk_pages * KV_PAGE;
     const int n_sh = cdiv(shared_len, C);
     const int n_own = cdiv(std::max(max_len - shared_len, 1), C);
     o.n_chunk_blocks = cdiv(std::max(n_sh, n_own), ATTN_WARPS);
     if (n_sh + n_own + 1 > MAX_CHUNKS) throw RtError(RT_ERR_INVALID, "attention split exceeds MAX_CHUNKS");
+    o.n_partials_max = n_sh + n_own;
 }
 
 static void check_deadline(double t0, uint64_t deadline_ms) {
@@ -744,33 +778,51 @@ void engine_export_weight(rt_engine* e, int tid, uint16_t* out, long long n_elem
     RT_REQUIRE(e->cfg.tp_size == 1, "weight export needs tp_size == 1");
     RT_CUDA(cudaSetDevice(e->dev));
     const int H = e->H, hd = e->hd;
-    auto copy_rows = [&](const bf16* src, long long rows, long long cols) {
-        RT_REQUIRE(n_elems == rows * cols, "n_elems does not match tensor shape");
-        RT_CUDA(cudaMemcpy(out, src, (size_t)rows * cols * 2, cudaMemcpyDeviceToHost));
+    // fetch a CM matrix and return it row-major (physical row order)
+    auto fetch_cm = [&](const bf16* src, int rows, int cols) {
+        std::vector<uint16_t> cm((size_t)rows * cols), rm((size_t)rows * cols);
+        RT_CUDA(cudaMemcpy(cm.data(), src, cm.size() * 2, cudaMemcpyDeviceToHost));
+        wgen::cm_to_rowmajor(cm.data(), rm.data(), rows, cols);
+        return rm;
     };
-    if (tid == 0) return copy_rows(e->embed, e->vocab, H);
-    if (tid == 1) return copy_rows(e->lm_head, e->vocab, H);
-    if (tid == 2) return copy_rows(e->final_norm, 1, H);
+    auto copy_vec = [&](const bf16* src, long long n) {
+        RT_REQUIRE(n_elems == n, "n_elems does not match tensor shape");
+        RT_CUDA(cudaMemcpy(out, src, (size_t)n * 2, cudaMemcpyDeviceToHost));
+    };
+    auto copy_all = [&](const std::vector<uint16_t>& rm) {
+        RT_REQUIRE(n_elems == (long long)rm.size(), "n_elems does not match tensor shape");
+        memcpy(out, rm.data(), rm.size() * 2);
+    };
+    // physical row of logical dim d inside a head (inverse of the RoPE pair permutation)
+    auto rope_row = [&](int d) { const int half = hd / 2; return d < half ? (d / 8) * 16 + d % 8 : ((d - half) / 8) * 16 + 8 + (d - half) % 8; };
+    if (tid == 0) return copy_all(fetch_cm(e->embed, e->vocab, H));
+    if (tid == 1) return copy_all(fetch_cm(e->lm_head, e->vocab, H));
+    if (tid == 2) return copy_vec(e->final_norm, H);
     const int l = tid / 16 - 1, k = tid % 16;
     RT_REQUIRE(l >= 0 && l < e->L && k <= 11, "bad tensor id");
     const LayerW& w = e->layers[l];
     const int qr = e->nq * hd, kr = e->nkv * hd;
     switch (k) {
-        case 0: return copy_rows(w.wqkv, qr, H);
-        case 1: return copy_rows(w.wqkv + (size_t)qr * H, kr, H);
-        case 2: return copy_rows(w.wqkv + (size_t)(qr + kr) * H, kr, H);
-        case 3: return copy_rows(w.wo, H, qr);
-        case 6: return copy_rows(w.wdown, H, e->F);
-        case 7: return copy_rows(w.norm1, 1, H);
-        case 8: return copy_rows(w.norm2, 1, H);
-        case 4:
-        case 5: {
+        case 0: case 1: case 2: {
+            const int off = k == 0 ? 0 : (k == 1 ? qr : qr + kr), cnt = k == 0 ? qr : kr;
+            RT_REQUIRE(n_elems == (long long)cnt * H, "n_elems does not match tensor shape");
+            const std::vector<uint16_t> rm = fetch_cm(w.wqkv, e->qkv_rows, H);
+            for (int r = 0; r < cnt; ++r) {
+                const int prow = off + (r / hd) * hd + rope_row(r % hd);
+                memcpy(out + (size_t)r * H, rm.data() + (size_t)prow * H, (size_t)H * 2);
+            }
+            return;
+        }
+        case 3: return copy_all(fetch_cm(w.wo, H, qr));
+        case 6: return copy_all(fetch_cm(w.wdown, H, e->F));
+        case 7: return copy_vec(w.norm1, H);
+        case 8: return copy_vec(w.norm2, H);
+        case 4: case 5: {
             RT_REQUIRE(n_elems == (long long)e->F * H, "n_elems does not match tensor shape");
-            std::vector<uint16_t> tmp((size_t)2 * e->F * H);
-            RT_CUDA(cudaMemcpy(tmp.data(), w.wgu, tmp.size() * 2, cudaMemcpyDeviceToHost));
+            const std::vector<uint16_t> rm = fetch_cm(w.wgu, 2 * e->F, H);
             for (int f = 0; f < e->F; ++f) {
                 const size_t prow = (size_t)(f / 8) * 16 + (k == 5 ? 8 : 0) + (f % 8);
-                memcpy(out + (size_t)f * H, tmp.data() + prow * H, (size_t)H * 2);
+                memcpy(out + (size_t)f * H, rm.data() + prow * H, (size_t)H * 2);
             }
             return;
         }
@@ -778,11 +830,12 @@ void engine_export_weight(rt_engine* e, int tid, uint16_t* out, long long n_elem
             RT_REQUIRE(w.bqkv != nullptr, "model has no qkv bias");
             const int off = k == 9 ? 0 : (k == 10 ? qr : qr + kr), cnt = k == 9 ? qr : kr;
             RT_REQUIRE(n_elems == cnt, "n_elems does not match tensor shape");
-            std::vector<float> tmp(cnt);
-            RT_CUDA(cudaMemcpy(tmp.data(), w.bqkv + off, (size_t)cnt * 4, cudaMemcpyDeviceToHost));
+            std::vector<float> tmp(e->qkv_rows);
+            RT_CUDA(cudaMemcpy(tmp.data(), w.bqkv, tmp.size() * 4, cudaMemcpyDeviceToHost));
             for (int i = 0; i < cnt; ++i) {
+                const float f = tmp[off + (i / hd) * hd + rope_row(i % hd)];
                 uint32_t u;
-                memcpy(&u, &tmp[i], 4);
+                memcpy(&u, &f, 4);
                 out[i] = (uint16_t)(u >> 16);
             }
             return;

@@ -27,6 +27,7 @@ struct StepOpts {
     int chunk_pages = 4;
     int n_chunk_blocks = 1;    // grid.x of the attention kernel
     int n_shared_tiles = 0;    // > 0 => cascade phase on
+    int n_partials_max = 1;    // most partials any (slot, head) will have (fused merge capacity check)
     float inv_temp = 0.f;
     unsigned long long seed = 0;
 };
@@ -68,6 +69,8 @@ struct rt_engine {
     float *x = nullptr, *qkv = nullptr, *delta = nullptr, *logits = nullptr;
     bf16 *xn = nullptr, *qb = nullptr, *attn_bf = nullptr, *act_bf = nullptr;
     float *part_o = nullptr, *part_ml = nullptr;
+    int* done_counter = nullptr;   // arrival counter of the residual projections' fused RMSNorm tail
+    bool use_pdl = true;
     float* cta_max = nullptr;
     int* cta_idx = nullptr;
     int lm_ctas = 0;

@@ -1,0 +1,452 @@
+// Decode projection kernel (v2): the weight stream of the generation backend.
+//
+// No reference counterpart (/root/reference/src/adapters/local-llm.ts:159 delegates generation to an
+// external server); SURVEY.md 8(a-K) row "decode QKV / O / gate-up / down projections" and "lm_head".
+//
+//   acc[t][n] = sum_k W[n][k] * X[t][k]        W bf16 [N][K] (HBM stream, read once), T <= 32 token slots
+//
+// Weight layout in HBM ("core-matrix-major", CM): the matrix is cut into 16-row tiles and 32-wide k-blocks;
+// one (tile, k-block) is 1 KB = [half h: rows 0-7 / 8-15][k-chunk q: 4 x 8 elements][row r: 8][8 elements].
+// Every 8-row x 16-byte "core matrix" is 128 contiguous bytes, so
+//   * a warp's mma.sync A-fragment load (lane (g,q) reads piece q*8+g of a half) is 512 CONTIGUOUS bytes,
+//     a whole tile is K/32 contiguous KB and a warp's k-range is a contiguous span of it;
+//   * the same bytes are a valid no-swizzle K-major canonical operand for tcgen05.mma (prefill path).
+// The 16 k's of one MMA are a permutation of memory order (a dot product does not care), chosen so that a
+// lane's fragment is one 16-byte piece: MMA #0 uses elements 0..3 of the piece, MMA #1 elements 4..7.
+//
+// A CTA owns 16*MT rows over the full K; its NW warps split K into contiguous spans; per-warp partial sums are
+// added in fixed warp order through shared memory (bit-reproducible, no atomics).  With PDL the first weight
+// loads are issued BEFORE griddepcontrol.wait, so the HBM stream keeps running across kernel boundaries.
+//
+// Fusions: EPI_QKV    -> + bias, RoPE, q -> bf16 Q buffer, k/v -> bf16 into their KV page;
+//          EPI_RESID  -> x += acc; the last CTA to finish then RMS-normalises the updated rows into the bf16
+//                        input of the next projection (no separate RMSNorm launch);
+//          EPI_SWIGLU -> bf16(silu(gate) * up);   EPI_LOGITS -> logits and per-CTA arg-max candidates.
+#pragma once
+#include "common.cuh"
+
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4 };
+
+constexpr int KV_PAGE = 16;
+
+struct GemvArgs {
+    const bf16* W;            // CM layout
+    int N, K, T;
+    // B operand
+    const bf16* X;            // !NORM: [>=NT*8][ldx] bf16 (rows >= T readable, finite)
+    int ldx;
+    // RESID "norm tail": the LAST CTA to finish the residual update normalises the new rows for the next
+    // projection (xn_out = bf16(x * rsqrt(mean x^2 + eps) * norm_w)), so no separate RMSNorm launch exists
+    const bf16* norm_w;       // [N] nullable => no tail
+    bf16* xn_out;             // [T][N]
+    int* done_counter;        // zero before the first launch; reset by the last CTA
+    float eps;
+    // outputs
+    float* out;               // STORE: out[t*ldo+n] = acc (+bias) ; RESID: out[t*ldo+n] += acc
+    int ldo;
+    const float* bias;        // STORE / QKV (physical row order), nullable
+    bf16* out_bf;             // SWIGLU: [t*ldob + col]
+    int ldob;
+    // LOGITS
+    float* logits;
+    int ld_logits;
+    float* cta_max;
+    int* cta_idx;
+    int row_offset;
+    float inv_temp;
+    unsigned long long seed;
+    const int* step_ptr;
+    // LOGITS "sampler tail" (next_tok nullable => candidates only)
+    int* next_tok;            // [T]
+    int* tok;                 // nullable: tok[t] = next (decode feeds the next step)
+    int* pos;                 // nullable: pos[t] += 1
+    int* out_tokens;          // nullable: out_tokens[t*max_out + *step_w] = next
+    int max_out;
+    int* step_w;              // nullable: incremented once per launch
+    // QKV + RoPE + KV append
+    const float* cos_t;
+    const float* sin_t;
+    const int* slot_seq;
+    const int* slot_pos;
+    const int* page_table;
+    int pt_stride;
+    bf16* Q;                  // [T][n_q*hd]
+    bf16* Kp;
+    bf16* Vp;
+    int n_q, n_kv, hd;
+};
+
+__device__ __forceinline__ float gumbel_noise(unsigned long long seed, int step, int slot, int idx) {
+    unsigned long long z = seed + 0x9E3779B97F4A7C15ull * ((unsigned long long)(unsigned)step * 64ull + (unsigned)slot) +
+                           ((unsigned long long)(unsigned)idx << 20);
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const float u = ((float)(z >> 40) + 0.5f) * (1.0f / 16777216.0f);  // (0,1)
+    return -logf(-logf(u));
+}
+
+// programmatic dependent launch (PDL): no-ops when the kernel was launched without the attribute
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;"); }
+
+template <int NT, int MT, int EPI, int NW>
+__global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
+    static_assert(NT * MT <= 4, "shared-memory reduction sized for NT*MT <= 4");
+    constexpr int U = (MT * NT >= 4) ? 2 : (MT * NT == 2 ? 4 : 8);
+    constexpr int NTHR = NW * 32;
+    __shared__ float4 red[NW][MT * NT][32];
+    __shared__ float res[MT * NT][16][8];
+    __shared__ float s_rn[NT * 8];
+    __shared__ int s_last;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+    const int tile0 = blockIdx.x * MT;
+    const int row0 = tile0 * 16;
+    const int nkb = a.K >> 5;
+    const int kb0 = (warp * nkb) / NW, kb1 = ((warp + 1) * nkb) / NW;
+
+    // lane's byte offset inside a 512-byte half: piece (q*8 + g)
+    const bf16* wbase[MT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+        int tile = tile0 + mt;
+        tile = tile * 16 < a.N ? tile : (a.N / 16 - 1);
+        wbase[mt] = a.W + (size_t)tile * nkb * 512 + (q * 8 + g) * 8;
+    }
+
+    float acc[MT][NT][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[mt][nt][i] = 0.f;
+
+    // ---- first batch of weight loads: independent of the previous kernel, issued before the PDL wait ----
+    uint4 av[U][MT][2];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const int kb = kb0 + u;
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt) {
+            if (kb < kb1) {
+                av[u][mt][0] = ld_stream16(wbase[mt] + (size_t)kb * 512);
+                av[u][mt][1] = ld_stream16(wbase[mt] + (size_t)kb * 512 + 256);
+            } else {
+                av[u][mt][0] = make_uint4(0, 0, 0, 0);
+                av[u][mt][1] = make_uint4(0, 0, 0, 0);
+            }
+        }
+    }
+    griddep_launch();
+    griddep_wait();
+
+    for (int kbb = kb0; kbb < kb1; kbb += U) {
+        // B operand for this batch
+        uint4 xv[U][NT];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int kb = kbb + u;
+            const int ko = (kb << 5) + q * 8;
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                const int slot = nt * 8 + g;
+                if (kb < kb1) {
+                    xv[u][nt] = *reinterpret_cast<const uint4*>(a.X + (size_t)slot * a.ldx + ko);
+                } else {
+                    xv[u][nt] = make_uint4(0, 0, 0, 0);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
+                                   xv[u][nt].x, xv[u][nt].y);
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
+                                   xv[u][nt].z, xv[u][nt].w);
+                }
+        // next batch of weights
+        if (kbb + U < kb1) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int kb = kbb + U + u;
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt) {
+                    if (kb < kb1) {
+                        av[u][mt][0] = ld_stream16(wbase[mt] + (size_t)kb * 512);
+                        av[u][mt][1] = ld_stream16(wbase[mt] + (size_t)kb * 512 + 256);
+                    } else {
+                        av[u][mt][0] = make_uint4(0, 0, 0, 0);
+                        av[u][mt][1] = make_uint4(0, 0, 0, 0);
+                    }
+                }
+            }
+        }
+    }
+
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+            red[warp][mt * NT + nt][lane] = make_float4(acc[mt][nt][0], acc[mt][nt][1], acc[mt][nt][2], acc[mt][nt][3]);
+    __syncthreads();
+
+    // fixed-order sum over the warps; element (tile, lane', i) -> row = lane'/4 + 8*(i>>1), slot = (lane'%4)*2 + (i&1)
+    for (int e = threadIdx.x; e < MT * NT * 32; e += NTHR) {
+        const int tile = e >> 5, l2 = e & 31;
+        float4 s = red[0][tile][l2];
+#pragma unroll
+        for (int w = 1; w < NW; ++w) {
+            const float4 v = red[w][tile][l2];
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        const int rr = l2 >> 2, cc = (l2 & 3) * 2;
+        res[tile][rr][cc] = s.x;
+        res[tile][rr][cc + 1] = s.y;
+        res[tile][rr + 8][cc] = s.z;
+        res[tile][rr + 8][cc + 1] = s.w;
+    }
+    __syncthreads();
+
+    if (EPI == EPI_STORE) {
+        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
+            const int r = e % (MT * 16), s = e / (MT * 16);
+            const int n = row0 + r;
+            if (s < a.T && n < a.N) {
+                float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                if (a.bias) v += a.bias[n];
+                a.out[(size_t)s * a.ldo + n] = v;
+            }
+        }
+    } else if (EPI == EPI_RESID) {
+        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
+            const int r = e % (MT * 16), s = e / (MT * 16);
+            const int n = row0 + r;
+            if (s < a.T && n < a.N) {
+                float* o = a.out + (size_t)s * a.ldo + n;
+                const float v = *o + res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                *o = v;
+            }
+        }
+        if (a.norm_w) {
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) s_last = atomicAdd(a.done_counter, 1) == (int)gridDim.x - 1;
+            __syncthreads();
+            if (s_last) {
+                __threadfence();
+                // every row of x is final: normalise the T slots for the next projection (fixed summation order).
+                // Fast path: 4 slots at a time, each thread holds its <= 4 float4 of every slot in registers, so the
+                // whole tail is one L2 round trip + one block reduction per group.
+                const int n4 = a.N >> 2;
+                constexpr int PER = 4, SG = 4;
+                float* sred = &res[0][0][0];                       // >= 128 floats; NW * SG <= 64 used
+                if (n4 <= PER * NTHR) {
+                    for (int s0 = 0; s0 < a.T; s0 += SG) {
+                        float4 v[SG][PER];
+                        float ss[SG];
+#pragma unroll
+                        for (int sl = 0; sl < SG; ++sl) {
+                            ss[sl] = 0.f;
+#pragma unroll
+                            for (int k = 0; k < PER; ++k) {
+                                const int c4 = threadIdx.x + k * NTHR;
+                                if (s0 + sl < a.T && c4 < n4) {
+                                    v[sl][k] = __ldcg(reinterpret_cast<const float4*>(a.out + (size_t)(s0 + sl) * a.ldo) + c4);
+                                    ss[sl] += v[sl][k].x * v[sl][k].x + v[sl][k].y * v[sl][k].y + v[sl][k].z * v[sl][k].z +
+                                              v[sl][k].w * v[sl][k].w;
+                                } else {
+                                    v[sl][k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int sl = 0; sl < SG; ++sl) {
+                            ss[sl] = warp_sum(ss[sl]);
+                            if (lane == 0) sred[warp * SG + sl] = ss[sl];
+                        }
+                        __syncthreads();
+#pragma unroll
+                        for (int sl = 0; sl < SG; ++sl) {
+                            float tot = 0.f;
+                            for (int w = 0; w < NW; ++w) tot += sred[w * SG + sl];
+                            const float r = 1.0f / sqrtf(tot / (float)a.N + a.eps);
+#pragma unroll
+                            for (int k = 0; k < PER; ++k) {
+                                const int c4 = threadIdx.x + k * NTHR;
+                                if (s0 + sl < a.T && c4 < n4) {
+                                    const uint2 wv = *reinterpret_cast<const uint2*>(a.norm_w + c4 * 4);
+                                    uint2 o;
+                                    o.x = pack_bf16(v[sl][k].x * r * bf16lo(wv.x), v[sl][k].y * r * bf16hi(wv.x));
+                                    o.y = pack_bf16(v[sl][k].z * r * bf16lo(wv.y), v[sl][k].w * r * bf16hi(wv.y));
+                                    *reinterpret_cast<uint2*>(a.xn_out + (size_t)(s0 + sl) * a.N + c4 * 4) = o;
+                                }
+                            }
+                        }
+                        __syncthreads();
+                    }
+                } else {
+                    for (int s = 0; s < a.T; ++s) {
+                        const float* xr = a.out + (size_t)s * a.ldo;
+                        float ss = 0.f;
+                        for (int c = threadIdx.x * 4; c < a.N; c += NTHR * 4) {
+                            const float4 v = __ldcg(reinterpret_cast<const float4*>(xr + c));
+                            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+                        }
+                        ss = warp_sum(ss);
+                        if (lane == 0) sred[warp] = ss;
+                        __syncthreads();
+                        float tot = 0.f;
+                        for (int w = 0; w < NW; ++w) tot += sred[w];
+                        const float r = 1.0f / sqrtf(tot / (float)a.N + a.eps);
+                        for (int c = threadIdx.x * 4; c < a.N; c += NTHR * 4) {
+                            const float4 v = __ldcg(reinterpret_cast<const float4*>(xr + c));
+                            const uint2 wv = *reinterpret_cast<const uint2*>(a.norm_w + c);
+                            uint2 o;
+                            o.x = pack_bf16(v.x * r * bf16lo(wv.x), v.y * r * bf16hi(wv.x));
+                            o.y = pack_bf16(v.z * r * bf16lo(wv.y), v.w * r * bf16hi(wv.y));
+                            *reinterpret_cast<uint2*>(a.xn_out + (size_t)s * a.N + c) = o;
+                        }
+                        __syncthreads();
+                    }
+                }
+                if (threadIdx.x == 0) *a.done_counter = 0;
+            }
+        }
+    } else if (EPI == EPI_SWIGLU) {
+        // rows 0..7 of every 16-row tile are gate_{8j+r}, rows 8..15 are up_{8j+r}
+        for (int e = threadIdx.x; e < MT * 8 * NT * 8; e += NTHR) {
+            const int r = e % (MT * 8), s = e / (MT * 8);
+            const int mt = r >> 3, rr = r & 7;
+            const int n = row0 + mt * 16;
+            if (s < a.T && n < a.N) {
+                const float gt = res[mt * NT + (s >> 3)][rr][s & 7];
+                const float up = res[mt * NT + (s >> 3)][rr + 8][s & 7];
+                const float act = gt / (1.0f + expf(-gt)) * up;
+                a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = __float2bfloat16_rn(act);
+            }
+        }
+    } else if (EPI == EPI_QKV) {
+        // tile j of a head holds dims [8j, 8j+8) in rows 0..7 and dims [hd/2+8j, hd/2+8j+8) in rows 8..15:
+        // a rotate_half pair (d, d+hd/2) sits in rows (r, r+8) of one tile.
+        const int half = a.hd >> 1;
+        for (int e = threadIdx.x; e < MT * 8 * NT * 8; e += NTHR) {
+            const int r = e % (MT * 8), s = e / (MT * 8);
+            const int mt = r >> 3, rr = r & 7;
+            const int n = row0 + mt * 16;
+            if (s < a.T && n < a.N) {
+                float x1 = res[mt * NT + (s >> 3)][rr][s & 7];
+                float x2 = res[mt * NT + (s >> 3)][rr + 8][s & 7];
+                if (a.bias) {
+                    x1 += a.bias[n + rr];
+                    x2 += a.bias[n + rr + 8];
+                }
+                const int head = n / a.hd;
+                const int d = ((n % a.hd) >> 4) * 8 + rr;
+                const int pos = a.slot_pos[s];
+                float y1 = x1, y2 = x2;
+                if (head < a.n_q + a.n_kv) {
+                    const float c = a.cos_t[(size_t)pos * half + d], sn = a.sin_t[(size_t)pos * half + d];
+                    y1 = x1 * c - x2 * sn;
+                    y2 = x2 * c + x1 * sn;
+                }
+                bf16* dst;
+                if (head < a.n_q) {
+                    dst = a.Q + (size_t)s * (a.n_q * a.hd) + (size_t)head * a.hd;
+                } else {
+                    const bool is_k = head < a.n_q + a.n_kv;
+                    const int kvh = head - a.n_q - (is_k ? 0 : a.n_kv);
+                    const int page = a.page_table[(size_t)a.slot_seq[s] * a.pt_stride + pos / KV_PAGE];
+                    dst = (is_k ? a.Kp : a.Vp) + (((size_t)page * a.n_kv + kvh) * KV_PAGE + (pos % KV_PAGE)) * a.hd;
+                }
+                dst[d] = __float2bfloat16_rn(y1);
+                dst[d + half] = __float2bfloat16_rn(y2);
+            }
+        }
+    } else {  // EPI_LOGITS
+        if (a.logits) {
+            for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
+                const int r = e % (MT * 16), s = e / (MT * 16);
+                const int n = row0 + r;
+                if (s < a.T && n < a.N) a.logits[(size_t)s * a.ld_logits + n] = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+            }
+        }
+        if (threadIdx.x < NT * 8) {
+            const int s = threadIdx.x;
+            float best = -INFINITY;
+            int bi = 0x7fffffff;
+            if (s < a.T) {
+                const int step = (a.inv_temp > 0.f && a.step_ptr) ? *a.step_ptr : 0;
+                for (int r = 0; r < MT * 16; ++r) {
+                    const int n = row0 + r;
+                    if (n >= a.N) break;
+                    float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                    if (a.inv_temp > 0.f) v = v * a.inv_temp + gumbel_noise(a.seed, step, s, a.row_offset + n);
+                    if (v > best) { best = v; bi = a.row_offset + n; }
+                }
+            }
+            a.cta_max[blockIdx.x * 32 + s] = best;
+            a.cta_idx[blockIdx.x * 32 + s] = bi;
+        }
+        if (a.next_tok) {
+            // the LAST CTA to publish its candidates picks the winners (lowest index wins ties, like torch.argmax)
+            // and advances the decode state on the device, so a decode step needs no separate sampler launch
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) s_last = atomicAdd(a.done_counter, 1) == (int)gridDim.x - 1;
+            __syncthreads();
+            if (s_last) {
+                __threadfence();
+                const int n_cta = gridDim.x;
+                float* sval = &res[0][0][0];                        // [NW] values, then [NW] indices
+                int* sidx = reinterpret_cast<int*>(sval + 32);
+                const int step = a.step_w ? *a.step_w : 0;
+                for (int t = 0; t < a.T; ++t) {
+                    float best = -INFINITY;
+                    int bi = 0x7fffffff;
+                    for (int c0 = threadIdx.x; c0 < n_cta; c0 += NTHR * 4) {
+                        float v[4];
+                        int ix[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int c = c0 + j * NTHR;
+                            v[j] = c < n_cta ? __ldcg(a.cta_max + c * 32 + t) : -INFINITY;
+                            ix[j] = c < n_cta ? __ldcg(a.cta_idx + c * 32 + t) : 0x7fffffff;
+                        }
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (v[j] > best || (v[j] == best && ix[j] < bi)) { best = v[j]; bi = ix[j]; }
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const float v2 = __shfl_xor_sync(0xffffffffu, best, o);
+                        const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
+                        if (v2 > best || (v2 == best && i2 < bi)) { best = v2; bi = i2; }
+                    }
+                    if (lane == 0) { sval[warp] = best; sidx[warp] = bi; }
+                    __syncthreads();
+                    if (threadIdx.x == 0) {
+                        for (int w = 1; w < NW; ++w)
+                            if (sval[w] > best || (sval[w] == best && sidx[w] < bi)) { best = sval[w]; bi = sidx[w]; }
+                        if (bi == 0x7fffffff) bi = 0;
+                        a.next_tok[t] = bi;
+                        if (a.tok) a.tok[t] = bi;
+                        if (a.pos) a.pos[t] += 1;
+                        if (a.out_tokens && step < a.max_out) a.out_tokens[(size_t)t * a.max_out + step] = bi;
+                    }
+                    __syncthreads();
+                }
+                if (threadIdx.x == 0) {
+                    if (a.step_w) *a.step_w = step + 1;
+                    *a.done_counter = 0;
+                }
+            }
+        }
+    }
+}

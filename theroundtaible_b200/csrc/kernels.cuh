@@ -8,23 +8,56 @@
 // shared-memory sums (deterministic: no atomics anywhere on the data path).
 #pragma once
 #include "common.cuh"
+#include "gemv.cuh"
 
 // =================================================================================================
-// Embedding gather:  x[t][:] = float(E[tok[t]][:])
+// Embedding gather from the CM-layout table (gemv.cuh):  x[t][:] = float(E[tok[t]][:]), and the first layer's
+// RMSNorm of it (xn = bf16(x * rsqrt(mean x^2 + eps) * w)).  One CTA per slot.
 // =================================================================================================
-static __global__ void embed_kernel(const bf16* __restrict__ E, const int* __restrict__ tok, float* __restrict__ x,
-                             int H, int vocab) {
-    const int t = blockIdx.y;
+static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __restrict__ E, const int* __restrict__ tok,
+                                                                float* __restrict__ x, const bf16* __restrict__ norm_w,
+                                                                bf16* __restrict__ xn, int H, int vocab, float eps) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ float red[8];
+    __shared__ float s_r;
+    const int t = blockIdx.x;
     int id = tok[t];
     id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
-    if (c >= H) return;
-    const uint4 v = *reinterpret_cast<const uint4*>(E + (size_t)id * H + c);
-    float4 a = make_float4(bf16lo(v.x), bf16hi(v.x), bf16lo(v.y), bf16hi(v.y));
-    float4 b = make_float4(bf16lo(v.z), bf16hi(v.z), bf16lo(v.w), bf16hi(v.w));
-    float4* o = reinterpret_cast<float4*>(x + (size_t)t * H + c);
-    o[0] = a;
-    o[1] = b;
+    const int nkb = H >> 5;
+    const int tile = id >> 4, h = (id >> 3) & 1, r = id & 7;
+    float ss = 0.f;
+    for (int k = threadIdx.x * 8; k < H; k += blockDim.x * 8) {
+        const int kb = k >> 5, q = (k & 31) >> 3;
+        const uint4 v = *reinterpret_cast<const uint4*>(E + ((((size_t)tile * nkb + kb) * 2 + h) * 4 + q) * 64 + r * 8);
+        const float4 a = make_float4(bf16lo(v.x), bf16hi(v.x), bf16lo(v.y), bf16hi(v.y));
+        const float4 b = make_float4(bf16lo(v.z), bf16hi(v.z), bf16lo(v.w), bf16hi(v.w));
+        float4* o = reinterpret_cast<float4*>(x + (size_t)t * H + k);
+        o[0] = a;
+        o[1] = b;
+        ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float tot = 0.f;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) tot += red[i];
+        s_r = 1.0f / sqrtf(tot / (float)H + eps);
+    }
+    __syncthreads();
+    const float rn = s_r;
+    for (int k = threadIdx.x * 8; k < H; k += blockDim.x * 8) {
+        const float4 a = *reinterpret_cast<const float4*>(x + (size_t)t * H + k);
+        const float4 b = *reinterpret_cast<const float4*>(x + (size_t)t * H + k + 4);
+        const uint4 wv = *reinterpret_cast<const uint4*>(norm_w + k);
+        uint4 o;
+        o.x = pack_bf16(a.x * rn * bf16lo(wv.x), a.y * rn * bf16hi(wv.x));
+        o.y = pack_bf16(a.z * rn * bf16lo(wv.y), a.w * rn * bf16hi(wv.y));
+        o.z = pack_bf16(b.x * rn * bf16lo(wv.z), b.y * rn * bf16hi(wv.z));
+        o.w = pack_bf16(b.z * rn * bf16lo(wv.w), b.w * rn * bf16hi(wv.w));
+        *reinterpret_cast<uint4*>(xn + (size_t)t * H + k) = o;
+    }
 }
 
 // =================================================================================================
@@ -69,211 +102,6 @@ static __global__ void __launch_bounds__(256) rmsnorm_kernel(float* __restrict__
     }
 }
 
-// =================================================================================================
-// Decode projection ("GEMV" with up to 32 token slots):   acc[t][n] = sum_k W[n][k] * X[t][k]
-//
-// W bf16 [N][K] row-major is the HBM stream (read exactly once).  A CTA owns 16*MT rows over the
-// FULL K; its 8 warps interleave over 32-wide k-blocks, so a row is read as 8 x 64 B contiguous
-// pieces per round.  Each lane issues 16-byte loads only.  The multiply runs on the legacy tensor
-// path (mma.sync m16n8k16, rows = M, token slots = N) so that the FMA pipe never becomes the bound
-// at 5..8 knights.  Because a dot product does not care about the order of k, the
-// 16 k's of one MMA are a PERMUTATION of memory order chosen so that every lane's A fragment is one
-// contiguous 16-byte piece:  lane (g=lane/4, q=lane%4) holds W[row g][kb*32 + 8q .. 8q+7]; MMA #0
-// consumes elements {0,1,2,3} of that piece, MMA #1 elements {4,5,6,7}; X uses the same map.
-// The 8 per-warp partial sums are added in fixed warp order through shared memory.
-// =================================================================================================
-enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3 };
-
-struct GemvArgs {
-    const bf16* W;
-    const bf16* X;       // [NT*8][ldx] bf16; rows >= T must be readable (zero padded)
-    int N, K, ldx, T;
-    float* out;          // STORE: out[t*ldo+n] = acc (+bias[n]);  RESID: out[t*ldo+n] += acc
-    int ldo;
-    const float* bias;   // nullable (STORE only)
-    bf16* out_bf;        // SWIGLU: out_bf[t*ldob + n/2-ish] = bf16(silu(gate)*up)
-    int ldob;
-    // LOGITS
-    float* logits;       // nullable: logits[t*ld_logits + n]
-    int ld_logits;
-    float* cta_max;      // [gridDim.x][32]
-    int* cta_idx;        // [gridDim.x][32]
-    int row_offset;      // vocab-parallel: global id of row 0
-    float inv_temp;      // 0 => greedy
-    unsigned long long seed;
-    const int* step_ptr;
-};
-
-__device__ __forceinline__ float gumbel_noise(unsigned long long seed, int step, int slot, int idx) {
-    unsigned long long z = seed + 0x9E3779B97F4A7C15ull * ((unsigned long long)(unsigned)step * 64ull + (unsigned)slot) +
-                           ((unsigned long long)(unsigned)idx << 20);
-    z += 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    const float u = ((float)(z >> 40) + 0.5f) * (1.0f / 16777216.0f);  // (0,1)
-    return -logf(-logf(u));
-}
-
-template <int NT, int MT, int EPI>
-__global__ void __launch_bounds__(256) gemv_tc_kernel(const GemvArgs a) {
-    static_assert(NT * MT <= 4, "shared-memory reduction sized for NT*MT <= 4");
-    constexpr int U = (MT * NT >= 4) ? 2 : (MT * NT == 2 ? 4 : 8);
-    __shared__ float4 red[8][MT * NT][32];
-    __shared__ float res[MT * NT][16][8];
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
-    const int row0 = blockIdx.x * (16 * MT);
-    const int nkb = a.K >> 5;
-
-    const bf16* wp[MT][2];
-#pragma unroll
-    for (int mt = 0; mt < MT; ++mt) {
-        int r0 = row0 + mt * 16 + g, r1 = r0 + 8;
-        r0 = r0 < a.N ? r0 : a.N - 1;
-        r1 = r1 < a.N ? r1 : a.N - 1;
-        wp[mt][0] = a.W + (size_t)r0 * a.K + q * 8;
-        wp[mt][1] = a.W + (size_t)r1 * a.K + q * 8;
-    }
-    const bf16* xp[NT];
-#pragma unroll
-    for (int nt = 0; nt < NT; ++nt) xp[nt] = a.X + (size_t)(nt * 8 + g) * a.ldx + q * 8;
-
-    float acc[MT][NT][4];
-#pragma unroll
-    for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) acc[mt][nt][i] = 0.f;
-
-    int kb = warp;
-    for (; kb + 8 * (U - 1) < nkb; kb += 8 * U) {
-        uint4 av[U][MT][2];
-        uint4 xv[U][NT];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int ko = (kb + 8 * u) << 5;
-#pragma unroll
-            for (int mt = 0; mt < MT; ++mt) {
-                av[u][mt][0] = ld_stream16(wp[mt][0] + ko);
-                av[u][mt][1] = ld_stream16(wp[mt][1] + ko);
-            }
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) xv[u][nt] = *reinterpret_cast<const uint4*>(xp[nt] + ko);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u)
-#pragma unroll
-            for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
-                                   xv[u][nt].x, xv[u][nt].y);
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
-                                   xv[u][nt].z, xv[u][nt].w);
-                }
-    }
-    for (; kb < nkb; kb += 8) {
-        const int ko = kb << 5;
-        uint4 av[MT][2];
-        uint4 xv[NT];
-#pragma unroll
-        for (int mt = 0; mt < MT; ++mt) {
-            av[mt][0] = ld_stream16(wp[mt][0] + ko);
-            av[mt][1] = ld_stream16(wp[mt][1] + ko);
-        }
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt) xv[nt] = *reinterpret_cast<const uint4*>(xp[nt] + ko);
-#pragma unroll
-        for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-                mma_bf16_16816(acc[mt][nt], av[mt][0].x, av[mt][1].x, av[mt][0].y, av[mt][1].y, xv[nt].x, xv[nt].y);
-                mma_bf16_16816(acc[mt][nt], av[mt][0].z, av[mt][1].z, av[mt][0].w, av[mt][1].w, xv[nt].z, xv[nt].w);
-            }
-    }
-
-#pragma unroll
-    for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-            red[warp][mt * NT + nt][lane] = make_float4(acc[mt][nt][0], acc[mt][nt][1], acc[mt][nt][2], acc[mt][nt][3]);
-    __syncthreads();
-
-    // fixed-order sum over the 8 warps; element (tile, lane', i) -> row = lane'/4 + 8*(i>>1), slot = (lane'%4)*2 + (i&1)
-    for (int e = threadIdx.x; e < MT * NT * 32; e += 256) {
-        const int tile = e >> 5, l2 = e & 31;
-        float4 s = red[0][tile][l2];
-#pragma unroll
-        for (int w = 1; w < 8; ++w) {
-            const float4 v = red[w][tile][l2];
-            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-        }
-        const int rr = l2 >> 2, cc = (l2 & 3) * 2;
-        res[tile][rr][cc] = s.x;
-        res[tile][rr][cc + 1] = s.y;
-        res[tile][rr + 8][cc] = s.z;
-        res[tile][rr + 8][cc + 1] = s.w;
-    }
-    __syncthreads();
-
-    if (EPI == EPI_STORE || EPI == EPI_RESID) {
-        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += 256) {
-            const int r = e % (MT * 16), s = e / (MT * 16);
-            const int n = row0 + r;
-            if (s < a.T && n < a.N) {
-                float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
-                float* o = a.out + (size_t)s * a.ldo + n;
-                if (EPI == EPI_STORE) {
-                    if (a.bias) v += a.bias[n];
-                    *o = v;
-                } else {
-                    *o += v;
-                }
-            }
-        }
-    } else if (EPI == EPI_SWIGLU) {
-        // rows 0..7 of every 16-row tile are gate_{8j+r}, rows 8..15 are up_{8j+r}
-        for (int e = threadIdx.x; e < MT * 8 * NT * 8; e += 256) {
-            const int r = e % (MT * 8), s = e / (MT * 8);
-            const int mt = r >> 3, rr = r & 7;
-            const int n = row0 + mt * 16;  // first physical row of the tile
-            if (s < a.T && n < a.N) {
-                const float gt = res[mt * NT + (s >> 3)][rr][s & 7];
-                const float up = res[mt * NT + (s >> 3)][rr + 8][s & 7];
-                const float act = gt / (1.0f + expf(-gt)) * up;
-                a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = __float2bfloat16_rn(act);
-            }
-        }
-    } else {  // EPI_LOGITS
-        if (a.logits) {
-            for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += 256) {
-                const int r = e % (MT * 16), s = e / (MT * 16);
-                const int n = row0 + r;
-                if (s < a.T && n < a.N) a.logits[(size_t)s * a.ld_logits + n] = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
-            }
-        }
-        if (threadIdx.x < NT * 8) {
-            const int s = threadIdx.x;
-            float best = -INFINITY;
-            int bi = 0x7fffffff;
-            if (s < a.T) {
-                const int step = (a.inv_temp > 0.f && a.step_ptr) ? *a.step_ptr : 0;
-                for (int r = 0; r < MT * 16; ++r) {
-                    const int n = row0 + r;
-                    if (n >= a.N) break;
-                    float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
-                    if (a.inv_temp > 0.f) v = v * a.inv_temp + gumbel_noise(a.seed, step, s, a.row_offset + n);
-                    if (v > best) { best = v; bi = a.row_offset + n; }
-                }
-            }
-            a.cta_max[blockIdx.x * 32 + s] = best;
-            a.cta_idx[blockIdx.x * 32 + s] = bi;
-        }
-    }
-}
-
 // final arg-max over the per-CTA candidates; advances the decode state on the device so that a
 // decode step can be replayed as a CUDA graph without host involvement.
 struct SampleArgs {
@@ -289,6 +117,8 @@ struct SampleArgs {
 };
 
 static __global__ void __launch_bounds__(256) sample_final_kernel(const SampleArgs a) {
+    griddep_launch();
+    griddep_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int step = a.step_ptr ? *a.step_ptr : 0;
     for (int t = warp; t < a.T; t += 8) {
@@ -318,61 +148,6 @@ static __global__ void __launch_bounds__(256) sample_final_kernel(const SampleAr
 }
 
 // =================================================================================================
-// RoPE + KV append.  qkv fp32 [T][(n_q+2*n_kv)*hd] (bias already added).  Rotated q -> bf16 Q buffer,
-// rotated k and v -> bf16 into the paged cache at (seq, pos).  rotate_half pairing (i, i+hd/2) as in
-// HF modeling_llama.py apply_rotary_pos_emb.  KV page layout: [page][kv_head][16 tokens][hd].
-// =================================================================================================
-constexpr int KV_PAGE = 16;
-
-struct RopeArgs {
-    const float* qkv;
-    int ld_qkv;
-    const float* cos_t;  // [max_pos][hd/2]
-    const float* sin_t;
-    const int* slot_seq;
-    const int* slot_pos;
-    const int* page_table;
-    int pt_stride;
-    bf16* Q;             // [T][n_q*hd]
-    int ldq;
-    bf16* Kp;
-    bf16* Vp;
-    int n_q, n_kv, hd;
-};
-
-static __global__ void rope_append_kernel(const RopeArgs a) {
-    const int t = blockIdx.y, head = blockIdx.x;
-    const int half = a.hd >> 1;
-    const int d = threadIdx.x;
-    if (d >= half) return;
-    const int pos = a.slot_pos[t];
-    const float* src = a.qkv + (size_t)t * a.ld_qkv + (size_t)head * a.hd;
-    const float x1 = src[d], x2 = src[d + half];
-    if (head < a.n_q + a.n_kv) {
-        const float c = a.cos_t[(size_t)pos * half + d], s = a.sin_t[(size_t)pos * half + d];
-        const float y1 = x1 * c - x2 * s;
-        const float y2 = x2 * c + x1 * s;
-        if (head < a.n_q) {
-            bf16* q = a.Q + (size_t)t * a.ldq + (size_t)head * a.hd;
-            q[d] = __float2bfloat16_rn(y1);
-            q[d + half] = __float2bfloat16_rn(y2);
-        } else {
-            const int kvh = head - a.n_q;
-            const int page = a.page_table[(size_t)a.slot_seq[t] * a.pt_stride + pos / KV_PAGE];
-            bf16* k = a.Kp + (((size_t)page * a.n_kv + kvh) * KV_PAGE + (pos % KV_PAGE)) * a.hd;
-            k[d] = __float2bfloat16_rn(y1);
-            k[d + half] = __float2bfloat16_rn(y2);
-        }
-    } else {
-        const int kvh = head - a.n_q - a.n_kv;
-        const int page = a.page_table[(size_t)a.slot_seq[t] * a.pt_stride + pos / KV_PAGE];
-        bf16* v = a.Vp + (((size_t)page * a.n_kv + kvh) * KV_PAGE + (pos % KV_PAGE)) * a.hd;
-        v[d] = __float2bfloat16_rn(x1);
-        v[d + half] = __float2bfloat16_rn(x2);
-    }
-}
-
-// =================================================================================================
 // Paged GQA decode attention, split over the KV length, with a shared-prefix (cascade) phase.
 //
 // Work item = one WARP: 16 query rows x one chunk of `chunk_pages` KV pages of one kv head.
@@ -382,7 +157,7 @@ static __global__ void rope_append_kernel(const RopeArgs a) {
 // Each warp streams its pages through a private 4-stage cp.async ring in shared memory (XOR-swizzled
 // 16-byte pieces, conflict-free ldmatrix), computes S = QK^T and O += PV with mma.sync m16n8k16 and an
 // online softmax in the exp2 domain, and writes an un-normalised partial (O, m, l).  attn_merge_kernel
-// combines the partials in fixed order.
+// combines the partials in fixed order (attn_merge2_kernel in the engine: one CTA per (slot, head), two L2 round trips).
 // =================================================================================================
 struct AttnArgs {
     const bf16* Q;
@@ -432,6 +207,8 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const Attn
     constexpr int STAGE_BYTES = 2 * KV_PAGE * HD * 2;
     constexpr int KT = HD / 16;  // k-steps for QK^T; pairs of 8-wide d tiles for PV
 
+    griddep_launch();
+    griddep_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
     const int h = blockIdx.y;
     const int G = a.n_q / a.n_kv;
@@ -612,6 +389,7 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const Attn
             *reinterpret_cast<float2*>(po + d * 8 + 2 * q) = make_float2(o[d][2 * r], o[d][2 * r + 1]);
         if (q == 0) *reinterpret_cast<float2*>(a.part_ml + base * 2) = make_float2(m_run[r], l_run[r]);
     }
+
 }
 
 struct MergeArgs {
@@ -646,4 +424,75 @@ static __global__ void attn_merge_kernel(const MergeArgs a) {
     const float r = acc / L;
     if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * a.hd + d] = __float2bfloat16_rn(r);
     if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * a.hd + d] = r;
+}
+
+// Merge for the engine's decode step: one CTA of 4 warps per (slot, q head).  Every warp reads all (m, l) pairs
+// (one round trip), derives the global max and its weights, then accumulates the partial outputs of chunks
+// i = warp, warp+4, ... in batches of 16 independent loads; the 4 warp sums are added in fixed order.
+template <int HD>
+static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs a) {
+    griddep_launch();
+    griddep_wait();
+    constexpr int VD = HD / 32;
+    __shared__ float sacc[4][HD];
+    __shared__ float sL[4];
+    const int t = blockIdx.y, head = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int len = a.slot_pos[t] + 1;
+    const int sh = (a.cascade && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
+    const int C = a.chunk_keys;
+    const int n = (sh + C - 1) / C + (len - sh + C - 1) / C;
+    const size_t base = ((size_t)t * a.n_q + head) * a.max_chunks;
+    constexpr int MAXB = (136 + 31) / 32;   // MAX_CHUNKS / 32
+    float2 ml[MAXB];
+    float M = -INFINITY;
+#pragma unroll
+    for (int b = 0; b < MAXB; ++b) {
+        const int i = b * 32 + lane;
+        ml[b] = i < n ? *reinterpret_cast<const float2*>(a.part_ml + (base + i) * 2) : make_float2(-INFINITY, 0.f);
+        M = fmaxf(M, ml[b].x);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+    float L = 0.f;
+#pragma unroll
+    for (int b = 0; b < MAXB; ++b) {
+        ml[b].x = exp2f(ml[b].x - M);   // weight of chunk b*32+lane (0 for absent chunks)
+        L += ml[b].y * ml[b].x;
+    }
+    L = warp_sum(L);
+    float acc[VD];
+#pragma unroll
+    for (int v = 0; v < VD; ++v) acc[v] = 0.f;
+    const float* src = a.part_o + base * HD + lane * VD;
+    for (int i0 = warp; i0 < n; i0 += 64) {
+        float pv[16][VD];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int i = i0 + 4 * j;
+#pragma unroll
+            for (int v = 0; v < VD; ++v) pv[j][v] = i < n ? src[(size_t)i * HD + v] : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int i = i0 + 4 * j;
+            float w = 0.f;
+#pragma unroll
+            for (int b = 0; b < MAXB; ++b) {
+                const float wb = __shfl_sync(0xffffffffu, ml[b].x, i & 31);
+                if ((i >> 5) == b) w = wb;
+            }
+#pragma unroll
+            for (int v = 0; v < VD; ++v) acc[v] += pv[j][v] * w;
+        }
+    }
+#pragma unroll
+    for (int v = 0; v < VD; ++v) sacc[warp][lane * VD + v] = acc[v];
+    if (lane == 0) sL[warp] = L;
+    __syncthreads();
+    if (threadIdx.x < HD) {
+        const float r = (sacc[0][threadIdx.x] + sacc[1][threadIdx.x]) + (sacc[2][threadIdx.x] + sacc[3][threadIdx.x]);
+        const float o = r / sL[0];
+        if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * HD + threadIdx.x] = __float2bfloat16_rn(o);
+        if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * HD + threadIdx.x] = o;
+    }
 }

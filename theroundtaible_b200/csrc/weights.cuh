@@ -37,47 +37,80 @@ __host__ __device__ inline float gen_value(unsigned long long key, unsigned long
     return v;
 }
 
-// A fused matrix [rows][cols] is described by up to 3 row segments, each taken from a logical HF
-// tensor [lrows][lcols] starting at (lrow0, lcol0); or by the gate/up 8-row interleave.
+// A fused matrix [rows][cols] is described by a ROW MAP (which logical HF tensor row a physical row holds) and
+// a physical LAYOUT (row-major, or the core-matrix-major "CM" layout of gemv.cuh).
+//   map 0: up to 3 row segments, each taken from a logical tensor [lrows][lcols] starting at (lrow0, lcol0)
+//   map 1: gate/up 8-row interleave (seg[0] = gate, seg[1] = up)
+//   map 2: segments (q, k, v heads) with the RoPE pair permutation inside every head of `hd` rows:
+//          physical row p of a head -> dim (p%16 < 8 ? 8*(p/16) + p%16 : hd/2 + 8*(p/16) + p%16 - 8)
 struct Seg {
     int prow0, nrows;             // physical rows [prow0, prow0+nrows)
     unsigned long long key;
     long long lrow0, lcols, lcol0;
 };
 struct GenDesc {
-    int mode;                     // 0 segments, 1 gate/up interleave (seg[0]=gate, seg[1]=up; lrow0 = first logical row)
+    int map;
     int nseg;
     Seg seg[3];
     int rows, cols;
+    int hd;                       // map 2
+    int cm;                       // 1 = CM layout, 0 = row-major
     float scale, offset;
-    int as_f32;                   // write fp32 (biases) instead of bf16
+    int as_f32;                   // write fp32 (biases; row-major only) instead of bf16
 };
+
+__host__ __device__ inline void map_row(const GenDesc& d, int pr, unsigned long long& key, long long& lrow, long long& lcols,
+                                        long long& lcol0) {
+    if (d.map == 1) {
+        const int tile = pr >> 4, w = pr & 15;
+        const Seg& s = d.seg[w < 8 ? 0 : 1];
+        key = s.key; lrow = s.lrow0 + tile * 8 + (w & 7); lcols = s.lcols; lcol0 = s.lcol0;
+        return;
+    }
+    int si = 0;
+    for (int j = 1; j < d.nseg; ++j)
+        if (pr >= d.seg[j].prow0) si = j;
+    const Seg& s = d.seg[si];
+    int local = pr - s.prow0;
+    if (d.map == 2) {
+        const int head = local / d.hd, p = local % d.hd, j = p >> 4, w = p & 15;
+        local = head * d.hd + (w < 8 ? 8 * j + w : d.hd / 2 + 8 * j + (w - 8));
+    }
+    key = s.key; lrow = s.lrow0 + local; lcols = s.lcols; lcol0 = s.lcol0;
+}
+
+// physical 16-byte piece index -> (row, first column) for the CM layout
+__host__ __device__ inline void cm_piece(long long piece, int cols, int& row, int& col) {
+    const int nkb = cols >> 5;
+    const int r = (int)(piece & 7);
+    const int q = (int)((piece >> 3) & 3);
+    const int h = (int)((piece >> 5) & 1);
+    const long long tk = piece >> 6;          // tile * nkb + kb
+    const int kb = (int)(tk % nkb);
+    const int tile = (int)(tk / nkb);
+    row = tile * 16 + h * 8 + r;
+    col = kb * 32 + q * 8;
+}
 
 static __global__ void gen_kernel(const GenDesc d, void* out) {
     const long long n8 = (long long)d.rows * d.cols / 8;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
-        const long long e = i * 8;
-        const int pr = (int)(e / d.cols), pc = (int)(e % d.cols);
-        unsigned long long key;
-        long long lidx;
-        if (d.mode == 1) {
-            const int tile = pr >> 4, w = pr & 15;
-            const Seg& s = d.seg[w < 8 ? 0 : 1];
-            key = s.key;
-            lidx = (s.lrow0 + tile * 8 + (w & 7)) * s.lcols + s.lcol0 + pc;
+        int pr, pc;
+        if (d.cm) {
+            cm_piece(i, d.cols, pr, pc);
         } else {
-            int si = 0;
-            for (int j = 1; j < d.nseg; ++j)
-                if (pr >= d.seg[j].prow0) si = j;
-            const Seg& s = d.seg[si];
-            key = s.key;
-            lidx = (s.lrow0 + (pr - s.prow0)) * s.lcols + s.lcol0 + pc;
+            pr = (int)((i * 8) / d.cols);
+            pc = (int)((i * 8) % d.cols);
         }
+        unsigned long long key;
+        long long lrow, lcols, lcol0;
+        map_row(d, pr, key, lrow, lcols, lcol0);
+        const long long lidx = lrow * lcols + lcol0 + pc;
         float v[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] = gen_value(key, (unsigned long long)(lidx + j), d.scale, d.offset);
         if (d.as_f32) {
-            float* o = reinterpret_cast<float*>(out) + e;
+            float* o = reinterpret_cast<float*>(out) + i * 8;
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] = __bfloat162float(__float2bfloat16_rn(v[j]));
         } else {
@@ -86,7 +119,7 @@ static __global__ void gen_kernel(const GenDesc d, void* out) {
             p.y = pack_bf16(v[2], v[3]);
             p.z = pack_bf16(v[4], v[5]);
             p.w = pack_bf16(v[6], v[7]);
-            *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(out) + e) = p;
+            *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(out) + i * 8) = p;
         }
     }
 }
@@ -97,6 +130,24 @@ inline void launch_gen(const GenDesc& d, void* out, cudaStream_t st) {
     if (blocks > 148 * 16) blocks = 148 * 16;
     if (blocks < 1) blocks = 1;
     gen_kernel<<<blocks, 256, 0, st>>>(d, out);
+}
+
+// host: CM buffer [rows][cols] (bf16 bits) -> row-major
+inline void cm_to_rowmajor(const uint16_t* cm, uint16_t* rm, int rows, int cols) {
+    const long long n8 = (long long)rows * cols / 8;
+    for (long long p = 0; p < n8; ++p) {
+        int r, c;
+        cm_piece(p, cols, r, c);
+        for (int e = 0; e < 8; ++e) rm[(size_t)r * cols + c + e] = cm[p * 8 + e];
+    }
+}
+inline void rowmajor_to_cm(const uint16_t* rm, uint16_t* cm, int rows, int cols) {
+    const long long n8 = (long long)rows * cols / 8;
+    for (long long p = 0; p < n8; ++p) {
+        int r, c;
+        cm_piece(p, cols, r, c);
+        for (int e = 0; e < 8; ++e) cm[p * 8 + e] = rm[(size_t)r * cols + c + e];
+    }
 }
 
 }  // namespace wgen
