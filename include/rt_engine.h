@@ -186,6 +186,9 @@ RT_API int rt_k_rmsnorm(const float* x, const uint16_t* w, uint16_t* y, int32_t 
 RT_API int rt_k_attention(const uint16_t* q, const uint16_t* k, const uint16_t* v, const int32_t* lens,
                           float* out, int32_t T, int32_t ctx, int32_t n_q, int32_t n_kv, int32_t hd,
                           int32_t shared, int32_t chunk, int32_t device);
+/* Prefill projection on the tcgen05 tensor cores: c[s][n] = sum_k a[s][k] * w[n][k]; a bf16 bits [S][K], w bf16 bits
+ * [N][K] (row-major; converted to the engine's core-matrix-major layout internally), c fp32 [S][N]. */
+RT_API int rt_k_gemm_tc5(const uint16_t* a, const uint16_t* w, float* c, int32_t S, int32_t N, int32_t K, int32_t device);
 /* Time `iters` back-to-back launches of the decode GEMV on an [N][K] bf16 matrix that is re-streamed
  * from HBM (rotating over enough copies to exceed L2); returns mean ms per launch. */
 RT_API int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t device, double* ms_out);

@@ -8,6 +8,7 @@
 #include "engine.cuh"
 #include "kernels.cuh"
 #include "weights.cuh"
+#include "prefill.cuh"
 
 int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi);
 void rt_attn_host_setup();
@@ -392,6 +393,47 @@ int rt_k_attention(const uint16_t* q, const uint16_t* k, const uint16_t* v, cons
         RT_CUDA(cudaGetLastError());
         RT_CUDA(cudaMemcpyAsync(out, dout, (size_t)T * n_q * hd * 4, cudaMemcpyDeviceToHost, st));
         RT_CUDA(cudaStreamSynchronize(st));
+    });
+}
+
+int rt_k_gemm_tc5(const uint16_t* a_bits, const uint16_t* w_bits, float* c, int32_t S, int32_t N, int32_t K, int32_t device) {
+    return guard(nullptr, [&] {
+        RT_REQUIRE(a_bits && w_bits && c, "null argument");
+        RT_REQUIRE(S >= 1 && N > 0 && N % 32 == 0 && K > 0 && K % 64 == 0, "need N % 32 == 0 and K % 64 == 0");
+        Scratch s(device);
+        const int S_pad = cdiv(S, 128) * 128;
+        bf16* da = s.alloc<bf16>((size_t)S_pad * K);
+        bf16* dw = s.alloc<bf16>((size_t)N * K, false);
+        float* dc = s.alloc<float>((size_t)S * N);
+        std::vector<uint16_t> cm((size_t)N * K);
+        wgen::rowmajor_to_cm(w_bits, cm.data(), N, K);
+        RT_CUDA(cudaMemcpyAsync(da, a_bits, (size_t)S * K * 2, cudaMemcpyHostToDevice, s.e.st));
+        RT_CUDA(cudaMemcpyAsync(dw, cm.data(), (size_t)N * K * 2, cudaMemcpyHostToDevice, s.e.st));
+        PfTensorMap ma, mw;
+        pf_make_map_a(&ma, da, S_pad, K);
+        pf_make_map_w(&mw, dw, N, K, PF_BN);
+        Gemm5Args g{};
+        g.S = S; g.N = N; g.K = K; g.out = dc; g.ldo = N;
+        pf_gemm(s.e.st, false, G5_EPI_STORE, ma, mw, g);
+        RT_CUDA(cudaGetLastError());
+        if (const char* it = getenv("RT_GEMM_BENCH_ITERS")) {
+            const int iters = atoi(it);
+            cudaEvent_t e0, e1;
+            RT_CUDA(cudaEventCreate(&e0));
+            RT_CUDA(cudaEventCreate(&e1));
+            RT_CUDA(cudaEventRecord(e0, s.e.st));
+            for (int i = 0; i < iters; ++i) pf_gemm(s.e.st, false, G5_EPI_STORE, ma, mw, g);
+            RT_CUDA(cudaEventRecord(e1, s.e.st));
+            RT_CUDA(cudaStreamSynchronize(s.e.st));
+            float ms = 0.f;
+            RT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            fprintf(stderr, "[gemm bench] S=%d N=%d K=%d: %.2f us per launch, %.1f TFLOP/s\n", S, N, K, 1e3 * ms / iters,
+                    2.0 * S * N * K / (ms / iters * 1e-3) / 1e12);
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+        }
+        RT_CUDA(cudaMemcpyAsync(c, dc, (size_t)S * N * 4, cudaMemcpyDeviceToHost, s.e.st));
+        RT_CUDA(cudaStreamSynchronize(s.e.st));
     });
 }
 

@@ -1,0 +1,85 @@
+// Host side of the tensor-core prefill path: TMA tensor maps and launches of gemm_tc5_kernel.
+#include "prefill.cuh"
+
+#include <cstring>
+
+#include "gemm_tc5.cuh"
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        RT_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (q != cudaDriverEntryPointSuccess || !p) throw RtError(RT_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+template <int BN, int EPI>
+void launch_gemm5(cudaStream_t st, bool pdl, const CUtensorMap& ma, const CUtensorMap& mw, const Gemm5Args& a) {
+    const size_t smem = gemm5_smem_bytes(BN);
+    RT_CUDA(cudaFuncSetAttribute(gemm_tc5_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(cdiv(a.N, BN), cdiv(a.S, G5_BM));
+    cfg.blockDim = dim3(192);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    RT_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc5_kernel<BN, EPI>, ma, mw, a));
+}
+
+}  // namespace
+
+// A operand: bf16 [rows][K] row-major; box = 128 rows x 64 k, 128-byte swizzle
+void pf_make_map_a(PfTensorMap* out, const void* base, int rows, int K) {
+    static_assert(sizeof(PfTensorMap) == sizeof(CUtensorMap), "PfTensorMap must mirror CUtensorMap");
+    RT_REQUIRE(K % G5_BK == 0, "prefill GEMM needs K to be a multiple of 64");
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    const cuuint32_t box[2] = {G5_BK, G5_BM};
+    const cuuint32_t es[2] = {1, 1};
+    const CUresult r = encode_fn()(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+                                   strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw RtError(RT_ERR_CUDA, "cuTensorMapEncodeTiled failed for an activation matrix (code " + std::to_string((int)r) + ")");
+}
+
+// W operand: bf16 CM layout [N/16 tiles][K/32 k-blocks][2 halves][256 elems]; viewed as a 4-D tensor
+// (256 elems, k-block, half, tile) so that one box lands as [tile][half][k-block][256] = the no-swizzle K-major
+// canonical layout with 8-row groups 1024 B apart (BK = 64)
+void pf_make_map_w(PfTensorMap* out, const void* base, int N, int K, int BN) {
+    RT_REQUIRE(K % G5_BK == 0 && N % 16 == 0, "prefill GEMM needs K % 64 == 0 and N % 16 == 0");
+    const cuuint64_t nkb = K / 32;
+    const cuuint64_t dims[4] = {256, nkb, 2, (cuuint64_t)(N / 16)};
+    const cuuint64_t strides[3] = {1024, 512, nkb * 1024};
+    const cuuint32_t box[4] = {256, 2, 2, (cuuint32_t)(BN / 16)};
+    const cuuint32_t es[4] = {1, 1, 1, 1};
+    const CUresult r = encode_fn()(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims,
+                                   strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw RtError(RT_ERR_CUDA, "cuTensorMapEncodeTiled failed for a weight matrix (code " + std::to_string((int)r) + ")");
+}
+
+void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const PfTensorMap& mw, const Gemm5Args& a) {
+    const CUtensorMap& A = reinterpret_cast<const CUtensorMap&>(ma);
+    const CUtensorMap& W = reinterpret_cast<const CUtensorMap&>(mw);
+    RT_REQUIRE(a.K % G5_BK == 0 && a.N % 32 == 0, "prefill GEMM needs K % 64 == 0 and N % 32 == 0");
+    switch (epi) {
+        case G5_EPI_QKV: launch_gemm5<PF_BN, G5_EPI_QKV>(st, pdl, A, W, a); break;
+        case G5_EPI_RESID: launch_gemm5<PF_BN, G5_EPI_RESID>(st, pdl, A, W, a); break;
+        case G5_EPI_SWIGLU: launch_gemm5<PF_BN, G5_EPI_SWIGLU>(st, pdl, A, W, a); break;
+        default: launch_gemm5<PF_BN, G5_EPI_STORE>(st, pdl, A, W, a); break;
+    }
+}

@@ -1,0 +1,39 @@
+// Interface of the tensor-core prefill path (prefill.cu): TMA tensor maps + tcgen05 GEMM launches.
+#pragma once
+#include "../../include/rt_engine.h"
+#include "common.cuh"
+
+constexpr int PF_BN = 256;   // weight rows per CTA tile (TMEM columns of the accumulator)
+
+// opaque mirror of CUtensorMap (128 bytes, 64-byte aligned) so that engine code need not include <cuda.h>
+struct alignas(64) PfTensorMap {
+    unsigned long long opaque[16];
+};
+
+enum { G5_EPI_QKV = 0, G5_EPI_RESID = 1, G5_EPI_SWIGLU = 2, G5_EPI_STORE = 3 };
+
+struct Gemm5Args {
+    int S, N, K;
+    // RESID: out[m*ldo + n] += acc ; STORE: out[m*ldo + n] = acc
+    float* out;
+    int ldo;
+    // SWIGLU
+    bf16* out_bf;
+    int ldob;
+    // QKV
+    const float* bias;
+    const float* cos_t;
+    const float* sin_t;
+    const int* tok_seq;
+    const int* tok_pos;
+    const int* page_table;
+    int pt_stride;
+    bf16* Q;
+    bf16* Kp;
+    bf16* Vp;
+    int n_q, n_kv, hd;
+};
+
+void pf_make_map_a(PfTensorMap* out, const void* base, int rows, int K);
+void pf_make_map_w(PfTensorMap* out, const void* base, int N, int K, int BN);
+void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const PfTensorMap& mw, const Gemm5Args& a);

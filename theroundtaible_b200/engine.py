@@ -54,7 +54,7 @@ class RtModelInfo(C.Structure):
 EXPORTS = ("rt_arch_by_name", "rt_engine_create", "rt_engine_destroy", "rt_last_error", "rt_model_info_get",
            "rt_generate", "rt_generate_batch", "rt_generate_ids", "rt_seq_reset", "rt_step_logits", "rt_result_free",
            "rt_tokenize_chat", "rt_detokenize", "rt_nccl_unique_id", "rt_weights_export", "rt_k_gemv", "rt_k_rmsnorm",
-           "rt_k_attention", "rt_k_gemv_bench", "rt_k_attention_noalloc")
+           "rt_k_attention", "rt_k_gemv_bench", "rt_k_attention_noalloc", "rt_k_gemm_tc5")
 
 _lib = None
 
@@ -104,6 +104,7 @@ def load_library():
                                  C.c_float, i32]
     lib.rt_k_attention.argtypes = [C.POINTER(C.c_uint16)] * 3 + [C.POINTER(i32), C.POINTER(C.c_float)] + [i32] * 8
     lib.rt_k_gemv_bench.argtypes = [i32, i32, i32, i32, i32, C.POINTER(C.c_double)]
+    lib.rt_k_gemm_tc5.argtypes = [C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.POINTER(C.c_float), i32, i32, i32, i32]
     lib.rt_k_attention_noalloc.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     _lib = lib
     return lib
@@ -281,6 +282,16 @@ def k_attention(q_bits, k_bits, v_bits, lens, shared: int = 0, chunk: int = 64, 
     _check(load_library().rt_k_attention(_p(q, C.c_uint16), _p(k, C.c_uint16), _p(v, C.c_uint16), _p(ln, C.c_int32),
                                          _p(out, C.c_float), T, ctx, n_q, n_kv, hd, shared, chunk, device))
     return out
+
+
+def k_gemm_tc5(a_bits: np.ndarray, w_bits: np.ndarray, device: int = 0) -> np.ndarray:
+    S, K = a_bits.shape
+    N = w_bits.shape[0]
+    a = np.ascontiguousarray(a_bits, dtype=np.uint16)
+    w = np.ascontiguousarray(w_bits, dtype=np.uint16)
+    c = np.empty((S, N), dtype=np.float32)
+    _check(load_library().rt_k_gemm_tc5(_p(a, C.c_uint16), _p(w, C.c_uint16), _p(c, C.c_float), S, N, K, device))
+    return c
 
 
 def k_gemv_bench(N: int, K: int, T: int, iters: int = 50, device: int = 0) -> float:
