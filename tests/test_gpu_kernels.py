@@ -26,6 +26,15 @@ def test_gemv_matches_fp32_matmul(N, K, T):
     assert np.abs(y - ref).max() <= tol
 
 
+@pytest.mark.parametrize("S,N,K", [(128, 256, 64), (100, 576, 448), (300, 512, 128), (1, 32, 64), (1216, 3072, 2048), (257, 4096, 8192)])
+def test_tcgen05_prefill_gemm_matches_fp64_matmul(S, N, K):
+    rng = np.random.default_rng(S + N + K)
+    a, w = _rand_bits(rng, (S, K)), _rand_bits(rng, (N, K), 0.05)
+    c = E.k_gemm_tc5(a, w)
+    ref = W.bf16_bits_to_f32(a).astype(np.float64) @ W.bf16_bits_to_f32(w).astype(np.float64).T
+    assert np.abs(c - ref).max() <= 2e-5 * np.abs(ref).max() + 1e-6     # fp32 accumulation in TMEM
+
+
 def test_gemv_is_deterministic_run_to_run():
     rng = np.random.default_rng(5)
     w, x = _rand_bits(rng, (2048, 2048), 0.05), _rand_bits(rng, (8, 2048))

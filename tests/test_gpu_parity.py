@@ -38,6 +38,43 @@ def test_teacher_forced_logits_match_oracle_and_hf(name):
     assert np.median(per_step) <= 3e-3                                # typical error is far below the bar
 
 
+@pytest.mark.parametrize("name", TINY)
+def test_tensor_core_prefill_logits_match_oracle_and_decode_path(name):
+    """mode 1 = tcgen05 GEMMs + flash prefill attention; mode 0 = decode kernels.  Same rounding points, so both must
+    sit within the tolerance of the oracle and of each other; appending in several calls exercises chunk continuation."""
+    g = np.load(os.path.join(GOLD, f"hf_{name}.npz"))
+    a, seed, ids = ARCHS[name], int(g["seed"]), g["ids"]
+    ref = OracleModel(a, seed, max_pos=256).forward(ids, KVState(), round_kv=True, round_act=True).numpy()
+    with E.Engine(name, seed=seed, max_batch=1, max_ctx=256) as eng:
+        eng.seq_reset()
+        got1 = np.concatenate([eng.step_logits(ids[:37], mode=1), eng.step_logits(ids[37:38], mode=1), eng.step_logits(ids[38:], mode=1)])
+        eng.seq_reset()
+        got0 = eng.step_logits(ids, mode=0)
+        eng.seq_reset()
+        mixed = np.concatenate([eng.step_logits(ids[:50], mode=1), eng.step_logits(ids[50:], mode=0)])   # prefill then decode kernels
+    scale = np.abs(ref).max(-1)
+    assert (np.abs(got1 - ref).max(-1) / scale).max() <= REL_TOL
+    assert (np.abs(got1 - got0).max(-1) / scale).max() <= REL_TOL
+    assert (np.abs(mixed - ref).max(-1) / scale).max() <= REL_TOL
+    assert np.median(np.abs(got1 - ref).max(-1) / scale) <= 3e-3
+
+
+def test_prefill_paths_agree_on_generation():
+    a = ARCHS["tiny-qwen-hd128"]
+    rng = np.random.default_rng(77)
+    common = rng.integers(0, a.vocab, 80).tolist()
+    prompts = [common + rng.integers(0, a.vocab, 11 + 3 * i).tolist() for i in range(4)]
+    oracle = OracleModel(a, 21, max_pos=256)
+    with E.Engine("tiny-qwen-hd128", seed=21, max_batch=4, max_ctx=256) as eng:
+        tc = eng.generate_ids(prompts, max_new_tokens=20)
+    with E.Engine("tiny-qwen-hd128", seed=21, max_batch=4, max_ctx=256, flags=E.RT_FLAG_PREFILL_VIA_DECODE) as eng:
+        slab = eng.generate_ids(prompts, max_new_tokens=20)
+    for p, x, y in zip(prompts, tc, slab):
+        _greedy_compare(x.tokens, oracle, p, 20, err_bound=REL_TOL * 2.5)
+        _greedy_compare(y.tokens, oracle, p, 20, err_bound=REL_TOL * 2.5)
+    assert sum(x.tokens == y.tokens for x, y in zip(tc, slab)) >= 3
+
+
 def _greedy_compare(eng_tokens, oracle: OracleModel, prompt, n_new, err_bound):
     """Margin-aware greedy comparison.  Returns number of accepted tie-breaks."""
     kv = KVState()

@@ -1,0 +1,194 @@
+// Causal prefill attention over the paged KV cache (flash-attention style, tensor cores via mma.sync m16n8k16).
+//
+// No reference counterpart (/root/reference/src/adapters/local-llm.ts:159 delegates generation to an external
+// server); SURVEY.md 8(a-K) row "prefill causal attention".
+//
+// The prompt tokens of a chunk are a flat array; a SEGMENT is a run of consecutive tokens of one sequence with
+// consecutive positions.  A work item (one CTA of 4 warps) = (segment piece of <= 64/G tokens, kv head): its 64 rows
+// are (token, q-head-of-the-group) pairs, 16 per warp.  The CTA walks the keys 0 .. last position of its tokens in
+// tiles of 4 pages (64 keys); every warp fetches one page of the tile with cp.async into a swizzled double buffer
+// shared by the CTA, then each warp runs S = QK^T, causal mask, online softmax (exp2 domain), O += PV per page with
+// the same fragment code as the decode kernel.  The chunk's own K/V are already in the cache (the QKV GEMM epilogue
+// wrote them), so there is one code path for old and new keys.
+#pragma once
+#include "kernels.cuh"
+#include "prefill.cuh"
+
+constexpr int PFA_STAGES = 2;
+constexpr int PFA_TILE_PAGES = 4;
+
+template <int HD>
+__global__ void __launch_bounds__(128) attn_prefill_kernel(const PfAttnArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int PAGE_BYTES = 2 * KV_PAGE * HD * 2;              // K + V of one page of one head
+    constexpr int STAGE_BYTES = PFA_TILE_PAGES * PAGE_BYTES;
+    constexpr int KT = HD / 16;
+    griddep_launch();
+    griddep_wait();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+    const int4 wk = a.work[blockIdx.x];
+    const int tok0 = wk.x, ntok = wk.y, seq = wk.z, h = wk.w;
+    const int G = a.n_q / a.n_kv;
+    const int pos0 = a.tok_pos[tok0];
+    const int ldq = a.n_q * HD;
+
+    // rows of this lane: R = warp*16 + g (+8) -> (token R/G, head R%G)
+    int row_tok[2], row_head[2], row_limit[2];
+    bool row_ok[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int R = warp * 16 + g + 8 * i;
+        const int tl = R / G;
+        row_ok[i] = tl < ntok;
+        row_tok[i] = tok0 + (row_ok[i] ? tl : 0);
+        row_head[i] = h * G + (row_ok[i] ? R % G : 0);
+        row_limit[i] = row_ok[i] ? pos0 + tl + 1 : 1;         // keys [0, limit) are visible
+    }
+    // the warp's largest limit (rows of a warp are ordered by token): last valid row of the warp
+    int warp_limit;
+    {
+        const int Rl = min(warp * 16 + 15, ntok * G - 1);
+        warp_limit = Rl >= warp * 16 ? pos0 + Rl / G + 1 : 1;
+    }
+
+    uint32_t qa[KT][4];
+    {
+        const bf16* q0 = a.Q + (size_t)row_tok[0] * ldq + (size_t)row_head[0] * HD;
+        const bf16* q1 = a.Q + (size_t)row_tok[1] * ldq + (size_t)row_head[1] * HD;
+#pragma unroll
+        for (int t = 0; t < KT; ++t) {
+            qa[t][0] = row_ok[0] ? *reinterpret_cast<const uint32_t*>(q0 + 16 * t + 2 * q) : 0u;
+            qa[t][1] = row_ok[1] ? *reinterpret_cast<const uint32_t*>(q1 + 16 * t + 2 * q) : 0u;
+            qa[t][2] = row_ok[0] ? *reinterpret_cast<const uint32_t*>(q0 + 16 * t + 8 + 2 * q) : 0u;
+            qa[t][3] = row_ok[1] ? *reinterpret_cast<const uint32_t*>(q1 + 16 * t + 8 + 2 * q) : 0u;
+        }
+    }
+
+    const uint32_t sbase = smem_u32(smem_raw);
+    const int* pt = a.page_table + (size_t)seq * a.pt_stride;
+    const int n_keys = pos0 + ntok;                                  // keys any row of this CTA may see
+    const int n_pages = (n_keys + KV_PAGE - 1) / KV_PAGE;
+    const int n_tiles = (n_pages + PFA_TILE_PAGES - 1) / PFA_TILE_PAGES;
+    const size_t page_stride = (size_t)a.n_kv * KV_PAGE * HD;
+    const size_t head_off = (size_t)h * KV_PAGE * HD;
+
+    auto issue_tile = [&](int tile) {
+        const int page = tile * PFA_TILE_PAGES + warp;               // warp w fetches page w of the tile
+        if (page < n_pages)
+            attn_issue_page<HD>(sbase + (tile % PFA_STAGES) * STAGE_BYTES + warp * PAGE_BYTES, a.Kp, a.Vp,
+                                (size_t)pt[page] * page_stride + head_off, lane);
+        cp_async_commit();
+    };
+
+    float o[HD / 8][4];
+#pragma unroll
+    for (int d = 0; d < HD / 8; ++d)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[d][i] = 0.f;
+    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+
+    issue_tile(0);
+    for (int tile = 0; tile < n_tiles; ++tile) {
+        if (tile + 1 < n_tiles) issue_tile(tile + 1);
+        else cp_async_commit();
+        cp_async_wait<1>();
+        __syncthreads();
+        const uint32_t stage = sbase + (tile % PFA_STAGES) * STAGE_BYTES;
+#pragma unroll 1
+        for (int pp = 0; pp < PFA_TILE_PAGES; ++pp) {
+            const int kbase = (tile * PFA_TILE_PAGES + pp) * KV_PAGE;
+            if (kbase >= warp_limit) break;                          // causal: nothing left for this warp (warp-uniform)
+            const uint32_t sK = stage + pp * PAGE_BYTES;
+            const uint32_t sV = sK + KV_PAGE * HD * 2;
+            float s[2][4];
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) s[j][i] = 0.f;
+            {
+                const int m = lane >> 3, i8 = lane & 7;
+                const int key = (m >> 1) * 8 + i8;
+#pragma unroll
+                for (int t = 0; t < KT; ++t) {
+                    const int chunk = 2 * t + (m & 1);
+                    uint32_t r0, r1, r2, r3;
+                    ldmatrix_x4(r0, r1, r2, r3, sK + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
+                    mma_bf16_16816(s[0], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r0, r1);
+                    mma_bf16_16816(s[1], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r2, r3);
+                }
+            }
+            float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int key = kbase + j * 8 + 2 * q + (i & 1);
+                    const float v = key < row_limit[i >> 1] ? s[j][i] * a.scale_log2 : -INFINITY;
+                    s[j][i] = v;
+                    mx[i >> 1] = fmaxf(mx[i >> 1], v);
+                }
+            float alpha[2];
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+                mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+                mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+                const float mn = fmaxf(m_run[r], mx[r]);   // finite from page 0 on: key 0 is visible to every row
+                alpha[r] = exp2f(m_run[r] - mn);
+                m_run[r] = mn;
+                l_run[r] *= alpha[r];
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float pv = exp2f(s[j][i] - m_run[i >> 1]);
+                    s[j][i] = pv;
+                    l_run[i >> 1] += pv;
+                }
+#pragma unroll
+            for (int d = 0; d < HD / 8; ++d) {
+                o[d][0] *= alpha[0]; o[d][1] *= alpha[0];
+                o[d][2] *= alpha[1]; o[d][3] *= alpha[1];
+            }
+            const uint32_t pa0 = pack_bf16(s[0][0], s[0][1]), pa1 = pack_bf16(s[0][2], s[0][3]);
+            const uint32_t pa2 = pack_bf16(s[1][0], s[1][1]), pa3 = pack_bf16(s[1][2], s[1][3]);
+            const uint32_t pl0 = pack_bf16(s[0][0] - bf16lo(pa0), s[0][1] - bf16hi(pa0));
+            const uint32_t pl1 = pack_bf16(s[0][2] - bf16lo(pa1), s[0][3] - bf16hi(pa1));
+            const uint32_t pl2 = pack_bf16(s[1][0] - bf16lo(pa2), s[1][1] - bf16hi(pa2));
+            const uint32_t pl3 = pack_bf16(s[1][2] - bf16lo(pa3), s[1][3] - bf16hi(pa3));
+            {
+                const int m = lane >> 3, i8 = lane & 7;
+                const int key = (m & 1) * 8 + i8;
+#pragma unroll
+                for (int dp = 0; dp < KT; ++dp) {
+                    const int chunk = 2 * dp + (m >> 1);
+                    uint32_t r0, r1, r2, r3;
+                    ldmatrix_x4_trans(r0, r1, r2, r3, sV + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
+                    mma_bf16_16816(o[2 * dp], pa0, pa1, pa2, pa3, r0, r1);
+                    mma_bf16_16816(o[2 * dp], pl0, pl1, pl2, pl3, r0, r1);
+                    mma_bf16_16816(o[2 * dp + 1], pa0, pa1, pa2, pa3, r2, r3);
+                    mma_bf16_16816(o[2 * dp + 1], pl0, pl1, pl2, pl3, r2, r3);
+                }
+            }
+        }
+        __syncthreads();   // everyone is done with this stage before it is refilled
+    }
+
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+        l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        if (!row_ok[r]) continue;
+        const float inv = 1.0f / l_run[r];
+        bf16* dst = a.out + (size_t)row_tok[r] * ldq + (size_t)row_head[r] * HD;
+#pragma unroll
+        for (int d = 0; d < HD / 8; ++d)
+            *reinterpret_cast<uint32_t*>(dst + d * 8 + 2 * q) = pack_bf16(o[d][2 * r] * inv, o[d][2 * r + 1] * inv);
+    }
+}
+
+constexpr size_t pfa_smem_bytes(int hd) { return (size_t)PFA_STAGES * PFA_TILE_PAGES * 2 * KV_PAGE * hd * 2; }

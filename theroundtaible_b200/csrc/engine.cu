@@ -351,6 +351,34 @@ void engine_init(rt_engine* e) {
     e->cta_max = zalloc_f((size_t)e->lm_ctas * 32);
     e->cta_idx = dalloc<int>(e, (size_t)e->lm_ctas * 32);
     e->logits = zalloc_f((size_t)MAX_SLOTS * e->vocab_l);
+
+    // tensor-core prefill path
+    e->pf_cap = std::min(2048, cdiv(std::min(c.max_ctx * c.max_batch, 1 << 20), 128) * 128);
+    const int bt = std::max(1, 64 / e->G);
+    e->pf_work_cap = (e->pf_cap / bt + 2 * e->n_seq + 2) * e->nkv_l;
+    e->pf_x = zalloc_f((size_t)e->pf_cap * e->H);
+    e->pf_xn = zalloc_b((size_t)e->pf_cap * e->H);
+    e->pf_q = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
+    e->pf_attn = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
+    e->pf_act = zalloc_b((size_t)e->pf_cap * e->F_l);
+    e->pf_tok = dalloc<int>(e, e->pf_cap);
+    e->pf_seq = dalloc<int>(e, e->pf_cap);
+    e->pf_pos = dalloc<int>(e, e->pf_cap);
+    e->pf_work = dalloc<int4>(e, e->pf_work_cap);
+    RT_CUDA(cudaMallocHost(&e->pf_host, ((size_t)3 * e->pf_cap + (size_t)4 * e->pf_work_cap) * sizeof(int)));
+    e->pf_ok = e->H % 64 == 0 && (e->nq_l * e->hd) % 64 == 0 && e->F_l % 64 == 0;
+    if (e->pf_ok) {
+        pf_make_map_a(&e->map_xn, e->pf_xn, e->pf_cap, e->H);
+        pf_make_map_a(&e->map_attn, e->pf_attn, e->pf_cap, e->nq_l * e->hd);
+        pf_make_map_a(&e->map_act, e->pf_act, e->pf_cap, e->F_l);
+        e->map_w.resize((size_t)4 * e->L);
+        for (int l = 0; l < e->L; ++l) {
+            pf_make_map_w(&e->map_w[4 * l + 0], e->layers[l].wqkv, e->qkv_rows, e->H, PF_BN);
+            pf_make_map_w(&e->map_w[4 * l + 1], e->layers[l].wo, e->H, e->nq_l * e->hd, PF_BN);
+            pf_make_map_w(&e->map_w[4 * l + 2], e->layers[l].wgu, 2 * e->F_l, e->H, PF_BN);
+            pf_make_map_w(&e->map_w[4 * l + 3], e->layers[l].wdown, e->H, e->F_l, PF_BN);
+        }
+    }
     RT_CUDA(cudaStreamSynchronize(e->st));
 }
 
@@ -361,6 +389,7 @@ void engine_free(rt_engine* e) {
     for (void* p : e->allocs) cudaFree(p);
     if (e->h_page_table) cudaFreeHost(e->h_page_table);
     if (e->h_stage) cudaFreeHost(e->h_stage);
+    if (e->pf_host) cudaFreeHost(e->pf_host);
     for (auto& ev : e->ev)
         if (ev) cudaEventDestroy(ev);
     if (e->st) cudaStreamDestroy(e->st);
@@ -546,6 +575,121 @@ static void prefill_via_slabs(rt_engine* e, const std::vector<int>& tok, const s
     }
 }
 
+// ===================================================================================================
+// Tensor-core prefill: a flat stream of prompt tokens (token, seq, pos) in chunks of <= pf_cap.  Per layer:
+//   tcgen05 GEMM [QKV + bias + RoPE + KV pages] -> causal flash attention over the pages -> tcgen05 GEMM [O + residual]
+//   -> RMSNorm -> tcgen05 GEMM [gate/up + SwiGLU] -> tcgen05 GEMM [down + residual] -> RMSNorm.
+// Rows whose `want_first` is a sequence id get their next token from the decode lm_head kernel.
+// With logits_out != null (teacher forcing) the logits of every token are produced instead.
+// ===================================================================================================
+static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std::vector<int>& seq, const std::vector<int>& pos,
+                           const std::vector<int>& want_first, const StepOpts& base, double t0, uint64_t deadline_ms,
+                           float* logits_out = nullptr) {
+    const int n = (int)tok.size(), H = e->H, hd = e->hd;
+    const int BT = std::max(1, 64 / e->G);
+    const bool pdl = e->use_pdl;
+    for (int c0 = 0; c0 < n; c0 += e->pf_cap) {
+        const int S = std::min(e->pf_cap, n - c0);
+        RT_CUDA(cudaStreamSynchronize(e->st));     // staging buffers are free again
+        int* ht = e->pf_host;
+        int* hs = ht + e->pf_cap;
+        int* hp = hs + e->pf_cap;
+        int4* hw = reinterpret_cast<int4*>(hp + e->pf_cap);
+        memcpy(ht, tok.data() + c0, S * sizeof(int));
+        memcpy(hs, seq.data() + c0, S * sizeof(int));
+        memcpy(hp, pos.data() + c0, S * sizeof(int));
+        int n_items = 0;
+        for (int s0 = 0; s0 < S;) {
+            int s1 = s0 + 1;
+            while (s1 < S && hs[s1] == hs[s0] && hp[s1] == hp[s1 - 1] + 1) ++s1;
+            for (int b = s0; b < s1; b += BT)
+                for (int kh = 0; kh < e->nkv_l; ++kh) {
+                    if (n_items >= e->pf_work_cap) throw RtError(RT_ERR_INVALID, "prefill work list overflow");
+                    hw[n_items++] = make_int4(b, std::min(BT, s1 - b), hs[s0], kh);
+                }
+            s0 = s1;
+        }
+        RT_CUDA(cudaMemcpyAsync(e->pf_tok, ht, S * sizeof(int), cudaMemcpyHostToDevice, e->st));
+        RT_CUDA(cudaMemcpyAsync(e->pf_seq, hs, S * sizeof(int), cudaMemcpyHostToDevice, e->st));
+        RT_CUDA(cudaMemcpyAsync(e->pf_pos, hp, S * sizeof(int), cudaMemcpyHostToDevice, e->st));
+        RT_CUDA(cudaMemcpyAsync(e->pf_work, hw, (size_t)n_items * sizeof(int4), cudaMemcpyHostToDevice, e->st));
+
+        launch_pdl(e, embed_norm_kernel, dim3(S), dim3(256), 0, (const bf16*)e->embed, (const int*)e->pf_tok, e->pf_x,
+                   (const bf16*)e->layers[0].norm1, e->pf_xn, H, e->vocab, e->cfg.rms_eps);
+        for (int l = 0; l < e->L; ++l) {
+            const LayerW& w = e->layers[l];
+            bf16* kp = e->kpool + (size_t)l * e->layer_pool_elems;
+            bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
+            Gemm5Args g{};
+            g.S = S; g.N = e->qkv_rows; g.K = H; g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t;
+            g.tok_seq = e->pf_seq; g.tok_pos = e->pf_pos; g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq;
+            g.Q = e->pf_q; g.Kp = kp; g.Vp = vp; g.n_q = e->nq_l; g.n_kv = e->nkv_l; g.hd = hd;
+            pf_gemm(e->st, pdl, G5_EPI_QKV, e->map_xn, e->map_w[4 * l + 0], g);
+            e->launches++;
+
+            PfAttnArgs a{};
+            a.Q = e->pf_q; a.Kp = kp; a.Vp = vp; a.page_table = e->d_page_table; a.pt_stride = e->max_pages_per_seq;
+            a.tok_pos = e->pf_pos; a.work = e->pf_work; a.n_q = e->nq_l; a.n_kv = e->nkv_l;
+            a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd)); a.out = e->pf_attn;
+            pf_attention(e->st, pdl, hd, n_items, a);
+            e->launches++;
+
+            Gemm5Args go{};
+            go.S = S; go.N = H; go.K = e->nq_l * hd; go.out = e->pf_x; go.ldo = H;
+            pf_gemm(e->st, pdl, G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
+            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, nullptr, w.norm2, e->pf_xn, H, H, e->cfg.rms_eps);
+            e->launches += 2;
+
+            Gemm5Args gu{};
+            gu.S = S; gu.N = 2 * e->F_l; gu.K = H; gu.out_bf = e->pf_act; gu.ldob = e->F_l;
+            pf_gemm(e->st, pdl, G5_EPI_SWIGLU, e->map_xn, e->map_w[4 * l + 2], gu);
+            Gemm5Args gd{};
+            gd.S = S; gd.N = H; gd.K = e->F_l; gd.out = e->pf_x; gd.ldo = H;
+            pf_gemm(e->st, pdl, G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
+            const bf16* nw = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;
+            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, nullptr, nw, e->pf_xn, H, H, e->cfg.rms_eps);
+            e->launches += 3;
+        }
+        RT_CUDA(cudaGetLastError());
+
+        // next tokens (or all logits) through the decode lm_head kernel, <= 32 rows at a time
+        auto lm_head_rows = [&](const std::vector<int>& rows, bool sample, bool store) {
+            const int T = (int)rows.size();
+            for (int j = 0; j < T; ++j)
+                RT_CUDA(cudaMemcpyAsync(e->xn + (size_t)j * H, e->pf_xn + (size_t)rows[j] * H, (size_t)H * sizeof(bf16),
+                                        cudaMemcpyDeviceToDevice, e->st));
+            GemvArgs gl{};
+            gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = H; gl.T = T; gl.X = e->xn; gl.ldx = H;
+            gl.logits = store ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
+            gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
+            gl.inv_temp = base.inv_temp; gl.seed = base.seed; gl.step_ptr = e->d_step;
+            if (sample) { gl.next_tok = e->d_next_tok; gl.done_counter = e->done_counter; }
+            gemv_dispatch<EPI_LOGITS>(e, gl);
+        };
+        if (logits_out) {
+            for (int r0 = 0; r0 < S; r0 += MAX_SLOTS) {
+                std::vector<int> rows;
+                for (int r = r0; r < std::min(S, r0 + MAX_SLOTS); ++r) rows.push_back(r);
+                lm_head_rows(rows, false, true);
+                RT_CUDA(cudaMemcpyAsync(logits_out + (size_t)(c0 + r0) * e->vocab_l, e->logits, rows.size() * (size_t)e->vocab_l * sizeof(float),
+                                        cudaMemcpyDeviceToHost, e->st));
+                RT_CUDA(cudaStreamSynchronize(e->st));
+            }
+        } else {
+            std::vector<int> rows, seqs;
+            for (int i = 0; i < S; ++i)
+                if (want_first[c0 + i] >= 0) { rows.push_back(i); seqs.push_back(want_first[c0 + i]); }
+            if (!rows.empty()) {
+                lm_head_rows(rows, true, false);
+                for (size_t j = 0; j < rows.size(); ++j)
+                    RT_CUDA(cudaMemcpyAsync(e->d_out_tokens + (size_t)seqs[j] * e->max_out, e->d_next_tok + j, sizeof(int),
+                                            cudaMemcpyDeviceToDevice, e->st));
+            }
+        }
+        check_deadline(t0, deadline_ms);
+    }
+}
+
 static void ensure_graph(rt_engine* e, const StepOpts& o) {
     const StepOpts& g = e->graph_opts;
     if (e->graph_exec && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks &&
@@ -637,7 +781,10 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
                 tok.push_back(prompts[i][p]); seq.push_back(i); pos.push_back(p);
                 want.push_back(p == lens[i] - 1 ? i : -1);
             }
-        prefill_via_slabs(e, tok, seq, pos, want, base, t0, deadline_ms);
+        if (e->pf_ok && !(e->cfg.flags & RT_FLAG_PREFILL_VIA_DECODE) && (int)tok.size() >= 32)
+            prefill_tensor(e, tok, seq, pos, want, base, t0, deadline_ms);
+        else
+            prefill_via_slabs(e, tok, seq, pos, want, base, t0, deadline_ms);
     }
     RT_CUDA(cudaEventRecord(e->ev[1], e->st));
 
@@ -743,7 +890,8 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
 // ===================================================================================================
 void engine_step_logits(rt_engine* e, const int32_t* ids, int n, int mode, float* logits_out) {
     RT_REQUIRE(n >= 1, "n must be >= 1");
-    RT_REQUIRE(mode == 0, "only mode 0 (decode kernels) is available in this build");
+    RT_REQUIRE(mode == 0 || mode == 1, "mode must be 0 (decode kernels) or 1 (tensor-core prefill kernels)");
+    RT_REQUIRE(mode == 0 || e->pf_ok, "the tensor-core prefill path needs hidden, n_q*head_dim and ffn to be multiples of 64");
     RT_CUDA(cudaSetDevice(e->dev));
     if (!e->scratch_active) {
         engine_reset_sequences(e);
@@ -759,6 +907,13 @@ void engine_step_logits(rt_engine* e, const int32_t* ids, int n, int mode, float
     StepOpts o{};
     plan_chunks(p0 + n, 0, o);
     o.store_logits = true;
+    if (mode == 1) {
+        std::vector<int> tok(ids, ids + n), seq(n, 0), pos(n), want(n, -1);
+        for (int i = 0; i < n; ++i) pos[i] = p0 + i;
+        prefill_tensor(e, tok, seq, pos, want, o, now_ms(), 0, logits_out);
+        e->seq_len[0] = p0 + n;
+        return;
+    }
     for (int s0 = 0; s0 < n; s0 += MAX_SLOTS) {
         const int T = std::min(MAX_SLOTS, n - s0);
         int tok[MAX_SLOTS], seq[MAX_SLOTS], pos[MAX_SLOTS];

@@ -5,6 +5,7 @@
 #include <vector>
 #include "../../include/rt_engine.h"
 #include "common.cuh"
+#include "prefill.cuh"
 
 constexpr int MAX_SLOTS = 32;      // token slots per forward step (decode: knights; slab prefill: tokens)
 constexpr int MAX_CHUNKS = 136;    // attention partials per (slot, head): <= 64 shared + <= 64 own (+ rounding)
@@ -74,6 +75,17 @@ struct rt_engine {
     float* cta_max = nullptr;
     int* cta_idx = nullptr;
     int lm_ctas = 0;
+
+    // tensor-core prefill path: activations of one chunk of <= pf_cap prompt tokens, TMA tensor maps
+    int pf_cap = 0, pf_work_cap = 0;
+    bool pf_ok = false;
+    float* pf_x = nullptr;
+    bf16 *pf_xn = nullptr, *pf_q = nullptr, *pf_attn = nullptr, *pf_act = nullptr;
+    int *pf_tok = nullptr, *pf_seq = nullptr, *pf_pos = nullptr;
+    int4* pf_work = nullptr;
+    int* pf_host = nullptr;        // pinned staging: tok, seq, pos (pf_cap each) + work items
+    PfTensorMap map_xn{}, map_attn{}, map_act{};
+    std::vector<PfTensorMap> map_w;   // per layer: qkv, o, gate/up, down
 
     // cached decode graph
     cudaGraphExec_t graph_exec = nullptr;

@@ -3,6 +3,7 @@
 
 #include <cstring>
 
+#include "attn_prefill.cuh"
 #include "gemm_tc5.cuh"
 
 namespace {
@@ -82,4 +83,29 @@ void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const Pf
         case G5_EPI_SWIGLU: launch_gemm5<PF_BN, G5_EPI_SWIGLU>(st, pdl, A, W, a); break;
         default: launch_gemm5<PF_BN, G5_EPI_STORE>(st, pdl, A, W, a); break;
     }
+}
+
+template <int HD>
+static void launch_pfa(cudaStream_t st, bool pdl, int n_items, const PfAttnArgs& a) {
+    const size_t smem = pfa_smem_bytes(HD);
+    RT_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(n_items);
+    cfg.blockDim = dim3(128);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    RT_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_kernel<HD>, a));
+}
+
+void pf_attention(cudaStream_t st, bool pdl, int hd, int n_items, const PfAttnArgs& a) {
+    if (n_items <= 0) return;
+    if (hd == 128) launch_pfa<128>(st, pdl, n_items, a);
+    else if (hd == 64) launch_pfa<64>(st, pdl, n_items, a);
+    else if (hd == 32) launch_pfa<32>(st, pdl, n_items, a);
+    else throw RtError(RT_ERR_INVALID, "head_dim must be 32, 64 or 128");
 }

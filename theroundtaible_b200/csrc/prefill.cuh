@@ -34,6 +34,20 @@ struct Gemm5Args {
     int n_q, n_kv, hd;
 };
 
+struct PfAttnArgs {
+    const bf16* Q;          // [S][n_q*hd] (RoPE applied, bf16)
+    const bf16* Kp;
+    const bf16* Vp;
+    const int* page_table;
+    int pt_stride;
+    const int* tok_pos;     // [S]
+    const int4* work;       // {first token (flat), n tokens, sequence, kv head}
+    int n_q, n_kv;
+    float scale_log2;
+    bf16* out;              // [S][n_q*hd]
+};
+
+void pf_attention(cudaStream_t st, bool pdl, int hd, int n_items, const PfAttnArgs& a);
 void pf_make_map_a(PfTensorMap* out, const void* base, int rows, int K);
 void pf_make_map_w(PfTensorMap* out, const void* base, int N, int K, int BN);
 void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const PfTensorMap& mw, const Gemm5Args& a);
