@@ -34,6 +34,9 @@ WORKLOADS = {
     "config2": dict(model="llama-3.2-1b", knights=3, shared=1024, own=64, new_tokens=512, max_ctx=2048, seed_idx=2),
     # BASELINE.json configs[2]: 5 knights, Llama-3.1-8B, 8k shared transcript prefix
     "config3": dict(model="llama-3.1-8b", knights=5, shared=8192, own=128, new_tokens=512, max_ctx=9216, seed_idx=3),
+    # BASELINE.json configs[3]/[4]: tensor parallel (run with --tp N under torchrun); layer count may be truncated with --layers
+    "config4": dict(model="qwen2.5-32b", knights=8, shared=2048, own=128, new_tokens=256, max_ctx=2560, seed_idx=4),
+    "config5": dict(model="llama-3.1-70b", knights=8, shared=16384, own=128, new_tokens=256, max_ctx=16896, seed_idx=5),
     # smoke-sized
     "tiny": dict(model="tiny-llama", knights=3, shared=64, own=8, new_tokens=32, max_ctx=256, seed_idx=0),
 }
@@ -201,9 +204,21 @@ def run_b200(args, w):
             torch.distributed.barrier()
         torch.cuda.synchronize()
 
-    eng = E.Engine(w["model"], seed=0, device=local, max_batch=max(w["knights"], 1), max_ctx=w["max_ctx"])
-    prompts = synth_prompts(w, eng.vocab, rank)
-    texts = synth_text_prompts(w, rank)
+    tp = args.tp if args.tp > 1 else 1
+    model = w["model"] + (f"@L{args.layers}" if args.layers else "")
+    if tp > 1:
+        assert world == tp, "--tp N needs torchrun with N ranks"
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(E.nccl_unique_id()), dtype=torch.uint8))
+        torch.distributed.broadcast(idt, 0)
+        eng = E.Engine(model, seed=0, device=local, max_batch=max(w["knights"], 1), max_ctx=w["max_ctx"], tp_rank=rank,
+                       tp_size=tp, nccl_id=bytes(idt.cpu().numpy().tobytes()))
+    else:
+        eng = E.Engine(model, seed=0, device=local, max_batch=max(w["knights"], 1), max_ctx=w["max_ctx"])
+    replicas = 1 if tp > 1 else world
+    prompts = synth_prompts(w, eng.vocab, 0 if tp > 1 else rank)
+    texts = synth_text_prompts(w, 0 if tp > 1 else rank)
     adapter = B200LocalLlmAdapter(f"b200://{local}", w["model"], "bench", max_new_tokens=w["new_tokens"], ignore_eos=True,
                                   engine=eng)
     nt = w["new_tokens"]
@@ -270,10 +285,10 @@ def run_b200(args, w):
         achieved = bytes_step / (step_ms * 1e-3) / 1e9
         # the dominant kernel alone: the gate/up projection stream of one layer, re-streamed from HBM
         cfg = eng.cfg
-        gu_ms = E.k_gemv_bench(2 * cfg.ffn, cfg.hidden, w["knights"], iters=200, device=local)
-        gu_gbs = 2 * cfg.ffn * cfg.hidden * 2 / (gu_ms * 1e-3) / 1e9
+        gu_ms = E.k_gemv_bench(2 * cfg.ffn // tp, cfg.hidden, w["knights"], iters=200, device=local)
+        gu_gbs = 2 * (cfg.ffn // tp) * cfg.hidden * 2 / (gu_ms * 1e-3) / 1e9
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and tp == 1 and info.n_params < 3e9:
             try:
                 cpu = cpu_baseline_leg(w)
             except Exception as ex:  # noqa: BLE001
@@ -281,13 +296,14 @@ def run_b200(args, w):
         h2d = sum(len(t.encode()) + 3 for t in texts) * 4 + 4 * 96 * ((sum(len(t.encode()) + 3 for t in texts) + 31) // 32)
         d2h = w["knights"] * nt * 4
         line = {
-            "metric": "decode_tok_per_s", "value": world * toks / (dec_ms_m * 1e-3), "unit": "tok/s", "n_gpus": world,
+            "metric": "decode_tok_per_s", "value": replicas * toks / (dec_ms_m * 1e-3), "unit": "tok/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall_ms_m / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "scaling": "strong" if tp > 1 else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": (f"{args.workload}: {w['knights']} knights, {w['model']} bf16, {w['shared']} shared + "
                                     f"{w['own']} own prompt tokens, {nt} new tokens per knight, greedy, BATCH round"),
                        "weights": "seeded random-init (Irwin-Hall approx of N(0,0.02)), bf16", "l2": "weights (2.47 GB+) exceed the 126 MB L2",
-                       "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
+                       "parallelism": (f"tp{tp}" if tp > 1 else (f"replicas x{world}" if world > 1 else "single GPU")),
+                       "model": model,
                        "prefill_ms_per_round": pre_ms_m / args.steps, "decode_ms_per_token_step": step_ms},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "of": "decode step (one CUDA-graph launch)",
@@ -295,7 +311,7 @@ def run_b200(args, w):
                          "dominant_kernel": {"name": "gemv_tc_kernel (gate/up projection)", "ms": gu_ms, "achieved": gu_gbs,
                                              "frac": gu_gbs / peak}},
             "cpu_baseline": cpu,
-            "e2e": {"value": world * e2e_tokens / (e2e_ms_m * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": h2d,
+            "e2e": {"value": replicas * e2e_tokens / (e2e_ms_m * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_round": e2e_ms_m / args.steps,
                     "note": "generated tokens / wall time of adapter.execute_round (tokenise, prefill, decode, detokenise)"},
             "gpu_launches": launches, "clocks": clocks,
@@ -317,6 +333,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tp", type=int, default=1, help="tensor-parallel degree (= torchrun ranks); default: replicas")
+    ap.add_argument("--layers", type=int, default=0, help="truncate the model depth (stated in config.model)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     w = dict(WORKLOADS[args.workload])

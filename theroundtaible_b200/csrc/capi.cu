@@ -212,9 +212,10 @@ int64_t rt_detokenize(const int32_t* ids, int32_t n, char* out, int64_t cap) {
 }
 
 int rt_nccl_unique_id(void* out128) {
-    (void)out128;
-    g_err = "invalid argument: tensor parallelism is not available in this build";
-    return RT_ERR_NCCL;
+    return guard(nullptr, [&] {
+        RT_REQUIRE(out128 != nullptr, "null argument");
+        tp_unique_id(out128);
+    });
 }
 
 int rt_weights_export(rt_engine* e, int32_t tensor_id, uint16_t* out, int64_t n_elems) {

@@ -268,7 +268,8 @@ void engine_init(rt_engine* e) {
     RT_REQUIRE(c.max_batch >= 1 && c.max_batch <= 8, "max_batch must be 1..8");
     RT_REQUIRE(c.max_ctx >= 32, "max_ctx must be >= 32");
     RT_REQUIRE(c.tp_size >= 1 && c.tp_rank >= 0 && c.tp_rank < c.tp_size, "bad tp_rank/tp_size");
-    RT_REQUIRE(c.tp_size == 1, "tensor parallelism is not available in this build");
+    RT_REQUIRE(c.n_q % c.tp_size == 0 && c.n_kv % c.tp_size == 0 && c.ffn % (8 * c.tp_size) == 0 && c.vocab % (16 * c.tp_size) == 0,
+               "n_q, n_kv, ffn/8 and vocab/16 must be divisible by tp_size");
     RT_REQUIRE(c.weights_path == nullptr, "safetensors loading is not available in this build");
 
     int ndev = 0;
@@ -286,6 +287,7 @@ void engine_init(rt_engine* e) {
     RT_CUDA(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (auto& ev : e->ev) RT_CUDA(cudaEventCreate(&ev));
     rt_attn_host_setup();
+    if (c.tp_size > 1) e->tp = tp_init(c.tp_rank, c.tp_size, c.nccl_id);
 
     e->L = c.layers; e->H = c.hidden; e->hd = c.head_dim; e->nq = c.n_q; e->nkv = c.n_kv; e->F = c.ffn; e->vocab = c.vocab;
     e->nq_l = e->nq / c.tp_size; e->nkv_l = e->nkv / c.tp_size; e->F_l = e->F / c.tp_size; e->vocab_l = e->vocab / c.tp_size;
@@ -352,6 +354,11 @@ void engine_init(rt_engine* e) {
     e->cta_idx = dalloc<int>(e, (size_t)e->lm_ctas * 32);
     e->logits = zalloc_f((size_t)MAX_SLOTS * e->vocab_l);
 
+    if (c.tp_size > 1) {
+        e->loc_best = zalloc_f(64);
+        e->all_best = zalloc_f((size_t)64 * c.tp_size);
+    }
+
     // tensor-core prefill path
     e->pf_cap = std::min(2048, cdiv(std::min(c.max_ctx * c.max_batch, 1 << 20), 128) * 128);
     const int bt = std::max(1, 64 / e->G);
@@ -361,6 +368,7 @@ void engine_init(rt_engine* e) {
     e->pf_q = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
     e->pf_attn = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
     e->pf_act = zalloc_b((size_t)e->pf_cap * e->F_l);
+    if (c.tp_size > 1) e->pf_delta = zalloc_f((size_t)e->pf_cap * e->H);
     e->pf_tok = dalloc<int>(e, e->pf_cap);
     e->pf_seq = dalloc<int>(e, e->pf_cap);
     e->pf_pos = dalloc<int>(e, e->pf_cap);
@@ -386,6 +394,8 @@ void engine_free(rt_engine* e) {
     if (e->dev >= 0) cudaSetDevice(e->dev);
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    tp_destroy(e->tp);
+    e->tp = nullptr;
     for (void* p : e->allocs) cudaFree(p);
     if (e->h_page_table) cudaFreeHost(e->h_page_table);
     if (e->h_stage) cudaFreeHost(e->h_stage);
@@ -448,6 +458,37 @@ void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* p
     RT_CUDA(cudaMemcpyAsync(e->d_pos, e->h_stage + 2 * MAX_SLOTS, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
 }
 
+// lm_head over the T rows of e->xn + sampling.  Single GPU: the projection's last CTA picks the winners and advances
+// the decode state.  Tensor parallel: vocab-parallel local winners -> all-gather -> tp_pick_kernel on every rank.
+static void lm_head_and_sample(rt_engine* e, int T, bool sample, bool advance, bool store_logits, float inv_temp,
+                               unsigned long long seed) {
+    GemvArgs gl{};
+    gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = e->H; gl.T = T; gl.X = e->xn; gl.ldx = e->H;
+    gl.logits = store_logits ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
+    gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
+    gl.inv_temp = inv_temp; gl.seed = seed; gl.step_ptr = e->d_step;
+    const bool tp = e->tp != nullptr;
+    if (sample) {
+        gl.done_counter = e->done_counter;
+        if (tp) {
+            gl.next_val = e->loc_best;
+            gl.next_tok = reinterpret_cast<int*>(e->loc_best) + 32;
+        } else {
+            gl.next_tok = e->d_next_tok;
+            if (advance) { gl.tok = e->d_tok; gl.pos = e->d_pos; gl.out_tokens = e->d_out_tokens; gl.max_out = e->max_out; gl.step_w = e->d_step; }
+        }
+    }
+    gemv_dispatch<EPI_LOGITS>(e, gl);
+    if (sample && tp) {
+        tp_allgather_bytes(e->tp, e->loc_best, e->all_best, 64 * sizeof(float), e->st);
+        TpPickArgs p{};
+        p.all_val = e->all_best; p.tp = e->cfg.tp_size; p.T = T; p.next_tok = e->d_next_tok;
+        if (advance) { p.tok = e->d_tok; p.pos = e->d_pos; p.out_tokens = e->d_out_tokens; p.max_out = e->max_out; p.step_w = e->d_step; }
+        launch_pdl(e, tp_pick_kernel, dim3(1), dim3(32), 0, p);
+        e->launches++;   // the NCCL kernel
+    }
+}
+
 // ===================================================================================================
 // One decoder pass over T token slots (slot = (token, sequence, position) held on the device).
 // 5 kernels per layer:  [norm + QKV + bias + RoPE + KV append] -> [attention + merge] -> [O-proj + residual]
@@ -495,9 +536,18 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
 
         GemvArgs go{};
         go.W = w.wo; go.X = e->attn_bf; go.N = H; go.K = e->nq_l * hd; go.ldx = e->nq_l * hd; go.T = T;
-        go.out = e->x; go.ldo = H;
-        go.norm_w = w.norm2; go.xn_out = e->xn; go.done_counter = e->done_counter; go.eps = e->cfg.rms_eps;
-        if (!(skip & 8)) gemv_dispatch<EPI_RESID>(e, go);
+        if (!e->tp) {
+            go.out = e->x; go.ldo = H;
+            go.norm_w = w.norm2; go.xn_out = e->xn; go.done_counter = e->done_counter; go.eps = e->cfg.rms_eps;
+            if (!(skip & 8)) gemv_dispatch<EPI_RESID>(e, go);
+        } else {
+            // row-parallel: partial sums -> all-reduce over NVLink -> residual add + RMSNorm
+            go.out = e->delta; go.ldo = H;
+            gemv_dispatch<EPI_STORE>(e, go);
+            tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
+            rmsnorm_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, w.norm2, e->xn, H, H, e->cfg.rms_eps);
+            e->launches += 2;
+        }
 
         GemvArgs gu{};
         gu.W = w.wgu; gu.N = 2 * e->F_l; gu.K = H; gu.T = T; gu.X = e->xn; gu.ldx = H;
@@ -506,26 +556,21 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
 
         GemvArgs gd{};
         gd.W = w.wdown; gd.X = e->act_bf; gd.N = H; gd.K = e->F_l; gd.ldx = e->F_l; gd.T = T;
-        gd.out = e->x; gd.ldo = H;
-        gd.norm_w = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;   // feeds the next layer's QKV, or the lm_head
-        gd.xn_out = e->xn; gd.done_counter = e->done_counter; gd.eps = e->cfg.rms_eps;
-        if (!(skip & 32)) gemv_dispatch<EPI_RESID>(e, gd);
+        const bf16* next_norm = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;   // feeds the next layer's QKV, or the lm_head
+        if (!e->tp) {
+            gd.out = e->x; gd.ldo = H;
+            gd.norm_w = next_norm; gd.xn_out = e->xn; gd.done_counter = e->done_counter; gd.eps = e->cfg.rms_eps;
+            if (!(skip & 32)) gemv_dispatch<EPI_RESID>(e, gd);
+        } else {
+            gd.out = e->delta; gd.ldo = H;
+            gemv_dispatch<EPI_STORE>(e, gd);
+            tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
+            rmsnorm_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, next_norm, e->xn, H, H, e->cfg.rms_eps);
+            e->launches += 2;
+        }
     }
 
-    if (o.sample || o.store_logits) {
-        GemvArgs gl{};
-        gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = H; gl.T = T; gl.X = e->xn; gl.ldx = H;
-        gl.logits = o.store_logits ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
-        gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
-        gl.inv_temp = o.inv_temp; gl.seed = o.seed; gl.step_ptr = e->d_step;
-        if (o.sample) {
-            gl.next_tok = e->d_next_tok; gl.done_counter = e->done_counter;
-            if (o.advance) {
-                gl.tok = e->d_tok; gl.pos = e->d_pos; gl.out_tokens = e->d_out_tokens; gl.max_out = e->max_out; gl.step_w = e->d_step;
-            }
-        }
-        if (!(skip & 64)) gemv_dispatch<EPI_LOGITS>(e, gl);
-    }
+    if ((o.sample || o.store_logits) && !(skip & 64)) lm_head_and_sample(e, T, o.sample, o.advance, o.store_logits, o.inv_temp, o.seed);
     RT_CUDA(cudaGetLastError());
 }
 
@@ -635,19 +680,23 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             e->launches++;
 
             Gemm5Args go{};
-            go.S = S; go.N = H; go.K = e->nq_l * hd; go.out = e->pf_x; go.ldo = H;
-            pf_gemm(e->st, pdl, G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
-            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, nullptr, w.norm2, e->pf_xn, H, H, e->cfg.rms_eps);
+            go.S = S; go.N = H; go.K = e->nq_l * hd; go.ldo = H;
+            go.out = e->tp ? e->pf_delta : e->pf_x;
+            pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
+            if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
+            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, w.norm2, e->pf_xn, H, H, e->cfg.rms_eps);
             e->launches += 2;
 
             Gemm5Args gu{};
             gu.S = S; gu.N = 2 * e->F_l; gu.K = H; gu.out_bf = e->pf_act; gu.ldob = e->F_l;
             pf_gemm(e->st, pdl, G5_EPI_SWIGLU, e->map_xn, e->map_w[4 * l + 2], gu);
             Gemm5Args gd{};
-            gd.S = S; gd.N = H; gd.K = e->F_l; gd.out = e->pf_x; gd.ldo = H;
-            pf_gemm(e->st, pdl, G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
+            gd.S = S; gd.N = H; gd.K = e->F_l; gd.ldo = H;
+            gd.out = e->tp ? e->pf_delta : e->pf_x;
+            pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
+            if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
             const bf16* nw = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;
-            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, nullptr, nw, e->pf_xn, H, H, e->cfg.rms_eps);
+            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, nw, e->pf_xn, H, H, e->cfg.rms_eps);
             e->launches += 3;
         }
         RT_CUDA(cudaGetLastError());
@@ -658,13 +707,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             for (int j = 0; j < T; ++j)
                 RT_CUDA(cudaMemcpyAsync(e->xn + (size_t)j * H, e->pf_xn + (size_t)rows[j] * H, (size_t)H * sizeof(bf16),
                                         cudaMemcpyDeviceToDevice, e->st));
-            GemvArgs gl{};
-            gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = H; gl.T = T; gl.X = e->xn; gl.ldx = H;
-            gl.logits = store ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
-            gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
-            gl.inv_temp = base.inv_temp; gl.seed = base.seed; gl.step_ptr = e->d_step;
-            if (sample) { gl.next_tok = e->d_next_tok; gl.done_counter = e->done_counter; }
-            gemv_dispatch<EPI_LOGITS>(e, gl);
+            lm_head_and_sample(e, T, sample, false, store, base.inv_temp, base.seed);
         };
         if (logits_out) {
             for (int r0 = 0; r0 < S; r0 += MAX_SLOTS) {

@@ -6,6 +6,7 @@
 #include "../../include/rt_engine.h"
 #include "common.cuh"
 #include "prefill.cuh"
+#include "tp.cuh"
 
 constexpr int MAX_SLOTS = 32;      // token slots per forward step (decode: knights; slab prefill: tokens)
 constexpr int MAX_CHUNKS = 136;    // attention partials per (slot, head): <= 64 shared + <= 64 own (+ rounding)
@@ -86,6 +87,12 @@ struct rt_engine {
     int* pf_host = nullptr;        // pinned staging: tok, seq, pos (pf_cap each) + work items
     PfTensorMap map_xn{}, map_attn{}, map_act{};
     std::vector<PfTensorMap> map_w;   // per layer: qkv, o, gate/up, down
+
+    // tensor parallel
+    TpComm* tp = nullptr;
+    float* loc_best = nullptr;     // [64 words]: 32 local winning scores, 32 local winning ids
+    float* all_best = nullptr;     // [tp][64 words]
+    float* pf_delta = nullptr;     // [pf_cap][H] partial sums of the row-parallel prefill GEMMs
 
     // cached decode graph
     cudaGraphExec_t graph_exec = nullptr;

@@ -58,6 +58,7 @@ struct GemvArgs {
     const int* step_ptr;
     // LOGITS "sampler tail" (next_tok nullable => candidates only)
     int* next_tok;            // [T]
+    float* next_val;          // nullable: winning score per slot (tensor parallel: ranks compare their local winners)
     int* tok;                 // nullable: tok[t] = next (decode feeds the next step)
     int* pos;                 // nullable: pos[t] += 1
     int* out_tokens;          // nullable: out_tokens[t*max_out + *step_w] = next
@@ -436,6 +437,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                             if (sval[w] > best || (sval[w] == best && sidx[w] < bi)) { best = sval[w]; bi = sidx[w]; }
                         if (bi == 0x7fffffff) bi = 0;
                         a.next_tok[t] = bi;
+                        if (a.next_val) a.next_val[t] = best;
                         if (a.tok) a.tok[t] = bi;
                         if (a.pos) a.pos[t] += 1;
                         if (a.out_tokens && step < a.max_out) a.out_tokens[(size_t)t * a.max_out + step] = bi;

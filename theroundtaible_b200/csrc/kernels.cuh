@@ -496,3 +496,38 @@ static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs
         if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * HD + threadIdx.x] = o;
     }
 }
+
+// Tensor parallel: every rank holds the local winners (score, token id) of all ranks after an all-gather; pick the
+// global arg-max (lowest id wins ties) and advance the decode state -- identically on every rank.
+struct TpPickArgs {
+    const float* all_val;   // [tp][64 words]: 32 scores then 32 ids per rank
+    int tp, T;
+    int* next_tok;
+    int* tok;
+    int* pos;
+    int* out_tokens;
+    int max_out;
+    int* step_w;
+};
+static __global__ void tp_pick_kernel(const TpPickArgs a) {
+    griddep_launch();
+    griddep_wait();
+    const int t = threadIdx.x;
+    const int step = a.step_w ? *a.step_w : 0;
+    if (t < a.T) {
+        float best = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int r = 0; r < a.tp; ++r) {
+            const float v = a.all_val[r * 64 + t];
+            const int i = reinterpret_cast<const int*>(a.all_val)[r * 64 + 32 + t];
+            if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+        }
+        if (bi == 0x7fffffff) bi = 0;
+        a.next_tok[t] = bi;
+        if (a.tok) a.tok[t] = bi;
+        if (a.pos) a.pos[t] += 1;
+        if (a.out_tokens && step < a.max_out) a.out_tokens[(size_t)t * a.max_out + step] = bi;
+    }
+    __syncthreads();
+    if (t == 0 && a.step_w) *a.step_w = step + 1;
+}

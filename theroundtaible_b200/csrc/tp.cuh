@@ -1,0 +1,13 @@
+// Tensor parallelism plumbing: NCCL loaded lazily (dlopen) so that single-GPU users need no NCCL at all.
+// One engine per GPU/process; the communicator spans the tp_size engines.  No reference counterpart
+// (/root/reference has no collective call site); SURVEY.md 8(e) defines the partitioning:
+// QKV / gate / up column-parallel, O / down row-parallel + all-reduce, KV heads / TP, lm_head vocab-parallel.
+#pragma once
+#include "common.cuh"
+
+struct TpComm;                                     // opaque
+void tp_unique_id(void* out128);
+TpComm* tp_init(int rank, int size, const void* id128);
+void tp_destroy(TpComm* c);
+void tp_allreduce_sum_f32(TpComm* c, float* buf, size_t count, cudaStream_t st);
+void tp_allgather_bytes(TpComm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);

@@ -143,13 +143,15 @@ class Engine:
     """One engine per GPU.  Calls are serialised by the caller (the reference issues one execute() at a time)."""
 
     def __init__(self, model: str, *, seed: int = 0, device: int = 0, max_batch: int = 8, max_ctx: int = 4096,
-                 kv_pool_bytes: int = 0, flags: int = 0):
+                 kv_pool_bytes: int = 0, flags: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl_id: bytes | None = None):
         lib = load_library()
         cfg = arch_config(model)
         cfg.seed = seed
         cfg.weights_path = None
         cfg.device = device
-        cfg.tp_rank, cfg.tp_size, cfg.nccl_id = 0, 1, None
+        self._nccl_id = C.create_string_buffer(nccl_id, 128) if nccl_id else None    # must outlive rt_engine_create
+        cfg.tp_rank, cfg.tp_size = tp_rank, tp_size
+        cfg.nccl_id = C.cast(self._nccl_id, C.c_void_p) if self._nccl_id else None
         cfg.max_batch, cfg.max_ctx, cfg.kv_pool_bytes, cfg.flags = max_batch, max_ctx, kv_pool_bytes, flags
         self.cfg = cfg
         self.model = model
@@ -223,7 +225,7 @@ class Engine:
 
     def step_logits(self, ids, mode: int = 0) -> np.ndarray:
         ids = np.ascontiguousarray(ids, dtype=np.int32)
-        out = np.empty((len(ids), self.vocab), dtype=np.float32)
+        out = np.empty((len(ids), self.vocab // self.cfg.tp_size), dtype=np.float32)    # vocab-parallel shard under TP
         _check(self._lib.rt_step_logits(self._h, _p(ids, C.c_int32), len(ids), mode, _p(out, C.c_float)), self._h)
         return out
 
@@ -234,6 +236,13 @@ class Engine:
 
 
 # ---- tokenizer + kernel hooks (module level: they need no engine) ----------------------------------
+def nccl_unique_id() -> bytes:
+    """rank 0 of a tensor-parallel group calls this and ships the 128 bytes to every rank (rt_config.nccl_id)."""
+    buf = C.create_string_buffer(128)
+    _check(load_library().rt_nccl_unique_id(buf))
+    return buf.raw
+
+
 def tokenize_chat(text: str) -> list:
     lib = load_library()
     b = text.encode("utf-8")
