@@ -12,6 +12,7 @@
 
 int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi);
 void rt_attn_host_setup();
+void rt_gemv_stream_alloc(rt_engine* e);
 void rt_attn_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunk_blocks);
 
 namespace {
@@ -246,6 +247,7 @@ struct Scratch {
         e.dev = device;
         e.sm_count = prop.multiProcessorCount;
         RT_CUDA(cudaStreamCreateWithFlags(&e.st, cudaStreamNonBlocking));
+        rt_gemv_stream_alloc(&e);
     }
     template <typename T>
     T* alloc(size_t n, bool zero = true) {
@@ -258,6 +260,7 @@ struct Scratch {
     ~Scratch() {
         if (e.st) cudaStreamSynchronize(e.st);
         for (void* p : bufs) cudaFree(p);
+        for (void* p : e.allocs) cudaFree(p);
         if (e.st) cudaStreamDestroy(e.st);
     }
 };

@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cuda_profiler_api.h>
 
+#include "gemv_stream.cuh"
 #include "kernels.cuh"
 #include "weights.cuh"
 
@@ -205,8 +206,23 @@ void gemv_pick_warps(rt_engine* e, const GemvArgs& a, int grid) {
     else gemv_launch<EPI, NT, MT, 8>(e, a, grid);
 }
 
+template <int EPI, int NT>
+void gemv_stream_launch(rt_engine* e, const GemvArgs& a, int grid) {
+    GemvStreamFix fx{e->gs_scratch, e->gs_flags};
+    launch_pdl(e, gemv_stream_kernel<NT, EPI>, dim3(grid), dim3(GS_THREADS), (size_t)GS_RING_BYTES, a, fx);
+}
+
 template <int EPI>
 int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
+    if (e->use_stream && e->gs_scratch) {
+        // persistent stream-K kernel: one CTA per SM, equal contiguous byte ranges; candidates are per 16-row tile
+        const long long units = (long long)(a.N / 16) * (a.K / 32);
+        const int grid = (int)std::min<long long>(e->sm_count, units);
+        if (a.T <= 8) gemv_stream_launch<EPI, 1>(e, a, grid);
+        else if (a.T <= 16) gemv_stream_launch<EPI, 2>(e, a, grid);
+        else gemv_stream_launch<EPI, 4>(e, a, grid);
+        return a.N / 16;
+    }
     static const int force_mt = env_int("RT_GEMV_MT", 0);
     const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);
     int mt = 4 / NT;
@@ -238,6 +254,30 @@ int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi) {
         case EPI_SWIGLU: return gemv_dispatch<EPI_SWIGLU>(e, a);
         default: throw RtError(RT_ERR_INVALID, "unsupported epilogue for the test hook");
     }
+}
+
+void rt_gemv_stream_setup() {
+    auto set = [](auto kern) { RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_RING_BYTES)); };
+    set(gemv_stream_kernel<1, EPI_STORE>); set(gemv_stream_kernel<2, EPI_STORE>); set(gemv_stream_kernel<4, EPI_STORE>);
+    set(gemv_stream_kernel<1, EPI_RESID>); set(gemv_stream_kernel<2, EPI_RESID>); set(gemv_stream_kernel<4, EPI_RESID>);
+    set(gemv_stream_kernel<1, EPI_SWIGLU>); set(gemv_stream_kernel<2, EPI_SWIGLU>); set(gemv_stream_kernel<4, EPI_SWIGLU>);
+    set(gemv_stream_kernel<1, EPI_LOGITS>); set(gemv_stream_kernel<2, EPI_LOGITS>); set(gemv_stream_kernel<4, EPI_LOGITS>);
+    set(gemv_stream_kernel<1, EPI_QKV>); set(gemv_stream_kernel<2, EPI_QKV>); set(gemv_stream_kernel<4, EPI_QKV>);
+}
+
+void rt_gemv_stream_alloc(rt_engine* e) {
+    // experimental: measured slower than gemv_kernel in round 1 (per-tile reduce is not overlapped with one CTA per SM),
+    // so it is opt-in (RT_GEMV_STREAM=1); profiles/r1_summary.md has the numbers
+    e->use_stream = env_int("RT_GEMV_STREAM", 0) != 0;
+    rt_gemv_stream_setup();
+    void* p = nullptr;
+    RT_CUDA(cudaMalloc(&p, (size_t)e->sm_count * 16 * 32 * sizeof(float)));
+    e->allocs.push_back(p);
+    e->gs_scratch = reinterpret_cast<float*>(p);
+    RT_CUDA(cudaMalloc(&p, (size_t)e->sm_count * sizeof(int)));
+    e->allocs.push_back(p);
+    e->gs_flags = reinterpret_cast<int*>(p);
+    RT_CUDA(cudaMemsetAsync(e->gs_flags, 0, (size_t)e->sm_count * sizeof(int), e->st));
 }
 
 void rt_attn_host_setup() {
@@ -287,6 +327,7 @@ void engine_init(rt_engine* e) {
     RT_CUDA(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (auto& ev : e->ev) RT_CUDA(cudaEventCreate(&ev));
     rt_attn_host_setup();
+    rt_gemv_stream_alloc(e);
     if (c.tp_size > 1) e->tp = tp_init(c.tp_rank, c.tp_size, c.nccl_id);
 
     e->L = c.layers; e->H = c.hidden; e->hd = c.head_dim; e->nq = c.n_q; e->nkv = c.n_kv; e->F = c.ffn; e->vocab = c.vocab;

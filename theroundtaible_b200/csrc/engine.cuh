@@ -73,6 +73,9 @@ struct rt_engine {
     float *part_o = nullptr, *part_ml = nullptr;
     int* done_counter = nullptr;   // arrival counter of the residual projections' fused RMSNorm tail
     bool use_pdl = true;
+    bool use_stream = false;       // persistent TMA-fed stream-K projection kernel (gemv_stream.cuh)
+    float* gs_scratch = nullptr;   // [SMs][16][32] stream-K partial tiles
+    int* gs_flags = nullptr;       // [SMs]
     float* cta_max = nullptr;
     int* cta_idx = nullptr;
     int lm_ctas = 0;
