@@ -197,12 +197,15 @@ int env_int(const char* name, int dflt) {
     return v ? atoi(v) : dflt;
 }
 
+// 16 warps only for very long rows (down-projection, K = FFN >= 8192): measured on B200 (scripts/gemv_tune*.py)
+inline int gemv_warps(int K) {
+    static const int force = env_int("RT_GEMV_NW", 0);
+    return force ? force : (K >= 8192 ? 16 : 8);
+}
+
 template <int EPI, int NT, int MT>
 void gemv_pick_warps(rt_engine* e, const GemvArgs& a, int grid) {
-    // long rows (down-projection, K = FFN) get 16 warps so that each warp still has only 1-2 batches of loads
-    static const int force = env_int("RT_GEMV_NW", 0);
-    const int nw = force ? force : (a.K >= 4096 ? 16 : 8);
-    if (nw == 16) gemv_launch<EPI, NT, MT, 16>(e, a, grid);
+    if (gemv_warps(a.K) == 16) gemv_launch<EPI, NT, MT, 16>(e, a, grid);
     else gemv_launch<EPI, NT, MT, 8>(e, a, grid);
 }
 
@@ -225,9 +228,15 @@ int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
     }
     static const int force_mt = env_int("RT_GEMV_MT", 0);
     const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);
-    int mt = 4 / NT;
-    // measured on B200 (scripts/gemv_tune.py): 64-row CTAs win once they still give >= 1.5 CTAs per SM
-    while (mt > 1 && (a.N % (16 * mt) != 0 || a.N / (16 * mt) < (3 * e->sm_count) / 2)) mt >>= 1;
+    // rows per CTA: the smallest 16*MT that fits the whole matrix into ONE wave of resident CTAs (2 per SM with 8 warps,
+    // 1 per SM with 16 warps); matrices that need several waves anyway take 32-row CTAs, the lm_head 64-row CTAs
+    const int tiles = a.N / 16;
+    const int capacity = e->sm_count * (gemv_warps(a.K) == 16 ? 1 : 2);
+    const int mt_max = 4 / NT;
+    int mt = 1;
+    while (mt < mt_max && (tiles + mt - 1) / mt > capacity) mt <<= 1;
+    if ((tiles + mt - 1) / mt > capacity) mt = std::min(mt_max, tiles >= 4096 ? 4 : 2);
+    while (mt > 1 && a.N % (16 * mt) != 0) mt >>= 1;
     if (force_mt && force_mt * NT <= 4 && a.N % (16 * force_mt) == 0) mt = force_mt;
     const int grid = cdiv(a.N, 16 * mt);
     if (NT == 1) {
