@@ -285,6 +285,18 @@ def run_b200(args, w):
         achieved = bytes_step / (step_ms * 1e-3) / 1e9
         # the dominant kernel alone: the gate/up projection stream of one layer, re-streamed from HBM
         cfg = eng.cfg
+        # prefill: tensor-core path.  FLOPs = 2 * projection weights * tokens + causal attention (QK^T and PV)
+        pf_tokens = shared_pages + w["knights"] * (w["shared"] - shared_pages + w["own"])
+        per_layer_w = (cfg.hidden * (cfg.n_q + 2 * cfg.n_kv) * cfg.head_dim + cfg.n_q * cfg.head_dim * cfg.hidden + 3 * cfg.hidden * cfg.ffn) // tp
+        attn_pairs = shared_pages * (shared_pages + 1) / 2 + w["knights"] * sum(range(shared_pages + 1, w["shared"] + w["own"] + 1))
+        pf_flops = cfg.layers * (2.0 * per_layer_w * pf_tokens + 4.0 * (cfg.n_q // tp) * cfg.head_dim * attn_pairs)
+        pf_ms = pre_ms_m / args.steps
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            tf_burst, tf_sust = float(peaks["bf16_tflops"]), float(peaks["bf16_tflops_sustained"])
+        except Exception:  # noqa: BLE001
+            tf_burst, tf_sust = 1590.0, 1400.0
+        pf_tflops = pf_flops / (pf_ms * 1e-3) / 1e12
         gu_ms = E.k_gemv_bench(2 * cfg.ffn // tp, cfg.hidden, w["knights"], iters=200, device=local)
         gu_gbs = 2 * (cfg.ffn // tp) * cfg.hidden * 2 / (gu_ms * 1e-3) / 1e9
         cpu = None
@@ -315,6 +327,9 @@ def run_b200(args, w):
                     "d2h_bytes_per_step": d2h, "ms_per_round": e2e_ms_m / args.steps,
                     "note": "generated tokens / wall time of adapter.execute_round (tokenise, prefill, decode, detokenise)"},
             "gpu_launches": launches, "clocks": clocks,
+            "prefill": {"tokens_prefilled": pf_tokens, "ms": pf_ms, "tok_per_s": pf_tokens / (pf_ms * 1e-3), "tflops": pf_tflops,
+                        "bound": "tensor", "frac_of_measured_burst": pf_tflops / tf_burst, "frac_of_measured_sustained": pf_tflops / tf_sust,
+                        "note": "whole prefill phase (tcgen05 GEMMs + flash attention + norms), algorithmic FLOPs / CUDA-event time"},
             "extra": {"seq": {"decode_tok_per_s": seq_tok / (seq_dec_ms * 1e-3), "round_ms": seq_round_ms,
                               "note": "SEQ = one knight per call (B=1), what orchestrator.ts:361-442 issues"},
                       "batch_round_ms": wall_ms_m / args.steps},

@@ -12,11 +12,7 @@ def run(T, n_q, n_kv, hd, L, shared, chunk):
     if shared:
         kb[:, :shared] = kb[0:1, :shared]; vb[:, :shared] = vb[0:1, :shared]
     E.k_attention(qb, kb, vb, [L] * T, shared=shared, chunk=chunk)
-for fused in (0, 1):
-    if fused: os.environ["RT_ATTN_BENCH_FUSED"] = "1"
-    print("fused", fused, file=sys.stderr)
-    for chunk in (64, 128, 256):
-        run(3, 32, 8, 64, 1344, 1024, chunk)
-    run(3, 32, 8, 64, 1344, 0, 128)
-    run(1, 32, 8, 64, 128, 0, 128)
-    run(5, 32, 8, 128, 8448, 8192, 128)
+for chunk in (32, 64, 128):
+    run(3, 32, 8, 64, 1344, 1024, chunk)
+for chunk in (64, 96, 128, 192, 256):
+    run(5, 32, 8, 128, 8448, 8192, chunk)

@@ -26,7 +26,7 @@ def _fingerprint() -> str:
             if fn.endswith((".cu", ".cuh", ".cpp", ".h")):
                 with open(os.path.join(root, fn), "rb") as f:
                     h.update(fn.encode() + b"\0" + f.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update((" ".join(NVCC_FLAGS) + os.environ.get("RT_NVCC_EXTRA", "")).encode())
     return h.hexdigest()
 
 
@@ -37,7 +37,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read().strip() == fp:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc, *NVCC_FLAGS, "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES]]
+    extra = os.environ.get("RT_NVCC_EXTRA", "").split()      # experiments only (e.g. -DRT_ATTN_STAGES=3)
+    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

@@ -625,9 +625,10 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
 }
 
 // ---- attention split geometry for a call whose longest sequence reaches max_len tokens ----------------
-static void plan_chunks(int max_len, int shared_len, StepOpts& o) {
+static void plan_chunks(int max_len, int shared_len, StepOpts& o, int hd = 64) {
     const int total_pages = cdiv(max_len, KV_PAGE);
-    o.chunk_pages = std::max(env_int("RT_ATTN_MIN_CHUNK_PAGES", 4), cdiv(total_pages, 64));
+    // measured (scripts/attn_bench.py): short chunks for head_dim 64 (latency-bound, tiny KV), 128-key chunks for 128
+    o.chunk_pages = std::max(env_int("RT_ATTN_MIN_CHUNK_PAGES", hd >= 128 ? 8 : 2), cdiv(total_pages, 64));
     const int C = o.chunk_pages * KV_PAGE;
     const int n_sh = cdiv(shared_len, C);
     const int n_own = cdiv(std::max(max_len - shared_len, 1), C);
@@ -860,11 +861,13 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     RT_CUDA(cudaMemsetAsync(e->d_step, 0, sizeof(int), e->st));   // sampling noise is keyed on the step counter
 
     StepOpts base{};
-    plan_chunks(max_len, 0, base);   // prefill slabs: no cascade phase
+    plan_chunks(max_len, 0, base, e->hd);   // prefill slabs: no cascade phase
     base.inv_temp = s.temperature > 0.f ? 1.0f / s.temperature : 0.f;
     base.seed = s.seed;
 
     // ---- prefill ----
+    const char* prof_phase = getenv("RT_PROFILE_PHASE");     // ncu --profile-from-start off: "prefill" | "decode"
+    if (prof_phase && !strcmp(prof_phase, "prefill")) cudaProfilerStart();
     RT_CUDA(cudaEventRecord(e->ev[0], e->st));
     {
         std::vector<int> tok, seq, pos, want;
@@ -880,6 +883,10 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
             prefill_via_slabs(e, tok, seq, pos, want, base, t0, deadline_ms);
     }
     RT_CUDA(cudaEventRecord(e->ev[1], e->st));
+    if (prof_phase && !strcmp(prof_phase, "prefill")) {
+        RT_CUDA(cudaStreamSynchronize(e->st));
+        cudaProfilerStop();
+    }
 
     // ---- decode state: slot b = sequence b, token = its first generated token ----
     std::vector<int> first(n);
@@ -901,7 +908,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     dec.sample = true;
     dec.advance = true;
     dec.n_shared_tiles = shared > 0 ? cdiv(n * e->G, 16) : 0;
-    plan_chunks(max_len, shared, dec);
+    plan_chunks(max_len, shared, dec, e->hd);
 
     const int n_steps = s.max_new_tokens - 1;
     const bool use_graph = !(e->cfg.flags & RT_FLAG_NO_GRAPH);
@@ -911,7 +918,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     std::vector<int> finish(n, 0);
     int steps_done = 0;
 
-    const bool prof = getenv("RT_PROFILE_DECODE") != nullptr;   // ncu --profile-from-start off: decode steps only
+    const bool prof = getenv("RT_PROFILE_DECODE") != nullptr || (prof_phase && !strcmp(prof_phase, "decode"));
     if (prof) cudaProfilerStart();
     RT_CUDA(cudaEventRecord(e->ev[2], e->st));
     while (steps_done < n_steps) {
@@ -998,7 +1005,7 @@ void engine_step_logits(rt_engine* e, const int32_t* ids, int n, int mode, float
     const int zero = 0;
     RT_CUDA(cudaMemcpyAsync(e->d_shared_len, &zero, sizeof(int), cudaMemcpyHostToDevice, e->st));
     StepOpts o{};
-    plan_chunks(p0 + n, 0, o);
+    plan_chunks(p0 + n, 0, o, e->hd);
     o.store_logits = true;
     if (mode == 1) {
         std::vector<int> tok(ids, ids + n), seq(n, 0), pos(n), want(n, -1);

@@ -178,7 +178,10 @@ struct AttnArgs {
     float scale_log2;           // log2(e)/sqrt(hd)
 };
 
-constexpr int ATTN_STAGES = 4;
+#ifndef RT_ATTN_STAGES
+#define RT_ATTN_STAGES 3
+#endif
+constexpr int ATTN_STAGES = RT_ATTN_STAGES;   // cp.async ring depth per warp (measured best on B200: 3 stages, 128-key chunks at head_dim 128)
 constexpr int ATTN_WARPS = 4;
 
 // XOR swizzle of the 16-byte piece index inside a shared-memory row of HD bf16, chosen so that the 8 rows an
@@ -202,7 +205,7 @@ __device__ __forceinline__ void attn_issue_page(uint32_t sbase, const bf16* __re
 }
 
 template <int HD>
-__global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const AttnArgs a) {
+__global__ void __launch_bounds__(ATTN_WARPS * 32, HD == 128 ? 2 : 4) attn_decode_kernel(const AttnArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int STAGE_BYTES = 2 * KV_PAGE * HD * 2;
     constexpr int KT = HD / 16;  // k-steps for QK^T; pairs of 8-wide d tiles for PV
@@ -366,9 +369,11 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32) attn_decode_kernel(const Attn
                 uint32_t r0, r1, r2, r3;
                 ldmatrix_x4_trans(r0, r1, r2, r3, sV + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
                 mma_bf16_16816(o[2 * dp], pa0, pa1, pa2, pa3, r0, r1);
-                mma_bf16_16816(o[2 * dp], pl0, pl1, pl2, pl3, r0, r1);
                 mma_bf16_16816(o[2 * dp + 1], pa0, pa1, pa2, pa3, r2, r3);
+#ifndef RT_ATTN_NO_LO
+                mma_bf16_16816(o[2 * dp], pl0, pl1, pl2, pl3, r0, r1);
                 mma_bf16_16816(o[2 * dp + 1], pl0, pl1, pl2, pl3, r2, r3);
+#endif
             }
         }
         __syncwarp();
