@@ -13,6 +13,7 @@
 
 #include "gemv_stream.cuh"
 #include "kernels.cuh"
+#include "tp_fused.cuh"
 #include "weights.cuh"
 
 namespace {
@@ -407,6 +408,21 @@ void engine_init(rt_engine* e) {
     if (c.tp_size > 1) {
         e->loc_best = zalloc_f(64);
         e->all_best = zalloc_f((size_t)64 * c.tp_size);
+        e->tpf_on = env_int("RT_TP_FUSED", 1) != 0 && c.tp_size <= TPF_MAX && e->H <= 16 * 512 && e->H % 4 == 0;
+        if (e->tpf_on) {
+            // separate allocations: CUDA IPC shares whole allocations
+            for (int j = 0; j < 2; ++j) e->tpf_delta[j] = zalloc_f((size_t)MAX_SLOTS * e->H);
+            e->tpf_flags = dalloc<int>(e, MAX_SLOTS * TPF_MAX);
+            e->tpf_epoch = dalloc<int>(e, MAX_SLOTS);
+            RT_CUDA(cudaMemsetAsync(e->tpf_flags, 0, MAX_SLOTS * TPF_MAX * sizeof(int), e->st));
+            RT_CUDA(cudaMemsetAsync(e->tpf_epoch, 0, MAX_SLOTS * sizeof(int), e->st));
+            RT_CUDA(cudaStreamSynchronize(e->st));
+            for (int j = 0; j < 2; ++j) tp_ipc_exchange(e->tp, e->tpf_delta[j], e->tpf_peer_delta[j], e->st);
+            tp_ipc_exchange(e->tp, e->tpf_flags, e->tpf_peer_flags, e->st);
+            // nobody may raise a flag before every rank has cleared its own: one more collective as a barrier
+            tp_allreduce_sum_f32(e->tp, e->loc_best, 64, e->st);
+            RT_CUDA(cudaStreamSynchronize(e->st));
+        }
     }
 
     // tensor-core prefill path
@@ -444,6 +460,10 @@ void engine_free(rt_engine* e) {
     if (e->dev >= 0) cudaSetDevice(e->dev);
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
+    if (e->tp && e->tpf_on) {
+        for (int j = 0; j < 2; ++j) tp_ipc_close(e->tp, e->tpf_peer_delta[j]);
+        tp_ipc_close(e->tp, e->tpf_peer_flags);
+    }
     tp_destroy(e->tp);
     e->tp = nullptr;
     for (void* p : e->allocs) cudaFree(p);
@@ -506,6 +526,30 @@ void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* p
     RT_CUDA(cudaMemcpyAsync(e->d_tok, e->h_stage, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
     RT_CUDA(cudaMemcpyAsync(e->d_seq, e->h_stage + MAX_SLOTS, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
     RT_CUDA(cudaMemcpyAsync(e->d_pos, e->h_stage + 2 * MAX_SLOTS, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
+}
+
+// row-parallel projection under tensor parallelism: partial sums -> all-reduce -> residual add -> RMSNorm.
+// Fused path: ONE kernel pulls every rank's partial over NVLink peer memory (tp_fused.cuh); otherwise NCCL + rmsnorm.
+static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, const bf16* norm_w) {
+    const int H = e->H;
+    if (e->tpf_on) {
+        g.out = e->tpf_delta[site]; g.ldo = H;
+        gemv_dispatch<EPI_STORE>(e, g);
+        TpFusedArgs a{};
+        for (int p = 0; p < e->cfg.tp_size; ++p) {
+            a.partial[p] = reinterpret_cast<const float*>(e->tpf_peer_delta[site][p]);
+            a.flags[p] = reinterpret_cast<int*>(e->tpf_peer_flags[p]);
+        }
+        a.epoch = e->tpf_epoch; a.rank = e->cfg.tp_rank; a.tp = e->cfg.tp_size; a.H = H;
+        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.eps = e->cfg.rms_eps;
+        launch_pdl(e, tp_fused_allreduce_norm_kernel<512>, dim3(T), dim3(512), 0, a);
+    } else {
+        g.out = e->delta; g.ldo = H;
+        gemv_dispatch<EPI_STORE>(e, g);
+        tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
+        rmsnorm_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, H, H, e->cfg.rms_eps);
+        e->launches += 2;
+    }
 }
 
 // lm_head over the T rows of e->xn + sampling.  Single GPU: the projection's last CTA picks the winners and advances
@@ -591,12 +635,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
             go.norm_w = w.norm2; go.xn_out = e->xn; go.done_counter = e->done_counter; go.eps = e->cfg.rms_eps;
             if (!(skip & 8)) gemv_dispatch<EPI_RESID>(e, go);
         } else {
-            // row-parallel: partial sums -> all-reduce over NVLink -> residual add + RMSNorm
-            go.out = e->delta; go.ldo = H;
-            gemv_dispatch<EPI_STORE>(e, go);
-            tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
-            rmsnorm_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, w.norm2, e->xn, H, H, e->cfg.rms_eps);
-            e->launches += 2;
+            tp_reduce_residual_norm(e, go, 0, T, w.norm2);
         }
 
         GemvArgs gu{};
@@ -612,11 +651,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
             gd.norm_w = next_norm; gd.xn_out = e->xn; gd.done_counter = e->done_counter; gd.eps = e->cfg.rms_eps;
             if (!(skip & 32)) gemv_dispatch<EPI_RESID>(e, gd);
         } else {
-            gd.out = e->delta; gd.ldo = H;
-            gemv_dispatch<EPI_STORE>(e, gd);
-            tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
-            rmsnorm_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, next_norm, e->xn, H, H, e->cfg.rms_eps);
-            e->launches += 2;
+            tp_reduce_residual_norm(e, gd, 1, T, next_norm);
         }
     }
 

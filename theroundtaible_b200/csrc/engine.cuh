@@ -96,6 +96,12 @@ struct rt_engine {
     float* loc_best = nullptr;     // [64 words]: 32 local winning scores, 32 local winning ids
     float* all_best = nullptr;     // [tp][64 words]
     float* pf_delta = nullptr;     // [pf_cap][H] partial sums of the row-parallel prefill GEMMs
+    // fused peer-memory all-reduce (tp_fused.cuh): two partial buffers (O-proj / down-proj call sites), flags, epochs
+    bool tpf_on = false;
+    float* tpf_delta[2] = {nullptr, nullptr};
+    int *tpf_flags = nullptr, *tpf_epoch = nullptr;
+    void* tpf_peer_delta[2][8] = {};
+    void* tpf_peer_flags[8] = {};
 
     // cached decode graph
     cudaGraphExec_t graph_exec = nullptr;

@@ -90,3 +90,41 @@ void tp_allreduce_sum_f32(TpComm* c, float* buf, size_t count, cudaStream_t st) 
 void tp_allgather_bytes(TpComm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st) {
     check(api().AllGather(send, recv, bytes_per_rank, NCCL_INT8, c->comm, st), "ncclAllGather");
 }
+
+int tp_rank(const TpComm* c) { return c->rank; }
+int tp_size(const TpComm* c) { return c->size; }
+
+void tp_ipc_exchange(TpComm* c, void* local, void** out_ptrs, cudaStream_t st) {
+    cudaIpcMemHandle_t mine;
+    RT_CUDA(cudaIpcGetMemHandle(&mine, local));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    void *dsend = nullptr, *drecv = nullptr;
+    RT_CUDA(cudaMalloc(&dsend, 64));
+    RT_CUDA(cudaMalloc(&drecv, (size_t)64 * c->size));
+    RT_CUDA(cudaMemcpyAsync(dsend, &mine, 64, cudaMemcpyHostToDevice, st));
+    tp_allgather_bytes(c, dsend, drecv, 64, st);
+    std::string all((size_t)64 * c->size, '\0');
+    RT_CUDA(cudaMemcpyAsync(&all[0], drecv, all.size(), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    cudaFree(dsend);
+    cudaFree(drecv);
+    for (int p = 0; p < c->size; ++p) {
+        if (p == c->rank) {
+            out_ptrs[p] = local;
+            continue;
+        }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, &all[(size_t)64 * p], 64);
+        const cudaError_t er = cudaIpcOpenMemHandle(&out_ptrs[p], h, cudaIpcMemLazyEnablePeerAccess);
+        if (er != cudaSuccess) {
+            cudaGetLastError();
+            throw RtError(RT_ERR_CUDA, std::string("cudaIpcOpenMemHandle failed (peer access between the GPUs of the tensor-parallel group is required): ") +
+                                           cudaGetErrorString(er));
+        }
+    }
+}
+
+void tp_ipc_close(TpComm* c, void** ptrs) {
+    for (int p = 0; p < c->size; ++p)
+        if (p != c->rank && ptrs[p]) cudaIpcCloseMemHandle(ptrs[p]);
+}

@@ -11,3 +11,10 @@ TpComm* tp_init(int rank, int size, const void* id128);
 void tp_destroy(TpComm* c);
 void tp_allreduce_sum_f32(TpComm* c, float* buf, size_t count, cudaStream_t st);
 void tp_allgather_bytes(TpComm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
+
+// Exchange a cudaMalloc'ed buffer with every rank through CUDA IPC: out_ptrs[p] is rank p's buffer mapped into this
+// process (out_ptrs[rank] = local).  Collective: every rank must call it in the same order.
+void tp_ipc_exchange(TpComm* c, void* local, void** out_ptrs, cudaStream_t st);
+void tp_ipc_close(TpComm* c, void** ptrs);
+int tp_rank(const TpComm* c);
+int tp_size(const TpComm* c);
