@@ -147,6 +147,31 @@ def test_real_architecture_truncated_depth_llama32_1b():
             assert g.prefix_shared_tokens in (0, 128)
 
 
+def test_config1_architecture_full_depth_qwen25_05b():
+    """BASELINE.json configs[0] names Qwen2.5-0.5B: the FULL 24-layer architecture (qkv bias, 14/2 heads, tied head,
+    151,936-token vocab) against the oracle: teacher-forced logits through both kernel paths and 64 greedy tokens for
+    3 knights sharing a prefix (margin-aware rule)."""
+    a = ARCHS["qwen2.5-0.5b"]
+    oracle = OracleModel(a, 0, max_pos=512)
+    rng = np.random.default_rng(1234 + 1)
+    ids = rng.integers(0, a.vocab, 96)
+    ref = oracle.forward(ids, KVState(), round_act=True).numpy()
+    scale = np.abs(ref).max(-1)
+    with E.Engine("qwen2.5-0.5b", seed=0, max_batch=3, max_ctx=512) as eng:
+        eng.seq_reset()
+        got1 = eng.step_logits(ids, mode=1)
+        eng.seq_reset()
+        got0 = eng.step_logits(ids, mode=0)
+        assert (np.abs(got1 - ref).max(-1) / scale).max() <= REL_TOL
+        assert (np.abs(got0 - ref).max(-1) / scale).max() <= REL_TOL
+        common = ids[:64].tolist()
+        prompts = [common + rng.integers(0, a.vocab, 20 + i).tolist() for i in range(3)]
+        gens = eng.generate_ids(prompts, max_new_tokens=64)
+    bound = REL_TOL * float(np.abs(ref).max())
+    ties = sum(_greedy_compare(g.tokens, oracle, p, 64, err_bound=bound) for p, g in zip(prompts, gens))
+    assert ties <= 6
+
+
 def test_temperature_sampling_is_seeded_and_varies():
     with E.Engine("tiny-llama", seed=1, max_batch=2, max_ctx=128) as eng:
         p = list(range(10, 40))
