@@ -172,6 +172,30 @@ def test_config1_architecture_full_depth_qwen25_05b():
     assert ties <= 6
 
 
+def test_real_architecture_truncated_depth_llama31_8b():
+    """True Llama-3.1-8B dimensions (head_dim 128, 32/8 heads, hidden 4096, FFN 14336, untied 128k head) at 2 layers
+    (truncated depth, stated -- SURVEY.md 8c): both kernel paths against the oracle, then 5 knights with a shared prefix."""
+    a = ARCHS["llama-3.1-8b"].with_layers(2)
+    oracle = OracleModel(a, 0, max_pos=512)
+    rng = np.random.default_rng(1234 + 3)
+    ids = rng.integers(0, a.vocab, 200)
+    ref = oracle.forward(ids, KVState(), round_act=True).numpy()
+    scale = np.abs(ref).max(-1)
+    with E.Engine("llama-3.1-8b@L2", seed=0, max_batch=5, max_ctx=512) as eng:
+        eng.seq_reset()
+        got1 = eng.step_logits(ids, mode=1)
+        eng.seq_reset()
+        got0 = eng.step_logits(ids[:70], mode=0)
+        assert (np.abs(got1 - ref).max(-1) / scale).max() <= REL_TOL
+        assert (np.abs(got0 - ref[:70]).max(-1) / scale[:70]).max() <= REL_TOL
+        prompts = [ids[:160].tolist() + rng.integers(0, a.vocab, 12 + i).tolist() for i in range(5)]
+        gens = eng.generate_ids(prompts, max_new_tokens=24)
+    bound = REL_TOL * float(np.abs(ref).max())
+    for p, g in zip(prompts, gens):
+        _greedy_compare(g.tokens, oracle, p, 24, err_bound=bound)
+        assert g.prefix_shared_tokens in (0, 160)
+
+
 def test_temperature_sampling_is_seeded_and_varies():
     with E.Engine("tiny-llama", seed=1, max_batch=2, max_ctx=128) as eng:
         p = list(range(10, 40))

@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cuda_profiler_api.h>
 
+#include "attn_decode2.cuh"
 #include "gemv_stream.cuh"
 #include "kernels.cuh"
 #include "tp_fused.cuh"
@@ -295,6 +296,25 @@ void rt_attn_host_setup() {
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(128)));
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(64)));
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(32)));
+}
+
+template <int HD, int NWARP>
+static void attn2_launch_t(rt_engine* e, const AttnArgs& a, int n_chunks) {
+    static_assert(ad2_smem_bytes(HD) <= 48 * 1024, "the ring fits the default dynamic shared memory limit");
+    (void)n_chunks;
+    launch_pdl(e, attn_decode2_kernel<HD, NWARP>, dim3(a.n_kv * (a.grid_nsh + a.T * a.grid_nown)), dim3(NWARP * 32), ad2_smem_bytes(HD), a);
+}
+template <int HD>
+static void attn2_launch_hd(rt_engine* e, const AttnArgs& a, int n_chunks) {
+    if (a.n_shared_tiles <= 1) attn2_launch_t<HD, 1>(e, a, n_chunks);
+    else if (a.n_shared_tiles == 2) attn2_launch_t<HD, 2>(e, a, n_chunks);
+    else attn2_launch_t<HD, 4>(e, a, n_chunks);
+}
+// version 2 of the decode attention (attn_decode2.cuh): CTA-shared page ring, one CTA per (kv head, chunk)
+void rt_attn2_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunks) {
+    if (hd == 128) attn2_launch_hd<128>(e, a, n_chunks);
+    else if (hd == 64) attn2_launch_hd<64>(e, a, n_chunks);
+    else attn2_launch_hd<32>(e, a, n_chunks);
 }
 
 void rt_attn_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunk_blocks) {
@@ -617,7 +637,12 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         a.part_o = e->part_o; a.part_ml = e->part_ml; a.max_chunks = MAX_CHUNKS;
         a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd));
         if (!(skip & 4)) {
-            rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
+            // version 2 (CTA-shared page ring) is correct but measured slower in round 1 (profiles/r1_summary.md): opt-in
+            static const int attn_v2 = env_int("RT_ATTN_V2", 0);
+            a.grid_nsh = o.n_shared_tiles > 0 ? o.n_sh : 0;
+            a.grid_nown = o.n_own;
+            if (attn_v2 && o.n_shared_tiles <= 4) rt_attn2_host_launch(e, a, hd, o.n_chunks);
+            else rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
             MergeArgs m{};
             m.part_o = e->part_o; m.part_ml = e->part_ml; m.max_chunks = MAX_CHUNKS; m.slot_pos = e->d_pos;
             m.shared_len_ptr = e->d_shared_len; m.cascade = o.n_shared_tiles > 0; m.chunk_keys = o.chunk_pages * KV_PAGE;
@@ -668,6 +693,9 @@ static void plan_chunks(int max_len, int shared_len, StepOpts& o, int hd = 64) {
     const int n_sh = cdiv(shared_len, C);
     const int n_own = cdiv(std::max(max_len - shared_len, 1), C);
     o.n_chunk_blocks = cdiv(std::max(n_sh, n_own), ATTN_WARPS);
+    o.n_chunks = std::max(n_sh, n_own);
+    o.n_sh = n_sh;
+    o.n_own = n_own;
     if (n_sh + n_own + 1 > MAX_CHUNKS) throw RtError(RT_ERR_INVALID, "attention split exceeds MAX_CHUNKS");
     o.n_partials_max = n_sh + n_own;
 }
@@ -821,7 +849,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
 
 static void ensure_graph(rt_engine* e, const StepOpts& o) {
     const StepOpts& g = e->graph_opts;
-    if (e->graph_exec && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks &&
+    if (e->graph_exec && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks && g.n_sh == o.n_sh && g.n_own == o.n_own &&
         g.n_shared_tiles == o.n_shared_tiles && g.inv_temp == o.inv_temp && g.seed == o.seed)
         return;
     if (e->graph_exec) {

@@ -27,7 +27,9 @@ struct StepOpts {
     bool advance = false;      // decode: feed the sampled token back, pos += 1, record it
     bool store_logits = false; // write logits[T][vocab]
     int chunk_pages = 4;
-    int n_chunk_blocks = 1;    // grid.x of the attention kernel
+    int n_chunk_blocks = 1;    // grid.x of the attention kernel (version 1: 4 chunks per CTA)
+    int n_chunks = 1;          // max(n_sh, n_own)
+    int n_sh = 0, n_own = 1;   // chunks of the shared prefix / of the longest own region (version 2 grid)
     int n_shared_tiles = 0;    // > 0 => cascade phase on
     int n_partials_max = 1;    // most partials any (slot, head) will have (fused merge capacity check)
     float inv_temp = 0.f;

@@ -176,6 +176,8 @@ struct AttnArgs {
     float* part_ml;             // [T][n_q][max_chunks][2]
     int max_chunks;
     float scale_log2;           // log2(e)/sqrt(hd)
+    // version 2 (attn_decode2.cuh): exact 1-D grid = n_kv * (grid_nsh + T * grid_nown) CTAs, no empty CTAs
+    int grid_nsh, grid_nown;
 };
 
 #ifndef RT_ATTN_STAGES
