@@ -45,7 +45,9 @@ enum { RT_FAMILY_LLAMA = 0, RT_FAMILY_QWEN2 = 1 };
 enum {
     RT_FLAG_NO_GRAPH = 1,        /* launch decode steps kernel by kernel instead of replaying a CUDA graph */
     RT_FLAG_NO_PREFIX_SHARE = 2, /* batch calls: do not share the common token prefix (every knight prefills and reads its own copy) */
-    RT_FLAG_PREFILL_VIA_DECODE = 4 /* debug: run prompts through the decode kernels in 32-token slabs instead of the tcgen05 prefill path */
+    RT_FLAG_PREFILL_VIA_DECODE = 4, /* debug: run prompts through the decode kernels in 32-token slabs instead of the tcgen05 prefill path */
+    RT_FLAG_PREFIX_CACHE = 8     /* keep the KV pages of past prompts and reuse the longest page-aligned common token prefix of a new
+                                    prompt (a knight's next-round prompt extends its last one: src/utils/prompt.ts:60-77) */
 };
 
 /* Model + runtime description.  Stands in for AdapterLocalConfig {endpoint, model, name?, source?}
@@ -103,6 +105,8 @@ typedef struct rt_result {
     double decode_ms;            /* CUDA-event time of the decode phase of the CALL */
     int32_t decode_steps;        /* decode steps timed in decode_ms */
     int32_t gpu_launches;        /* kernels this call launched (graph replays count their nodes) */
+    int32_t prefix_cached_tokens;/* prompt tokens whose KV came from the cross-call prefix cache (RT_FLAG_PREFIX_CACHE) */
+    int32_t reserved;
 } rt_result;
 
 typedef struct rt_model_info {

@@ -196,6 +196,41 @@ def test_real_architecture_truncated_depth_llama31_8b():
         assert g.prefix_shared_tokens in (0, 160)
 
 
+def test_cross_round_prefix_cache_reuses_a_knights_own_prompt():
+    """in the real flow knights speak one at a time (SEQ) and a knight's next-round prompt extends
+    its previous one (src/utils/prompt.ts:60-77).  With RT_FLAG_PREFIX_CACHE the engine keeps the prompt's KV pages and
+    prefills only the new tail; results must still match the oracle, and a small pool must evict instead of failing."""
+    name = "tiny-llama-hd128"
+    a = ARCHS[name]
+    oracle = OracleModel(a, 6, max_pos=512)
+    rng = np.random.default_rng(8)
+    heads = [rng.integers(0, a.vocab, 70 + 5 * k).tolist() for k in range(3)]      # three knights, distinct prompt heads
+    with E.Engine(name, seed=6, max_batch=1, max_ctx=512, flags=E.RT_FLAG_PREFIX_CACHE) as eng:
+        round1 = [eng.generate_ids([h], max_new_tokens=12)[0] for h in heads]
+        assert all(g.prefix_cached_tokens == 0 for g in round1)
+        prompts2 = [h + rng.integers(0, a.vocab, 40).tolist() for h in heads]      # transcript grew
+        round2 = [eng.generate_ids([p], max_new_tokens=12)[0] for p in prompts2]
+        for h, p, g in zip(heads, prompts2, round2):
+            assert g.prefix_cached_tokens == (len(h) // 16) * 16                   # whole pages of the old prompt
+            _greedy_compare(g.tokens, oracle, p, 12, err_bound=REL_TOL * 2.5)
+        again = eng.generate_ids([prompts2[0]], max_new_tokens=12)[0]              # identical prompt: all but the last page part
+        assert again.prefix_cached_tokens == ((len(prompts2[0]) - 1) // 16) * 16
+        _greedy_compare(again.tokens, oracle, prompts2[0], 12, err_bound=REL_TOL * 2.5)
+        # batch call: knight 0's pages come from the cache, the others share / prefill as usual
+        common = prompts2[0][:96]
+        batch = [common + rng.integers(0, a.vocab, 10 + i).tolist() for i in range(1)]
+        g = eng.generate_ids(batch, max_new_tokens=8)[0]
+        assert g.prefix_cached_tokens == 96
+        _greedy_compare(g.tokens, oracle, batch[0], 8, err_bound=REL_TOL * 2.5)
+    # pool of 40 pages (640 tokens): the third distinct 300-token prompt can only fit if older entries are evicted
+    kv_bytes = 40 * 2 * a.layers * a.n_kv * 16 * a.head_dim * 2
+    with E.Engine(name, seed=6, max_batch=1, max_ctx=512, flags=E.RT_FLAG_PREFIX_CACHE, kv_pool_bytes=kv_bytes) as eng:
+        for k in range(4):
+            p = rng.integers(0, a.vocab, 300).tolist()
+            g = eng.generate_ids([p], max_new_tokens=8)[0]
+            assert len(g.tokens) == 8 and g.prefix_cached_tokens == 0
+
+
 def test_temperature_sampling_is_seeded_and_varies():
     with E.Engine("tiny-llama", seed=1, max_batch=2, max_ctx=128) as eng:
         p = list(range(10, 40))

@@ -18,7 +18,7 @@ from __future__ import annotations
 import re
 from typing import Optional
 
-from .engine import Engine, EngineError
+from .engine import RT_FLAG_PREFIX_CACHE, Engine, EngineError
 
 
 class AdapterError(Exception):
@@ -85,7 +85,8 @@ class B200LocalLlmAdapter(BaseAdapter):
         self.max_new_tokens = max_new_tokens
         self.ignore_eos = ignore_eos
         self._engine = engine
-        self._engine_args = dict(seed=seed, max_batch=max_batch, max_ctx=max_ctx)
+        # the adapter keeps each knight's prompt KV between turns: its next prompt extends the last one (prompt.ts:60-77)
+        self._engine_args = dict(seed=seed, max_batch=max_batch, max_ctx=max_ctx, flags=RT_FLAG_PREFIX_CACHE)
         self._load_error: Optional[BaseException] = None
 
     # -- engine life cycle ----------------------------------------------------------------------

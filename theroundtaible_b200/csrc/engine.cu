@@ -385,6 +385,8 @@ void engine_init(rt_engine* e) {
     RT_CUDA(cudaMemsetAsync(e->kpool, 0, e->layer_pool_elems * e->L * sizeof(bf16), e->st));
     RT_CUDA(cudaMemsetAsync(e->vpool, 0, e->layer_pool_elems * e->L * sizeof(bf16), e->st));
     e->page_ref.assign(e->n_pages, 0);
+    e->free_pages.clear();
+    for (int p = e->n_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
     e->seq_pages.assign(e->n_seq, {});
     e->seq_len.assign(e->n_seq, 0);
     RT_CUDA(cudaMallocHost(&e->h_page_table, (size_t)e->n_seq * e->max_pages_per_seq * sizeof(int)));
@@ -496,13 +498,29 @@ void engine_free(rt_engine* e) {
 }
 
 // ---- page management ---------------------------------------------------------------------------------
+static void page_release(rt_engine* e, int p) {
+    if (--e->page_ref[p] == 0) e->free_pages.push_back(p);
+}
+
+// Drop every sequence's pages; pages still referenced by the prefix cache stay alive.
 void engine_reset_sequences(rt_engine* e) {
-    e->free_pages.clear();
-    for (int p = e->n_pages - 1; p >= 0; --p) e->free_pages.push_back(p);
-    std::fill(e->page_ref.begin(), e->page_ref.end(), 0);
-    for (auto& v : e->seq_pages) v.clear();
+    for (auto& v : e->seq_pages) {
+        for (int p : v) page_release(e, p);
+        v.clear();
+    }
     std::fill(e->seq_len.begin(), e->seq_len.end(), 0);
     e->scratch_active = false;
+}
+
+// Evict the least recently used prefix-cache entry; false if the cache is empty.
+static bool cache_evict_one(rt_engine* e) {
+    if (e->cache.empty()) return false;
+    size_t lru = 0;
+    for (size_t i = 1; i < e->cache.size(); ++i)
+        if (e->cache[i].stamp < e->cache[lru].stamp) lru = i;
+    for (int p : e->cache[lru].pages) page_release(e, p);
+    e->cache.erase(e->cache.begin() + lru);
+    return true;
 }
 
 void engine_alloc_pages(rt_engine* e, int seq, int n_tokens_total) {
@@ -512,13 +530,74 @@ void engine_alloc_pages(rt_engine* e, int seq, int n_tokens_total) {
                                       " tokens but max_ctx is " + std::to_string(e->cfg.max_ctx));
     auto& pages = e->seq_pages[seq];
     while ((int)pages.size() < need) {
-        if (e->free_pages.empty()) throw RtError(RT_ERR_OOM, "context length exceeded: KV page pool exhausted");
+        while (e->free_pages.empty())
+            if (!cache_evict_one(e)) throw RtError(RT_ERR_OOM, "context length exceeded: KV page pool exhausted");
         const int p = e->free_pages.back();
         e->free_pages.pop_back();
         e->page_ref[p] = 1;
         e->h_page_table[(size_t)seq * e->max_pages_per_seq + pages.size()] = p;
         pages.push_back(p);
     }
+}
+
+// ---- cross-call prefix cache -------------------------------------------------------
+// The reference rebuilds every knight's prompt each turn; its head is constant and the transcript is append-only
+// (/root/reference/src/utils/prompt.ts:60-77), so a knight's round r+1 prompt starts with its round r prompt up to
+// the end of the old transcript.  Entries keep the token ids of a past prompt and the pages that hold its KV (whole
+// pages only); a new prompt reuses the longest page-aligned common token prefix and prefills only the rest.
+static int cache_lookup(rt_engine* e, const int32_t* prompt, int len, int* entry_out) {
+    int best = 0, best_i = -1;
+    for (size_t i = 0; i < e->cache.size(); ++i) {
+        const auto& t = e->cache[i].tokens;
+        const int lim = std::min((int)e->cache[i].pages.size() * KV_PAGE, std::min((int)t.size(), len - 1));
+        int l = 0;
+        while (l < lim && t[l] == prompt[l]) ++l;
+        l = (l / KV_PAGE) * KV_PAGE;
+        if (l > best) { best = l; best_i = (int)i; }
+    }
+    *entry_out = best_i;
+    return best;
+}
+
+// seq (empty) takes the first n_tokens/16 pages of a cache entry
+static void cache_attach(rt_engine* e, int entry, int seq, int n_tokens) {
+    auto& dst = e->seq_pages[seq];
+    RT_REQUIRE(dst.empty(), "cache_attach target must be empty");
+    auto& ce = e->cache[entry];
+    ce.stamp = ++e->cache_clock;
+    for (int i = 0; i < n_tokens / KV_PAGE; ++i) {
+        const int p = ce.pages[i];
+        e->page_ref[p]++;
+        e->h_page_table[(size_t)seq * e->max_pages_per_seq + i] = p;
+        dst.push_back(p);
+    }
+}
+
+// remember the prompt of seq (its KV is complete for positions < len)
+static void cache_insert(rt_engine* e, int seq, const int32_t* prompt, int len) {
+    const int n_pages = len / KV_PAGE;
+    if (n_pages == 0) return;
+    // an existing entry that already covers this prompt is only refreshed; entries this one extends are replaced
+    for (size_t i = 0; i < e->cache.size();) {
+        auto& ce = e->cache[i];
+        const int common = std::min((int)ce.pages.size(), n_pages) * KV_PAGE;
+        bool same = (int)ce.tokens.size() >= common;
+        for (int l = 0; same && l < common; ++l) same = ce.tokens[l] == prompt[l];
+        if (same && (int)ce.pages.size() >= n_pages) { ce.stamp = ++e->cache_clock; return; }
+        if (same) {
+            for (int p : ce.pages) page_release(e, p);
+            e->cache.erase(e->cache.begin() + i);
+        } else {
+            ++i;
+        }
+    }
+    while (e->cache.size() >= 16) cache_evict_one(e);
+    rt_engine::CacheEntry ne;
+    ne.tokens.assign(prompt, prompt + n_pages * KV_PAGE);
+    ne.pages.assign(e->seq_pages[seq].begin(), e->seq_pages[seq].begin() + n_pages);
+    for (int p : ne.pages) e->page_ref[p]++;
+    ne.stamp = ++e->cache_clock;
+    e->cache.push_back(std::move(ne));
 }
 
 void engine_share_prefix(rt_engine* e, int from_seq, int to_seq, int n_pages) {
@@ -914,10 +993,25 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
         }
         shared = (lc / KV_PAGE) * KV_PAGE;
     }
-    // pages
-    engine_alloc_pages(e, 0, lens[0] + s.max_new_tokens);
-    for (int i = 1; i < n; ++i) {
-        engine_share_prefix(e, 0, i, shared / KV_PAGE);
+    // pages: cached prefix (if any) -> batch-shared prefix -> fresh pages
+    const bool use_cache = (e->cfg.flags & RT_FLAG_PREFIX_CACHE) != 0;
+    std::vector<int> start(n, 0);          // first prompt position each sequence still has to prefill itself
+    std::vector<int> cached(n, 0);
+    for (int i = 0; i < n; ++i) {
+        int entry = -1;
+        const int hit = use_cache ? cache_lookup(e, prompts[i], lens[i], &entry) : 0;
+        if (i == 0) {
+            if (hit > 0) cache_attach(e, entry, 0, hit);
+            cached[0] = hit;
+            start[0] = std::max(hit, shared);       // [hit, shared) is prefilled once, as the batch-shared part
+        } else if (hit > shared) {
+            cache_attach(e, entry, i, hit);
+            cached[i] = hit;
+            start[i] = hit;
+        } else {
+            engine_share_prefix(e, 0, i, shared / KV_PAGE);
+            start[i] = shared;
+        }
         engine_alloc_pages(e, i, lens[i] + s.max_new_tokens);
     }
     engine_upload_page_table(e);
@@ -934,9 +1028,9 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     RT_CUDA(cudaEventRecord(e->ev[0], e->st));
     {
         std::vector<int> tok, seq, pos, want;
-        for (int p = 0; p < shared; ++p) { tok.push_back(prompts[0][p]); seq.push_back(0); pos.push_back(p); want.push_back(-1); }
+        for (int p = cached[0]; p < shared; ++p) { tok.push_back(prompts[0][p]); seq.push_back(0); pos.push_back(p); want.push_back(-1); }
         for (int i = 0; i < n; ++i)
-            for (int p = shared; p < lens[i]; ++p) {
+            for (int p = start[i]; p < lens[i]; ++p) {
                 tok.push_back(prompts[i][p]); seq.push_back(i); pos.push_back(p);
                 want.push_back(p == lens[i] - 1 ? i : -1);
             }
@@ -1018,6 +1112,8 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     RT_CUDA(cudaEventElapsedTime(&pre_ms, e->ev[0], e->ev[1]));
     RT_CUDA(cudaEventElapsedTime(&dec_ms, e->ev[2], e->ev[3]));
 
+    if (use_cache)
+        for (int i = 0; i < n; ++i) cache_insert(e, i, prompts[i], lens[i]);
     const int produced = steps_done + 1;
     for (int i = 0; i < n; ++i) {
         RT_CUDA(cudaMemcpy(host_out.data() + (size_t)i * s.max_new_tokens, e->d_out_tokens + (size_t)i * e->max_out,
@@ -1039,7 +1135,8 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
         memcpy(r.text, text.c_str(), text.size() + 1);
         r.text_len = text.size();
         r.n_prompt_tokens = lens[i];
-        r.prefix_shared_tokens = i == 0 ? 0 : shared;
+        r.prefix_shared_tokens = (i == 0 || cached[i] > shared) ? 0 : shared;
+        r.prefix_cached_tokens = cached[i];
         r.finish_reason = finish[i];
         r.prefill_ms = pre_ms;
         r.decode_ms = dec_ms;

@@ -62,6 +62,14 @@ struct rt_engine {
     int* h_page_table = nullptr;  // pinned [n_seq][max_pages_per_seq]
     int* d_page_table = nullptr;
     std::vector<int> seq_len;
+    // cross-call prefix cache: token ids of past prompts + the pages holding their KV (ref-counted)
+    struct CacheEntry {
+        std::vector<int> tokens;
+        std::vector<int> pages;
+        long long stamp = 0;
+    };
+    std::vector<CacheEntry> cache;
+    long long cache_clock = 0;
 
     // step state (device)
     int *d_tok = nullptr, *d_seq = nullptr, *d_pos = nullptr, *d_shared_len = nullptr, *d_step = nullptr;

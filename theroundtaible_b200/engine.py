@@ -16,6 +16,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_lib", "li
 RT_FLAG_NO_GRAPH = 1
 RT_FLAG_NO_PREFIX_SHARE = 2
 RT_FLAG_PREFILL_VIA_DECODE = 4
+RT_FLAG_PREFIX_CACHE = 8
 
 RT_ERR_TIMEOUT = -4
 RT_ERR_OOM = -3
@@ -42,7 +43,8 @@ class RtResult(C.Structure):
     _fields_ = [("text", C.POINTER(C.c_char)), ("text_len", C.c_size_t), ("tokens", C.POINTER(C.c_int32)),
                 ("n_tokens", C.c_int32), ("n_prompt_tokens", C.c_int32), ("prefix_shared_tokens", C.c_int32),
                 ("finish_reason", C.c_int32), ("prefill_ms", C.c_double), ("decode_ms", C.c_double),
-                ("decode_steps", C.c_int32), ("gpu_launches", C.c_int32)]
+                ("decode_steps", C.c_int32), ("gpu_launches", C.c_int32), ("prefix_cached_tokens", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 class RtModelInfo(C.Structure):
@@ -133,6 +135,7 @@ class Generation:
     decode_ms: float
     decode_steps: int
     gpu_launches: int
+    prefix_cached_tokens: int = 0
 
 
 def _p(arr: np.ndarray, ctype):
@@ -192,7 +195,7 @@ class Engine:
             toks = [r.tokens[k] for k in range(r.n_tokens)]
             text = C.string_at(r.text, r.text_len).decode("utf-8", "replace")
             out.append(Generation(text, toks, r.n_prompt_tokens, r.prefix_shared_tokens, r.finish_reason, r.prefill_ms,
-                                  r.decode_ms, r.decode_steps, r.gpu_launches))
+                                  r.decode_ms, r.decode_steps, r.gpu_launches, r.prefix_cached_tokens))
             self._lib.rt_result_free(C.byref(res[i]))
         return out
 
