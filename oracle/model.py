@@ -14,8 +14,9 @@ Rounding points (they mirror the engine so that parity can be tight):
   * K (after RoPE) and V are rounded to bf16 when they enter the KV cache, and every
     attention read -- including the current token's own K/V -- sees the rounded values
     (``round_kv``);
-  * with ``round_act`` (the engine's tensor-core prefill path) the inputs of every matmul
-    (normed hidden, attention output, SwiGLU output) and Q are rounded to bf16;
+  * with ``round_act`` the inputs of every matmul (x * norm weight -- the RMSNorm scalar r is applied
+    to the projection's output, see ``_rms_split`` --, attention output, SwiGLU output) and Q are
+    rounded to bf16;
   * everything else (residual stream, softmax, accumulation) is fp32.
 """
 from __future__ import annotations
@@ -88,6 +89,15 @@ class OracleModel:
         var = (x * x).mean(-1, keepdim=True)
         return x * torch.rsqrt(var + self.a.rms_eps) * w
 
+    def _rms_split(self, x, w):
+        """RMSNorm(x)·w factored as (x*w, r) with r = rsqrt(mean x^2 + eps): the per-row scalar r commutes
+        with the projection that follows, so ``(x*w) @ W.T * r`` is the same function as
+        ``_rms(x, w) @ W.T`` (modeling_llama.py LlamaRMSNorm + the Linear after it).  The engine rounds
+        x*w to bf16 and applies r to the fp32 accumulators; with ``round_act`` the oracle rounds at the
+        same point."""
+        var = (x * x).mean(-1, keepdim=True)
+        return x * w, torch.rsqrt(var + self.a.rms_eps)
+
     def _rope(self, t, pos):  # t [T, heads, hd]; pos LongTensor [T]
         hd = self.a.head_dim
         c = self.cos[pos][:, None, :]
@@ -116,10 +126,11 @@ class OracleModel:
             kv.v = [torch.zeros(a.n_kv, 0, a.head_dim) for _ in range(a.layers)]
         for l in range(a.layers):
             p = f"l{l}."
-            h = ra(self._rms(x, sd[p + "in_norm"]))
-            q = h @ sd[p + "q"].T
-            k = h @ sd[p + "k"].T
-            v = h @ sd[p + "v"].T
+            h, r = self._rms_split(x, sd[p + "in_norm"])
+            h = ra(h)
+            q = (h @ sd[p + "q"].T) * r
+            k = (h @ sd[p + "k"].T) * r
+            v = (h @ sd[p + "v"].T) * r
             if a.qkv_bias:
                 q = q + sd[p + "q_bias"]
                 k = k + sd[p + "k_bias"]
@@ -143,16 +154,17 @@ class OracleModel:
             o = torch.bmm(pr, V).view(a.n_kv, G, T, a.head_dim)
             o = o.permute(2, 0, 1, 3).reshape(T, a.n_q * a.head_dim)
             x = x + ra(o) @ sd[p + "o"].T
-            h = ra(self._rms(x, sd[p + "post_norm"]))
-            g = h @ sd[p + "gate"].T
-            u = h @ sd[p + "up"].T
+            h, r = self._rms_split(x, sd[p + "post_norm"])
+            h = ra(h)
+            g = (h @ sd[p + "gate"].T) * r
+            u = (h @ sd[p + "up"].T) * r
             act = torch.nn.functional.silu(g) * u
             x = x + ra(act) @ sd[p + "down"].T
         kv.length = p0 + T
         if last_only:
             x = x[-1:]
-        xf = ra(self._rms(x, sd["final_norm"]))
-        return xf @ sd["lm_head"].T
+        xf, r = self._rms_split(x, sd["final_norm"])
+        return (ra(xf) @ sd["lm_head"].T) * r
 
     @torch.no_grad()
     def generate(self, prompt_ids, max_new_tokens: int, kv: KVState | None = None, round_act: bool = True,
@@ -214,8 +226,9 @@ def decode_step_batch(m: OracleModel, tokens, kvs, round_act: bool = True) -> to
     scale = 1.0 / math.sqrt(a.head_dim)
     for l in range(a.layers):
         p = f"l{l}."
-        h = ra(m._rms(x, sd[p + "in_norm"]))
-        q, k, v = h @ sd[p + "q"].T, h @ sd[p + "k"].T, h @ sd[p + "v"].T
+        h, r = m._rms_split(x, sd[p + "in_norm"])
+        h = ra(h)
+        q, k, v = (h @ sd[p + "q"].T) * r, (h @ sd[p + "k"].T) * r, (h @ sd[p + "v"].T) * r
         if a.qkv_bias:
             q, k, v = q + sd[p + "q_bias"], k + sd[p + "k_bias"], v + sd[p + "v_bias"]
         q = ra(m._rope(q.view(B, a.n_q, a.head_dim), pos))
@@ -230,9 +243,11 @@ def decode_step_batch(m: OracleModel, tokens, kvs, round_act: bool = True) -> to
             o = torch.bmm(torch.softmax(s, dim=-1), kv.v[l])
             outs.append(o.reshape(a.n_q * a.head_dim))
         x = x + ra(torch.stack(outs)) @ sd[p + "o"].T
-        h = ra(m._rms(x, sd[p + "post_norm"]))
-        act = torch.nn.functional.silu(h @ sd[p + "gate"].T) * (h @ sd[p + "up"].T)
+        h, r = m._rms_split(x, sd[p + "post_norm"])
+        h = ra(h)
+        act = torch.nn.functional.silu((h @ sd[p + "gate"].T) * r) * ((h @ sd[p + "up"].T) * r)
         x = x + ra(act) @ sd[p + "down"].T
     for kv in kvs:
         kv.length += 1
-    return ra(m._rms(x, sd["final_norm"])) @ sd["lm_head"].T
+    xf, r = m._rms_split(x, sd["final_norm"])
+    return (ra(xf) @ sd["lm_head"].T) * r

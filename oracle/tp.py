@@ -35,10 +35,11 @@ def forward_tp(m: OracleModel, ids, kv: KVState, rank: int, tp: int):
     rows = lambda t, n: t[rank * n:(rank + 1) * n]
     for l in range(a.layers):
         p = f"l{l}."
-        h = _rbf16(m._rms(x, sd[p + "in_norm"]))
-        q = h @ rows(sd[p + "q"], nq * hd).T
-        k = h @ rows(sd[p + "k"], nkv * hd).T
-        v = h @ rows(sd[p + "v"], nkv * hd).T
+        h, r = m._rms_split(x, sd[p + "in_norm"])
+        h = _rbf16(h)
+        q = (h @ rows(sd[p + "q"], nq * hd).T) * r
+        k = (h @ rows(sd[p + "k"], nkv * hd).T) * r
+        v = (h @ rows(sd[p + "v"], nkv * hd).T) * r
         if a.qkv_bias:
             q, k, v = q + rows(sd[p + "q_bias"], nq * hd), k + rows(sd[p + "k_bias"], nkv * hd), v + rows(sd[p + "v_bias"], nkv * hd)
         q = _rbf16(m._rope(q.view(T, nq, hd), pos))
@@ -57,13 +58,15 @@ def forward_tp(m: OracleModel, ids, kv: KVState, rank: int, tp: int):
         part = o @ sd[p + "o"][:, rank * nq * hd:(rank + 1) * nq * hd].T          # row-parallel partial sum
         dist.all_reduce(part)
         x = x + part
-        h = _rbf16(m._rms(x, sd[p + "post_norm"]))
-        act = torch.nn.functional.silu(h @ rows(sd[p + "gate"], F).T) * (h @ rows(sd[p + "up"], F).T)
+        h, r = m._rms_split(x, sd[p + "post_norm"])
+        h = _rbf16(h)
+        act = torch.nn.functional.silu((h @ rows(sd[p + "gate"], F).T) * r) * ((h @ rows(sd[p + "up"], F).T) * r)
         part = _rbf16(act) @ sd[p + "down"][:, rank * F:(rank + 1) * F].T
         dist.all_reduce(part)
         x = x + part
     kv.length = p0 + T
-    return _rbf16(m._rms(x, sd["final_norm"])) @ rows(sd["lm_head"], V).T
+    xf, r = m._rms_split(x, sd["final_norm"])
+    return (_rbf16(xf) @ rows(sd["lm_head"], V).T) * r
 
 
 def argmax_tp(local_logits: torch.Tensor, rank: int, tp: int) -> list:

@@ -219,7 +219,7 @@ void gemv_stream_launch(rt_engine* e, const GemvArgs& a, int grid) {
 
 template <int EPI>
 int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
-    if (e->use_stream && e->gs_scratch) {
+    if (e->use_stream && e->gs_scratch && EPI == EPI_STORE && !a.ss_in && !a.inv_rms) {
         // persistent stream-K kernel: one CTA per SM, equal contiguous byte ranges; candidates are per 16-row tile
         const long long units = (long long)(a.N / 16) * (a.K / 32);
         const int grid = (int)std::min<long long>(e->sm_count, units);
@@ -419,6 +419,8 @@ void engine_init(rt_engine* e) {
     e->act_bf = zalloc_b((size_t)MAX_SLOTS * e->F_l);
     e->part_o = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * e->hd);
     e->part_ml = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * 2);
+    e->ss_part = zalloc_f((size_t)(e->H / 16) * 32);
+    e->inv_rms = zalloc_f(MAX_SLOTS);
     e->done_counter = dalloc<int>(e, 1);
     RT_CUDA(cudaMemsetAsync(e->done_counter, 0, sizeof(int), e->st));
     e->use_pdl = getenv("RT_NO_PDL") == nullptr;
@@ -457,6 +459,7 @@ void engine_init(rt_engine* e) {
     e->pf_attn = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
     e->pf_act = zalloc_b((size_t)e->pf_cap * e->F_l);
     if (c.tp_size > 1) e->pf_delta = zalloc_f((size_t)e->pf_cap * e->H);
+    e->pf_inv_rms = zalloc_f(e->pf_cap);
     e->pf_tok = dalloc<int>(e, e->pf_cap);
     e->pf_seq = dalloc<int>(e, e->pf_cap);
     e->pf_pos = dalloc<int>(e, e->pf_cap);
@@ -640,23 +643,32 @@ static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, c
             a.flags[p] = reinterpret_cast<int*>(e->tpf_peer_flags[p]);
         }
         a.epoch = e->tpf_epoch; a.rank = e->cfg.tp_rank; a.tp = e->cfg.tp_size; a.H = H;
-        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.eps = e->cfg.rms_eps;
+        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.inv_rms = e->inv_rms; a.eps = e->cfg.rms_eps;
         launch_pdl(e, tp_fused_allreduce_norm_kernel<512>, dim3(T), dim3(512), 0, a);
     } else {
         g.out = e->delta; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
         tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
-        rmsnorm_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, H, H, e->cfg.rms_eps);
+        rms_xw_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, e->inv_rms, H, e->cfg.rms_eps);
         e->launches += 2;
     }
+}
+
+// where the consuming projection finds the RMSNorm scale of e->xn's rows: per-tile partial sums (single-GPU decode:
+// the producing projection left them) or r itself (tensor parallel / rows copied from a prefill chunk)
+static void set_norm_scale(rt_engine* e, GemvArgs& g, bool direct) {
+    g.eps = e->cfg.rms_eps;
+    if (direct || e->tp) g.inv_rms = e->inv_rms;
+    else { g.ss_in = e->ss_part; g.n_parts_in = e->H / 16; }
 }
 
 // lm_head over the T rows of e->xn + sampling.  Single GPU: the projection's last CTA picks the winners and advances
 // the decode state.  Tensor parallel: vocab-parallel local winners -> all-gather -> tp_pick_kernel on every rank.
 static void lm_head_and_sample(rt_engine* e, int T, bool sample, bool advance, bool store_logits, float inv_temp,
-                               unsigned long long seed) {
+                               unsigned long long seed, bool direct_scale = false) {
     GemvArgs gl{};
     gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = e->H; gl.T = T; gl.X = e->xn; gl.ldx = e->H;
+    set_norm_scale(e, gl, direct_scale);
     gl.logits = store_logits ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
     gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
     gl.inv_temp = inv_temp; gl.seed = seed; gl.step_ptr = e->d_step;
@@ -695,7 +707,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
     static const int skip = env_int("RT_SKIP_MASK", 0);
 
     launch_pdl(e, embed_norm_kernel, dim3(T), dim3(256), 0, (const bf16*)e->embed, (const int*)e->d_tok, e->x,
-               (const bf16*)e->layers[0].norm1, e->xn, H, e->vocab, e->cfg.rms_eps);
+               (const bf16*)e->layers[0].norm1, e->xn, e->ss_part, e->inv_rms, H, e->vocab, e->cfg.rms_eps);
 
     for (int l = 0; l < e->L; ++l) {
         const LayerW& w = e->layers[l];
@@ -703,6 +715,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
 
         GemvArgs g{};
+        set_norm_scale(e, g, false);
         g.W = w.wqkv; g.N = e->qkv_rows; g.K = H; g.T = T; g.X = e->xn; g.ldx = H;
         g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t; g.slot_seq = e->d_seq; g.slot_pos = e->d_pos;
         g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq; g.Q = e->qb; g.Kp = kp; g.Vp = vp;
@@ -736,7 +749,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         go.W = w.wo; go.X = e->attn_bf; go.N = H; go.K = e->nq_l * hd; go.ldx = e->nq_l * hd; go.T = T;
         if (!e->tp) {
             go.out = e->x; go.ldo = H;
-            go.norm_w = w.norm2; go.xn_out = e->xn; go.done_counter = e->done_counter; go.eps = e->cfg.rms_eps;
+            go.norm_w = w.norm2; go.xn_out = e->xn; go.ss_out = e->ss_part;
             if (!(skip & 8)) gemv_dispatch<EPI_RESID>(e, go);
         } else {
             tp_reduce_residual_norm(e, go, 0, T, w.norm2);
@@ -744,6 +757,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
 
         GemvArgs gu{};
         gu.W = w.wgu; gu.N = 2 * e->F_l; gu.K = H; gu.T = T; gu.X = e->xn; gu.ldx = H;
+        set_norm_scale(e, gu, false);
         gu.out_bf = e->act_bf; gu.ldob = e->F_l;
         if (!(skip & 16)) gemv_dispatch<EPI_SWIGLU>(e, gu);
 
@@ -752,7 +766,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         const bf16* next_norm = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;   // feeds the next layer's QKV, or the lm_head
         if (!e->tp) {
             gd.out = e->x; gd.ldo = H;
-            gd.norm_w = next_norm; gd.xn_out = e->xn; gd.done_counter = e->done_counter; gd.eps = e->cfg.rms_eps;
+            gd.norm_w = next_norm; gd.xn_out = e->xn; gd.ss_out = e->ss_part;
             if (!(skip & 32)) gemv_dispatch<EPI_RESID>(e, gd);
         } else {
             tp_reduce_residual_norm(e, gd, 1, T, next_norm);
@@ -853,13 +867,13 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
         RT_CUDA(cudaMemcpyAsync(e->pf_work, hw, (size_t)n_items * sizeof(int4), cudaMemcpyHostToDevice, e->st));
 
         launch_pdl(e, embed_norm_kernel, dim3(S), dim3(256), 0, (const bf16*)e->embed, (const int*)e->pf_tok, e->pf_x,
-                   (const bf16*)e->layers[0].norm1, e->pf_xn, H, e->vocab, e->cfg.rms_eps);
+                   (const bf16*)e->layers[0].norm1, e->pf_xn, (float*)nullptr, e->pf_inv_rms, H, e->vocab, e->cfg.rms_eps);
         for (int l = 0; l < e->L; ++l) {
             const LayerW& w = e->layers[l];
             bf16* kp = e->kpool + (size_t)l * e->layer_pool_elems;
             bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
             Gemm5Args g{};
-            g.S = S; g.N = e->qkv_rows; g.K = H; g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t;
+            g.S = S; g.N = e->qkv_rows; g.K = H; g.row_scale = e->pf_inv_rms; g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t;
             g.tok_seq = e->pf_seq; g.tok_pos = e->pf_pos; g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq;
             g.Q = e->pf_q; g.Kp = kp; g.Vp = vp; g.n_q = e->nq_l; g.n_kv = e->nkv_l; g.hd = hd;
             pf_gemm(e->st, pdl, G5_EPI_QKV, e->map_xn, e->map_w[4 * l + 0], g);
@@ -877,11 +891,11 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             go.out = e->tp ? e->pf_delta : e->pf_x;
             pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
             if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
-            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, w.norm2, e->pf_xn, H, H, e->cfg.rms_eps);
+            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, w.norm2, e->pf_xn, e->pf_inv_rms, H, e->cfg.rms_eps);
             e->launches += 2;
 
             Gemm5Args gu{};
-            gu.S = S; gu.N = 2 * e->F_l; gu.K = H; gu.out_bf = e->pf_act; gu.ldob = e->F_l;
+            gu.S = S; gu.N = 2 * e->F_l; gu.K = H; gu.row_scale = e->pf_inv_rms; gu.out_bf = e->pf_act; gu.ldob = e->F_l;
             pf_gemm(e->st, pdl, G5_EPI_SWIGLU, e->map_xn, e->map_w[4 * l + 2], gu);
             Gemm5Args gd{};
             gd.S = S; gd.N = H; gd.K = e->F_l; gd.ldo = H;
@@ -889,7 +903,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
             if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
             const bf16* nw = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;
-            rmsnorm_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, nw, e->pf_xn, H, H, e->cfg.rms_eps);
+            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, nw, e->pf_xn, e->pf_inv_rms, H, e->cfg.rms_eps);
             e->launches += 3;
         }
         RT_CUDA(cudaGetLastError());
@@ -898,9 +912,12 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
         auto lm_head_rows = [&](const std::vector<int>& rows, bool sample, bool store) {
             const int T = (int)rows.size();
             for (int j = 0; j < T; ++j)
+            {
                 RT_CUDA(cudaMemcpyAsync(e->xn + (size_t)j * H, e->pf_xn + (size_t)rows[j] * H, (size_t)H * sizeof(bf16),
                                         cudaMemcpyDeviceToDevice, e->st));
-            lm_head_and_sample(e, T, sample, false, store, base.inv_temp, base.seed);
+                RT_CUDA(cudaMemcpyAsync(e->inv_rms + j, e->pf_inv_rms + rows[j], sizeof(float), cudaMemcpyDeviceToDevice, e->st));
+            }
+            lm_head_and_sample(e, T, sample, false, store, base.inv_temp, base.seed, true);
         };
         if (logits_out) {
             for (int r0 = 0; r0 < S; r0 += MAX_SLOTS) {

@@ -81,6 +81,9 @@ struct rt_engine {
     float *x = nullptr, *qkv = nullptr, *delta = nullptr, *logits = nullptr;
     bf16 *xn = nullptr, *qb = nullptr, *attn_bf = nullptr, *act_bf = nullptr;
     float *part_o = nullptr, *part_ml = nullptr;
+    float* ss_part = nullptr;      // [H/16][32] per-tile partial sums of x^2 (split RMSNorm, gemv.cuh)
+    float* inv_rms = nullptr;      // [32] r per slot when a whole row was available (tensor parallel, prefill rows)
+    float* pf_inv_rms = nullptr;   // [pf_cap]
     int* done_counter = nullptr;   // arrival counter of the residual projections' fused RMSNorm tail
     bool use_pdl = true;
     bool use_stream = false;       // persistent TMA-fed stream-K projection kernel (gemv_stream.cuh)

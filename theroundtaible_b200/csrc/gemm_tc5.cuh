@@ -180,6 +180,11 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
             tc5_ld32(tmem_d + ((uint32_t)(quad * 32) << 16) + c * 32, v);
             const int n0 = n_blk * BN + c * 32;
             if (!row_ok || n0 >= a.N) continue;
+            if (a.row_scale) {
+                const float rs = a.row_scale[m];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] *= rs;
+            }
             if (EPI == G5_EPI_RESID || EPI == G5_EPI_STORE) {
                 float4* o = reinterpret_cast<float4*>(a.out + (size_t)m * a.ldo + n0);
 #pragma unroll

@@ -19,8 +19,8 @@
 // loads are issued BEFORE griddepcontrol.wait, so the HBM stream keeps running across kernel boundaries.
 //
 // Fusions: EPI_QKV    -> + bias, RoPE, q -> bf16 Q buffer, k/v -> bf16 into their KV page;
-//          EPI_RESID  -> x += acc; the last CTA to finish then RMS-normalises the updated rows into the bf16
-//                        input of the next projection (no separate RMSNorm launch);
+//          EPI_RESID  -> x += acc, xw = bf16(x * w_next) and per-tile partial sums of x^2: the next projection applies
+//                        the RMSNorm scale to its accumulators (no RMSNorm launch, no tail);
 //          EPI_SWIGLU -> bf16(silu(gate) * up);   EPI_LOGITS -> logits and per-CTA arg-max candidates.
 #pragma once
 #include "common.cuh"
@@ -35,11 +35,17 @@ struct GemvArgs {
     // B operand
     const bf16* X;            // !NORM: [>=NT*8][ldx] bf16 (rows >= T readable, finite)
     int ldx;
-    // RESID "norm tail": the LAST CTA to finish the residual update normalises the new rows for the next
-    // projection (xn_out = bf16(x * rsqrt(mean x^2 + eps) * norm_w)), so no separate RMSNorm launch exists
-    const bf16* norm_w;       // [N] nullable => no tail
-    bf16* xn_out;             // [T][N]
-    int* done_counter;        // zero before the first launch; reset by the last CTA
+    // RMSNorm is split around the projections ("scale after the matmul"): the PRODUCER of the residual stream (RESID
+    // epilogue, embed kernel) writes xw = bf16(x * norm_w) per element plus the per-16-row-tile partial sums of x^2; the
+    // CONSUMER projection multiplies its accumulators by r = rsqrt(mean x^2 + eps) in the epilogue.  No kernel ever
+    // waits for a whole row, so there is no RMSNorm launch and no last-CTA tail on the critical path.
+    const bf16* norm_w;       // RESID: weight of the NEXT norm [N]; nullable => no xw / partial sums
+    bf16* xn_out;             // RESID: xw out [T][N]
+    float* ss_out;            // RESID: [N/16][32] partial sums of x^2 of the updated rows
+    const float* ss_in;       // consumer: partial sums [n_parts_in][32] of the rows behind X (nullable)
+    int n_parts_in;
+    const float* inv_rms;     // consumer alternative: r per slot given directly [T] (tensor-parallel / prefill paths)
+    int* done_counter;        // LOGITS sampler tail: arrival counter (zero before the first launch; reset by the last CTA)
     float eps;
     // outputs
     float* out;               // STORE: out[t*ldo+n] = acc (+bias) ; RESID: out[t*ldo+n] += acc
@@ -144,6 +150,24 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     griddep_launch();
     griddep_wait();
 
+    // RMSNorm scale of every slot (used in the epilogue only: these loads overlap the weight stream)
+    if (a.ss_in || a.inv_rms) {
+        for (int s = warp; s < NT * 8; s += NW) {
+            float v = 0.f;
+            if (s < a.T) {
+                if (a.inv_rms) {
+                    v = lane == 0 ? a.inv_rms[s] : 0.f;
+                } else {
+                    for (int p = lane; p < a.n_parts_in; p += 32) v += a.ss_in[p * 32 + s];
+                }
+            }
+            v = warp_sum(v);
+            if (lane == 0) s_rn[s] = s >= a.T ? 0.f : (a.inv_rms ? v : 1.0f / sqrtf(v / (float)a.K + a.eps));
+        }
+    } else if (threadIdx.x < NT * 8) {
+        s_rn[threadIdx.x] = 1.0f;
+    }
+
     for (int kbb = kb0; kbb < kb1; kbb += U) {
         // B operand for this batch
         uint4 xv[U][NT];
@@ -220,7 +244,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             const int r = e % (MT * 16), s = e / (MT * 16);
             const int n = row0 + r;
             if (s < a.T && n < a.N) {
-                float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] * s_rn[s];
                 if (a.bias) v += a.bias[n];
                 a.out[(size_t)s * a.ldo + n] = v;
             }
@@ -233,91 +257,25 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 float* o = a.out + (size_t)s * a.ldo + n;
                 const float v = *o + res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
                 *o = v;
+                if (a.norm_w) {
+                    a.xn_out[(size_t)s * a.N + n] = __float2bfloat16_rn(v * __bfloat162float(a.norm_w[n]));
+                    res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] = v;
+                }
             }
         }
         if (a.norm_w) {
-            __threadfence();
             __syncthreads();
-            if (threadIdx.x == 0) s_last = atomicAdd(a.done_counter, 1) == (int)gridDim.x - 1;
-            __syncthreads();
-            if (s_last) {
-                __threadfence();
-                // every row of x is final: normalise the T slots for the next projection (fixed summation order).
-                // Fast path: 4 slots at a time, each thread holds its <= 4 float4 of every slot in registers, so the
-                // whole tail is one L2 round trip + one block reduction per group.
-                const int n4 = a.N >> 2;
-                constexpr int PER = 4, SG = 4;
-                float* sred = &res[0][0][0];                       // >= 128 floats; NW * SG <= 64 used
-                if (n4 <= PER * NTHR) {
-                    for (int s0 = 0; s0 < a.T; s0 += SG) {
-                        float4 v[SG][PER];
-                        float ss[SG];
+            for (int e = threadIdx.x; e < MT * NT * 8; e += NTHR) {
+                const int mt = e / (NT * 8), s = e % (NT * 8);
+                if (s < a.T && (tile0 + mt) * 16 < a.N) {
+                    float ss = 0.f;
 #pragma unroll
-                        for (int sl = 0; sl < SG; ++sl) {
-                            ss[sl] = 0.f;
-#pragma unroll
-                            for (int k = 0; k < PER; ++k) {
-                                const int c4 = threadIdx.x + k * NTHR;
-                                if (s0 + sl < a.T && c4 < n4) {
-                                    v[sl][k] = __ldcg(reinterpret_cast<const float4*>(a.out + (size_t)(s0 + sl) * a.ldo) + c4);
-                                    ss[sl] += v[sl][k].x * v[sl][k].x + v[sl][k].y * v[sl][k].y + v[sl][k].z * v[sl][k].z +
-                                              v[sl][k].w * v[sl][k].w;
-                                } else {
-                                    v[sl][k] = make_float4(0.f, 0.f, 0.f, 0.f);
-                                }
-                            }
-                        }
-#pragma unroll
-                        for (int sl = 0; sl < SG; ++sl) {
-                            ss[sl] = warp_sum(ss[sl]);
-                            if (lane == 0) sred[warp * SG + sl] = ss[sl];
-                        }
-                        __syncthreads();
-#pragma unroll
-                        for (int sl = 0; sl < SG; ++sl) {
-                            float tot = 0.f;
-                            for (int w = 0; w < NW; ++w) tot += sred[w * SG + sl];
-                            const float r = 1.0f / sqrtf(tot / (float)a.N + a.eps);
-#pragma unroll
-                            for (int k = 0; k < PER; ++k) {
-                                const int c4 = threadIdx.x + k * NTHR;
-                                if (s0 + sl < a.T && c4 < n4) {
-                                    const uint2 wv = *reinterpret_cast<const uint2*>(a.norm_w + c4 * 4);
-                                    uint2 o;
-                                    o.x = pack_bf16(v[sl][k].x * r * bf16lo(wv.x), v[sl][k].y * r * bf16hi(wv.x));
-                                    o.y = pack_bf16(v[sl][k].z * r * bf16lo(wv.y), v[sl][k].w * r * bf16hi(wv.y));
-                                    *reinterpret_cast<uint2*>(a.xn_out + (size_t)(s0 + sl) * a.N + c4 * 4) = o;
-                                }
-                            }
-                        }
-                        __syncthreads();
+                    for (int r = 0; r < 16; ++r) {
+                        const float v = res[mt * NT + (s >> 3)][r][s & 7];
+                        ss += v * v;
                     }
-                } else {
-                    for (int s = 0; s < a.T; ++s) {
-                        const float* xr = a.out + (size_t)s * a.ldo;
-                        float ss = 0.f;
-                        for (int c = threadIdx.x * 4; c < a.N; c += NTHR * 4) {
-                            const float4 v = __ldcg(reinterpret_cast<const float4*>(xr + c));
-                            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-                        }
-                        ss = warp_sum(ss);
-                        if (lane == 0) sred[warp] = ss;
-                        __syncthreads();
-                        float tot = 0.f;
-                        for (int w = 0; w < NW; ++w) tot += sred[w];
-                        const float r = 1.0f / sqrtf(tot / (float)a.N + a.eps);
-                        for (int c = threadIdx.x * 4; c < a.N; c += NTHR * 4) {
-                            const float4 v = __ldcg(reinterpret_cast<const float4*>(xr + c));
-                            const uint2 wv = *reinterpret_cast<const uint2*>(a.norm_w + c);
-                            uint2 o;
-                            o.x = pack_bf16(v.x * r * bf16lo(wv.x), v.y * r * bf16hi(wv.x));
-                            o.y = pack_bf16(v.z * r * bf16lo(wv.y), v.w * r * bf16hi(wv.y));
-                            *reinterpret_cast<uint2*>(a.xn_out + (size_t)s * a.N + c) = o;
-                        }
-                        __syncthreads();
-                    }
+                    a.ss_out[(size_t)(tile0 + mt) * 32 + s] = ss;
                 }
-                if (threadIdx.x == 0) *a.done_counter = 0;
             }
         }
     } else if (EPI == EPI_SWIGLU) {
@@ -327,8 +285,8 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             const int mt = r >> 3, rr = r & 7;
             const int n = row0 + mt * 16;
             if (s < a.T && n < a.N) {
-                const float gt = res[mt * NT + (s >> 3)][rr][s & 7];
-                const float up = res[mt * NT + (s >> 3)][rr + 8][s & 7];
+                const float gt = res[mt * NT + (s >> 3)][rr][s & 7] * s_rn[s];
+                const float up = res[mt * NT + (s >> 3)][rr + 8][s & 7] * s_rn[s];
                 const float act = gt / (1.0f + expf(-gt)) * up;
                 a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = __float2bfloat16_rn(act);
             }
@@ -342,8 +300,8 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             const int mt = r >> 3, rr = r & 7;
             const int n = row0 + mt * 16;
             if (s < a.T && n < a.N) {
-                float x1 = res[mt * NT + (s >> 3)][rr][s & 7];
-                float x2 = res[mt * NT + (s >> 3)][rr + 8][s & 7];
+                float x1 = res[mt * NT + (s >> 3)][rr][s & 7] * s_rn[s];
+                float x2 = res[mt * NT + (s >> 3)][rr + 8][s & 7] * s_rn[s];
                 if (a.bias) {
                     x1 += a.bias[n + rr];
                     x2 += a.bias[n + rr + 8];
@@ -375,7 +333,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
                 const int r = e % (MT * 16), s = e / (MT * 16);
                 const int n = row0 + r;
-                if (s < a.T && n < a.N) a.logits[(size_t)s * a.ld_logits + n] = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                if (s < a.T && n < a.N) a.logits[(size_t)s * a.ld_logits + n] = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] * s_rn[s];
             }
         }
         if (threadIdx.x < NT * 8) {
@@ -387,7 +345,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 for (int r = 0; r < MT * 16; ++r) {
                     const int n = row0 + r;
                     if (n >= a.N) break;
-                    float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                    float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] * s_rn[s];
                     if (a.inv_temp > 0.f) v = v * a.inv_temp + gumbel_noise(a.seed, step, s, a.row_offset + n);
                     if (v > best) { best = v; bi = a.row_offset + n; }
                 }

@@ -12,51 +12,89 @@
 
 // =================================================================================================
 // Embedding gather from the CM-layout table (gemv.cuh):  x[t][:] = float(E[tok[t]][:]), and the first layer's
-// RMSNorm of it (xn = bf16(x * rsqrt(mean x^2 + eps) * w)).  One CTA per slot.
+// RMSNorm in its split form (gemv.cuh): xw = bf16(x * w), per-16-element partial sums of x^2 (decode consumers) and
+// r = rsqrt(mean x^2 + eps) (prefill / tensor-parallel consumers).  One CTA per slot, one thread per 16 elements.
 // =================================================================================================
 static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __restrict__ E, const int* __restrict__ tok,
                                                                 float* __restrict__ x, const bf16* __restrict__ norm_w,
-                                                                bf16* __restrict__ xn, int H, int vocab, float eps) {
+                                                                bf16* __restrict__ xw, float* __restrict__ ss_part,
+                                                                float* __restrict__ inv_rms, int H, int vocab, float eps) {
     griddep_launch();
     griddep_wait();
     __shared__ float red[8];
-    __shared__ float s_r;
     const int t = blockIdx.x;
     int id = tok[t];
     id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
     const int nkb = H >> 5;
     const int tile = id >> 4, h = (id >> 3) & 1, r = id & 7;
-    float ss = 0.f;
-    for (int k = threadIdx.x * 8; k < H; k += blockDim.x * 8) {
-        const int kb = k >> 5, q = (k & 31) >> 3;
-        const uint4 v = *reinterpret_cast<const uint4*>(E + ((((size_t)tile * nkb + kb) * 2 + h) * 4 + q) * 64 + r * 8);
-        const float4 a = make_float4(bf16lo(v.x), bf16hi(v.x), bf16lo(v.y), bf16hi(v.y));
-        const float4 b = make_float4(bf16lo(v.z), bf16hi(v.z), bf16lo(v.w), bf16hi(v.w));
-        float4* o = reinterpret_cast<float4*>(x + (size_t)t * H + k);
-        o[0] = a;
-        o[1] = b;
-        ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
+    float tot = 0.f;
+    for (int part = threadIdx.x; part < H / 16; part += blockDim.x) {
+        float ss = 0.f;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int k = part * 16 + c * 8;
+            const int kb = k >> 5, q = (k & 31) >> 3;
+            const uint4 v = *reinterpret_cast<const uint4*>(E + ((((size_t)tile * nkb + kb) * 2 + h) * 4 + q) * 64 + r * 8);
+            const uint4 wv = *reinterpret_cast<const uint4*>(norm_w + k);
+            const float4 a = make_float4(bf16lo(v.x), bf16hi(v.x), bf16lo(v.y), bf16hi(v.y));
+            const float4 b = make_float4(bf16lo(v.z), bf16hi(v.z), bf16lo(v.w), bf16hi(v.w));
+            float4* o = reinterpret_cast<float4*>(x + (size_t)t * H + k);
+            o[0] = a;
+            o[1] = b;
+            uint4 p;
+            p.x = pack_bf16(a.x * bf16lo(wv.x), a.y * bf16hi(wv.x));
+            p.y = pack_bf16(a.z * bf16lo(wv.y), a.w * bf16hi(wv.y));
+            p.z = pack_bf16(b.x * bf16lo(wv.z), b.y * bf16hi(wv.z));
+            p.w = pack_bf16(b.z * bf16lo(wv.w), b.w * bf16hi(wv.w));
+            *reinterpret_cast<uint4*>(xw + (size_t)t * H + k) = p;
+            ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
+        }
+        if (ss_part) ss_part[part * 32 + (t & 31)] = ss;
+        tot += ss;
     }
+    if (inv_rms) {
+        tot = warp_sum(tot);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = tot;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float a2 = 0.f;
+            for (int i = 0; i < (int)(blockDim.x >> 5); ++i) a2 += red[i];
+            inv_rms[t] = 1.0f / sqrtf(a2 / (float)H + eps);
+        }
+    }
+}
+
+// Split RMSNorm for the paths that have a whole row in one place (prefill, tensor parallel): x (+= delta) stays fp32,
+// xw = bf16(x * w), inv_rms[t] = rsqrt(mean x^2 + eps).  One CTA per token.
+static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ x, const float* __restrict__ delta,
+                                                            const bf16* __restrict__ w, bf16* __restrict__ xw,
+                                                            float* __restrict__ inv_rms, int H, float eps) {
+    const int t = blockIdx.x;
+    float* xr = x + (size_t)t * H;
+    const float* dr = delta ? delta + (size_t)t * H : nullptr;
+    float ss = 0.f;
+    for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
+        float4 v = *reinterpret_cast<const float4*>(xr + c);
+        if (dr) {
+            const float4 d = *reinterpret_cast<const float4*>(dr + c);
+            v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+            *reinterpret_cast<float4*>(xr + c) = v;
+        }
+        const uint2 wv = *reinterpret_cast<const uint2*>(w + c);
+        uint2 o;
+        o.x = pack_bf16(v.x * bf16lo(wv.x), v.y * bf16hi(wv.x));
+        o.y = pack_bf16(v.z * bf16lo(wv.y), v.w * bf16hi(wv.y));
+        *reinterpret_cast<uint2*>(xw + (size_t)t * H + c) = o;
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    __shared__ float red[8];
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
     if (threadIdx.x == 0) {
         float tot = 0.f;
         for (int i = 0; i < (int)(blockDim.x >> 5); ++i) tot += red[i];
-        s_r = 1.0f / sqrtf(tot / (float)H + eps);
-    }
-    __syncthreads();
-    const float rn = s_r;
-    for (int k = threadIdx.x * 8; k < H; k += blockDim.x * 8) {
-        const float4 a = *reinterpret_cast<const float4*>(x + (size_t)t * H + k);
-        const float4 b = *reinterpret_cast<const float4*>(x + (size_t)t * H + k + 4);
-        const uint4 wv = *reinterpret_cast<const uint4*>(norm_w + k);
-        uint4 o;
-        o.x = pack_bf16(a.x * rn * bf16lo(wv.x), a.y * rn * bf16hi(wv.x));
-        o.y = pack_bf16(a.z * rn * bf16lo(wv.y), a.w * rn * bf16hi(wv.y));
-        o.z = pack_bf16(b.x * rn * bf16lo(wv.z), b.y * rn * bf16hi(wv.z));
-        o.w = pack_bf16(b.z * rn * bf16lo(wv.w), b.w * rn * bf16hi(wv.w));
-        *reinterpret_cast<uint4*>(xn + (size_t)t * H + k) = o;
+        inv_rms[t] = 1.0f / sqrtf(tot / (float)H + eps);
     }
 }
 

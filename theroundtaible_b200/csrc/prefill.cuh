@@ -14,6 +14,7 @@ enum { G5_EPI_QKV = 0, G5_EPI_RESID = 1, G5_EPI_SWIGLU = 2, G5_EPI_STORE = 3 };
 
 struct Gemm5Args {
     int S, N, K;
+    const float* row_scale;   // nullable: acc *= row_scale[token] first (split RMSNorm: r = rsqrt(mean x^2 + eps))
     // RESID: out[m*ldo + n] += acc ; STORE: out[m*ldo + n] = acc
     float* out;
     int ldo;

@@ -9,7 +9,8 @@
 //     peers[p].flags[t][r] = e          for all p     (st.release.sys over NVLink)
 //     wait local flags[t][p] >= e       for all p     (ld.acquire.sys)
 //     x[t][:] += sum_p peers[p].partial[t][:]         (P2P loads, summed in rank order => identical on every rank)
-//     xn[t][:] = bf16(x * rsqrt(mean x^2 + eps) * w)
+//     xw[t][:] = bf16(x * w),  inv_rms[t] = rsqrt(mean x^2 + eps)     (split RMSNorm: the scale is applied by the
+//                                                                       next projection's epilogue, gemv.cuh)
 //
 // The partial buffers are per call site (O-projection / down-projection), so a buffer is rewritten one full layer
 // later; by then every peer has passed the next all-reduce's wait, i.e. finished reading it -- no trailing barrier.
@@ -26,7 +27,8 @@ struct TpFusedArgs {
     int rank, tp, H;
     float* x;                        // local residual stream [T][H]
     const bf16* norm_w;
-    bf16* xn;                        // local [T][H]
+    bf16* xn;                        // local [T][H]: xw = bf16(x * w) (split RMSNorm, gemv.cuh)
+    float* inv_rms;                  // local [T]: rsqrt(mean x^2 + eps) for the consuming projection's epilogue
     float eps;
 };
 
@@ -40,7 +42,6 @@ __device__ __forceinline__ int tpf_ld_acquire_sys(const int* p) {
 template <int NTHR>
 __global__ void __launch_bounds__(NTHR) tp_fused_allreduce_norm_kernel(const TpFusedArgs a) {
     __shared__ float sred[NTHR / 32];
-    __shared__ float s_r;
     griddep_launch();
     griddep_wait();                         // this rank's partial comes from the previous kernel
     const int t = blockIdx.x;
@@ -83,18 +84,16 @@ __global__ void __launch_bounds__(NTHR) tp_fused_allreduce_norm_kernel(const TpF
     if (threadIdx.x == 0) {
         float tot = 0.f;
         for (int w = 0; w < NTHR / 32; ++w) tot += sred[w];
-        s_r = 1.0f / sqrtf(tot / (float)a.H + a.eps);
+        a.inv_rms[t] = 1.0f / sqrtf(tot / (float)a.H + a.eps);
     }
-    __syncthreads();
-    const float r = s_r;
 #pragma unroll
     for (int k = 0; k < PER; ++k) {
         const int c4 = threadIdx.x + k * NTHR;
         if (c4 < n4) {
             const uint2 wv = *reinterpret_cast<const uint2*>(a.norm_w + c4 * 4);
             uint2 o;
-            o.x = pack_bf16(v[k].x * r * bf16lo(wv.x), v[k].y * r * bf16hi(wv.x));
-            o.y = pack_bf16(v[k].z * r * bf16lo(wv.y), v[k].w * r * bf16hi(wv.y));
+            o.x = pack_bf16(v[k].x * bf16lo(wv.x), v[k].y * bf16hi(wv.x));
+            o.y = pack_bf16(v[k].z * bf16lo(wv.y), v[k].w * bf16hi(wv.y));
             *reinterpret_cast<uint2*>(a.xn + (size_t)t * a.H + c4 * 4) = o;
         }
     }
