@@ -66,7 +66,9 @@ typedef struct rt_config {
     int32_t rope_orig_ctx;
     /* weights */
     uint64_t seed;               /* seeded random-init weights (see DESIGN.md "weights") */
-    const char* weights_path;    /* optional .safetensors (bf16, HF names); NULL = seeded */
+    const char* weights_path;    /* optional: a .safetensors file or a directory of them (Hugging Face Llama / Qwen2 tensor
+                                    names, BF16 / F16 / F32); NULL or "" = seeded random weights.  Under tensor parallel
+                                    every rank reads its own rows / columns from the same path */
     /* runtime */
     int32_t device;              /* CUDA ordinal */
     int32_t tp_rank, tp_size;    /* tensor parallel: one engine per GPU/process */

@@ -55,3 +55,41 @@ def test_tp2_generation_and_logits_match_oracle(name, mode):
     from tests.test_gpu_parity import _greedy_compare
     for p, t in zip(prompts, res[0][0]):
         _greedy_compare(t, oracle, p, 20, err_bound=2.5e-2)
+
+
+def _ckpt_rank_main(rank, tp, nccl_id, path, ids, q):
+    try:
+        torch.cuda.set_device(rank)
+        kw = dict(tp_rank=rank, tp_size=tp, nccl_id=nccl_id) if tp > 1 else {}
+        with E.Engine.from_pretrained(path, device=rank, max_batch=1, max_ctx=256, **kw) as eng:
+            q.put((rank, eng.step_logits(ids, mode=1), None))
+    except Exception as ex:  # noqa: BLE001
+        q.put((rank, None, repr(ex)))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_tp2_checkpoint_shards_match_hf(tmp_path):
+    """A safetensors checkpoint loaded at TP=2: every rank takes its rows / columns of each tensor from the file, and
+    the concatenated vocab shards equal the Hugging Face forward."""
+    from tests.test_gpu_safetensors import _hf_model
+    m = _hf_model("qwen2", tied=False, head_dim=64, seed=21)
+    m.to(torch.bfloat16).save_pretrained(tmp_path, safe_serialization=True)
+    m.to(torch.float32)
+    ids = np.random.default_rng(5).integers(0, 512, 64).tolist()
+    with torch.no_grad():
+        want = m(torch.tensor(ids)[None]).logits[0].float().numpy()
+    nccl_id = E.nccl_unique_id()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_ckpt_rank_main, args=(r, 2, nccl_id, str(tmp_path), ids, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(2):
+        r, logits, err = q.get(timeout=300)
+        assert err is None, err
+        res[r] = logits
+    for p in procs:
+        p.join(timeout=60)
+    full = np.concatenate([res[0], res[1]], axis=-1)
+    assert np.abs(full - want).max() <= 1e-2 * np.abs(want).max()

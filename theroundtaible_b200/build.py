@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "_lib")
 LIB = os.path.join(LIB_DIR, "librt_engine.so")
-SOURCES = ["engine.cu", "capi.cu", "noalloc.cu", "prefill.cu", "tp.cu", "tokenizer.cpp"]
+SOURCES = ["engine.cu", "capi.cu", "noalloc.cu", "prefill.cu", "tp.cu", "tokenizer.cpp", "safetensors.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared", "-ldl"]
 

@@ -10,10 +10,12 @@
 #include <cstring>
 #include <cstdlib>
 #include <cuda_profiler_api.h>
+#include <memory>
 
 #include "attn_decode2.cuh"
 #include "gemv_stream.cuh"
 #include "kernels.cuh"
+#include "safetensors.h"
 #include "tp_fused.cuh"
 #include "weights.cuh"
 
@@ -164,6 +166,170 @@ void build_weights(rt_engine* e) {
         w.norm2 = dalloc<bf16>(e, H);
         gen_plain(e, w.norm1, 1, H, tensor_id(IN_NORM, l), 0, H, 0, 0.02f, 1.0f, false);
         gen_plain(e, w.norm2, 1, H, tensor_id(POST_NORM, l), 0, H, 0, 0.02f, 1.0f, false);
+    }
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaStreamSynchronize(e->st));
+}
+
+// ---- checkpoint weights (rt_config.weights_path) ------------------------------------------------------
+// The Hugging Face tensors of a Llama / Qwen2 checkpoint go through the SAME layout kernel as the seeded generator
+// (weights.cuh: row maps + CM layout); only the value source differs.  Each tensor -- for tensor parallel only this
+// rank's rows (column-parallel matrices, lm_head) or columns (row-parallel matrices) -- is copied from the file
+// mapping into a staging buffer in HBM and laid out from there.
+namespace {
+struct Stager {
+    rt_engine* e;
+    unsigned char* buf = nullptr;
+    size_t cap = 0, used = 0;
+    void reserve(size_t bytes) {
+        RT_CUDA(cudaMalloc(&buf, bytes));
+        cap = bytes;
+    }
+    void reset() {
+        RT_CUDA(cudaStreamSynchronize(e->st));     // the layout kernel of the previous matrix has read its staging
+        used = 0;
+    }
+    // rows [r0, r0+nr) x columns [c0, c0+nc) of a row-major [R][C] tensor -> contiguous [nr][nc] in the staging buffer
+    const void* put(const st::Tensor& t, long long r0, long long nr, long long c0, long long nc) {
+        const long long C = t.shape.size() == 2 ? t.shape[1] : t.shape[0];
+        const size_t es = (size_t)t.elem_size();
+        const size_t bytes = ((size_t)nr * nc * es + 255) & ~(size_t)255;
+        if (used + bytes > cap) throw RtError(RT_ERR_IO, "checkpoint staging buffer too small");
+        unsigned char* dst = buf + used;
+        used += bytes;
+        const unsigned char* src = t.data + ((size_t)r0 * C + c0) * es;
+        // on the engine's stream: a legacy-stream cudaMemcpy from pageable memory may return before its DMA has landed
+        // and is not ordered against the (non-blocking) stream the layout kernel runs on
+        if (nc == C) RT_CUDA(cudaMemcpyAsync(dst, src, (size_t)nr * nc * es, cudaMemcpyHostToDevice, e->st));
+        else RT_CUDA(cudaMemcpy2DAsync(dst, (size_t)nc * es, src, (size_t)C * es, (size_t)nc * es, (size_t)nr, cudaMemcpyHostToDevice, e->st));
+        return dst;
+    }
+    ~Stager() { if (buf) cudaFree(buf); }
+};
+int st_dtype(const st::Tensor& t) { return t.dtype == "BF16" ? 0 : t.dtype == "F16" ? 1 : 2; }
+
+// one logical tensor slice -> a matrix in row-major or CM layout
+void load_plain(rt_engine* e, Stager& sg, const st::Tensor& t, void* out, long long r0, int rows, long long c0, int cols, bool cm) {
+    sg.reset();
+    wgen::GenDesc d{};
+    d.map = 0;
+    d.nseg = 1;
+    d.seg[0] = {0, rows, 0ull, 0, cols, 0, sg.put(t, r0, rows, c0, cols)};
+    d.rows = rows;
+    d.cols = cols;
+    d.cm = cm ? 1 : 0;
+    d.src_dtype = st_dtype(t);
+    wgen::launch_gen(d, out, e->st);
+}
+float st_scalar(const st::Tensor& t, long long i) {
+    if (t.dtype == "F32") { float v; memcpy(&v, t.data + 4 * i, 4); return v; }
+    uint16_t h; memcpy(&h, t.data + 2 * i, 2);
+    if (t.dtype == "BF16") { const uint32_t u = (uint32_t)h << 16; float v; memcpy(&v, &u, 4); return v; }
+    return __half2float(__ushort_as_half(h));
+}
+}  // namespace
+
+void load_weights(rt_engine* e) {
+    using namespace wgen;
+    const rt_config& c = e->cfg;
+    const int H = e->H, hd = e->hd, rank = c.tp_rank;
+    const long long V = e->vocab, F = e->F, QR = (long long)e->nq * hd, KR = (long long)e->nkv * hd;
+    std::unique_ptr<st::Files> files;
+    try {
+        files.reset(new st::Files(c.weights_path));
+    } catch (const std::exception& ex) {
+        throw RtError(RT_ERR_INVALID, ex.what());
+    }
+    auto get = [&](const std::string& name, std::initializer_list<long long> shape) -> const st::Tensor& {
+        try {
+            return files->get(name, shape);
+        } catch (const std::exception& ex) {
+            throw RtError(RT_ERR_IO, ex.what());
+        }
+    };
+    Stager sg{e};
+    {
+        const size_t qkv = (size_t)e->qkv_rows * H, gu = (size_t)2 * e->F_l * H, emb = (size_t)V * H;
+        sg.reserve(std::max({qkv, gu, emb}) * 4 + 4096);      // fp32 sources at worst
+    }
+    const st::Tensor& emb = get("model.embed_tokens.weight", {V, H});
+    e->embed = dalloc<bf16>(e, (size_t)V * H);
+    load_plain(e, sg, emb, e->embed, 0, (int)V, 0, H, true);
+    const st::Tensor* head = files->find("lm_head.weight");
+    if (c.tied || !head) {
+        RT_REQUIRE(c.tied, "the checkpoint has no lm_head.weight but the configuration is not tied");
+        if (c.tp_size == 1) {
+            e->lm_head = e->embed;
+        } else {
+            e->lm_head = dalloc<bf16>(e, (size_t)e->vocab_l * H);
+            load_plain(e, sg, emb, e->lm_head, (long long)rank * e->vocab_l, e->vocab_l, 0, H, true);
+        }
+    } else {
+        e->lm_head = dalloc<bf16>(e, (size_t)e->vocab_l * H);
+        load_plain(e, sg, get("lm_head.weight", {V, H}), e->lm_head, (long long)rank * e->vocab_l, e->vocab_l, 0, H, true);
+    }
+    e->final_norm = dalloc<bf16>(e, H);
+    load_plain(e, sg, get("model.norm.weight", {H}), e->final_norm, 0, 1, 0, H, false);
+
+    e->layers.resize(e->L);
+    const int qr = e->nq_l * hd, kr = e->nkv_l * hd;
+    for (int l = 0; l < e->L; ++l) {
+        LayerW& w = e->layers[l];
+        const std::string p = "model.layers." + std::to_string(l) + ".";
+        {
+            const st::Tensor& tq = get(p + "self_attn.q_proj.weight", {QR, H});
+            const st::Tensor& tk = get(p + "self_attn.k_proj.weight", {KR, H});
+            const st::Tensor& tv = get(p + "self_attn.v_proj.weight", {KR, H});
+            RT_REQUIRE(tq.dtype == tk.dtype && tq.dtype == tv.dtype, "q/k/v projections of one layer must share a dtype");
+            sg.reset();
+            w.wqkv = dalloc<bf16>(e, (size_t)e->qkv_rows * H);
+            GenDesc d{};
+            d.map = 2; d.hd = hd; d.cm = 1; d.nseg = 3;
+            d.seg[0] = {0, qr, 0ull, 0, H, 0, sg.put(tq, (long long)rank * qr, qr, 0, H)};
+            d.seg[1] = {qr, kr, 0ull, 0, H, 0, sg.put(tk, (long long)rank * kr, kr, 0, H)};
+            d.seg[2] = {qr + kr, kr, 0ull, 0, H, 0, sg.put(tv, (long long)rank * kr, kr, 0, H)};
+            d.rows = e->qkv_rows; d.cols = H; d.src_dtype = st_dtype(tq);
+            launch_gen(d, w.wqkv, e->st);
+        }
+        if (c.qkv_bias) {
+            const st::Tensor* tb[3] = {&get(p + "self_attn.q_proj.bias", {QR}), &get(p + "self_attn.k_proj.bias", {KR}),
+                                       &get(p + "self_attn.v_proj.bias", {KR})};
+            GenDesc d{};                                            // the row map only (host)
+            d.map = 2; d.hd = hd; d.nseg = 3;
+            d.seg[0] = {0, qr, 0ull, (long long)rank * qr, 1, 0, nullptr};
+            d.seg[1] = {qr, kr, 1ull, (long long)rank * kr, 1, 0, nullptr};
+            d.seg[2] = {qr + kr, kr, 2ull, (long long)rank * kr, 1, 0, nullptr};
+            std::vector<float> hb(e->qkv_rows);
+            for (int r = 0; r < e->qkv_rows; ++r) {
+                unsigned long long which; long long lrow, lcols, lcol0; const void* src;
+                map_row(d, r, which, lrow, lcols, lcol0, src);
+                hb[r] = __bfloat162float(__float2bfloat16_rn(st_scalar(*tb[which], lrow)));
+            }
+            w.bqkv = dalloc<float>(e, e->qkv_rows);
+            RT_CUDA(cudaMemcpyAsync(w.bqkv, hb.data(), hb.size() * sizeof(float), cudaMemcpyHostToDevice, e->st));
+            RT_CUDA(cudaStreamSynchronize(e->st));                   // hb goes out of scope
+        }
+        w.wo = dalloc<bf16>(e, (size_t)H * qr);
+        load_plain(e, sg, get(p + "self_attn.o_proj.weight", {H, QR}), w.wo, 0, H, (long long)rank * qr, qr, true);
+        {
+            const st::Tensor& tg = get(p + "mlp.gate_proj.weight", {F, H});
+            const st::Tensor& tu = get(p + "mlp.up_proj.weight", {F, H});
+            RT_REQUIRE(tg.dtype == tu.dtype, "gate/up projections of one layer must share a dtype");
+            sg.reset();
+            w.wgu = dalloc<bf16>(e, (size_t)2 * e->F_l * H);
+            GenDesc d{};
+            d.map = 1; d.cm = 1; d.nseg = 2;
+            d.seg[0] = {0, 0, 0ull, 0, H, 0, sg.put(tg, (long long)rank * e->F_l, e->F_l, 0, H)};
+            d.seg[1] = {0, 0, 0ull, 0, H, 0, sg.put(tu, (long long)rank * e->F_l, e->F_l, 0, H)};
+            d.rows = 2 * e->F_l; d.cols = H; d.src_dtype = st_dtype(tg);
+            launch_gen(d, w.wgu, e->st);
+        }
+        w.wdown = dalloc<bf16>(e, (size_t)H * e->F_l);
+        load_plain(e, sg, get(p + "mlp.down_proj.weight", {H, F}), w.wdown, 0, H, (long long)rank * e->F_l, e->F_l, true);
+        w.norm1 = dalloc<bf16>(e, H);
+        w.norm2 = dalloc<bf16>(e, H);
+        load_plain(e, sg, get(p + "input_layernorm.weight", {H}), w.norm1, 0, 1, 0, H, false);
+        load_plain(e, sg, get(p + "post_attention_layernorm.weight", {H}), w.norm2, 0, 1, 0, H, false);
     }
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaStreamSynchronize(e->st));
@@ -340,7 +506,6 @@ void engine_init(rt_engine* e) {
     RT_REQUIRE(c.tp_size >= 1 && c.tp_rank >= 0 && c.tp_rank < c.tp_size, "bad tp_rank/tp_size");
     RT_REQUIRE(c.n_q % c.tp_size == 0 && c.n_kv % c.tp_size == 0 && c.ffn % (8 * c.tp_size) == 0 && c.vocab % (16 * c.tp_size) == 0,
                "n_q, n_kv, ffn/8 and vocab/16 must be divisible by tp_size");
-    RT_REQUIRE(c.weights_path == nullptr, "safetensors loading is not available in this build");
 
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
@@ -366,7 +531,8 @@ void engine_init(rt_engine* e) {
     e->qkv_rows = (e->nq_l + 2 * e->nkv_l) * e->hd;
     RT_REQUIRE(e->qkv_rows % 16 == 0 && (2 * e->F_l) % 16 == 0 && e->H % 16 == 0, "projection row counts must be multiples of 16");
 
-    build_weights(e);
+    if (c.weights_path && c.weights_path[0]) load_weights(e);
+    else build_weights(e);
     build_rope_tables(e);
 
     // KV pool

@@ -3,6 +3,8 @@
 // RNE to bf16), so the CPU oracle and the GPU engine hold identical bytes without a 139 GB file.
 // No counterpart in the reference (it holds no weights; local-llm.ts:162 only names a model).
 #pragma once
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace wgen {
@@ -47,6 +49,8 @@ struct Seg {
     int prow0, nrows;             // physical rows [prow0, prow0+nrows)
     unsigned long long key;
     long long lrow0, lcols, lcol0;
+    const void* src;              // non-null: copy from this row-major [*][lcols] device tensor (a staged checkpoint
+                                  // tensor, dtype GenDesc.src_dtype) instead of generating
 };
 struct GenDesc {
     int map;
@@ -57,14 +61,15 @@ struct GenDesc {
     int cm;                       // 1 = CM layout, 0 = row-major
     float scale, offset;
     int as_f32;                   // write fp32 (biases; row-major only) instead of bf16
+    int src_dtype;                // Seg.src element type: 0 bf16, 1 fp16, 2 fp32 (converted RNE to bf16)
 };
 
 __host__ __device__ inline void map_row(const GenDesc& d, int pr, unsigned long long& key, long long& lrow, long long& lcols,
-                                        long long& lcol0) {
+                                        long long& lcol0, const void*& src) {
     if (d.map == 1) {
         const int tile = pr >> 4, w = pr & 15;
         const Seg& s = d.seg[w < 8 ? 0 : 1];
-        key = s.key; lrow = s.lrow0 + tile * 8 + (w & 7); lcols = s.lcols; lcol0 = s.lcol0;
+        key = s.key; lrow = s.lrow0 + tile * 8 + (w & 7); lcols = s.lcols; lcol0 = s.lcol0; src = s.src;
         return;
     }
     int si = 0;
@@ -76,7 +81,7 @@ __host__ __device__ inline void map_row(const GenDesc& d, int pr, unsigned long 
         const int head = local / d.hd, p = local % d.hd, j = p >> 4, w = p & 15;
         local = head * d.hd + (w < 8 ? 8 * j + w : d.hd / 2 + 8 * j + (w - 8));
     }
-    key = s.key; lrow = s.lrow0 + local; lcols = s.lcols; lcol0 = s.lcol0;
+    key = s.key; lrow = s.lrow0 + local; lcols = s.lcols; lcol0 = s.lcol0; src = s.src;
 }
 
 // physical 16-byte piece index -> (row, first column) for the CM layout
@@ -104,11 +109,29 @@ static __global__ void gen_kernel(const GenDesc d, void* out) {
         }
         unsigned long long key;
         long long lrow, lcols, lcol0;
-        map_row(d, pr, key, lrow, lcols, lcol0);
+        const void* src;
+        map_row(d, pr, key, lrow, lcols, lcol0, src);
         const long long lidx = lrow * lcols + lcol0 + pc;
         float v[8];
+        if (src) {
+            // checkpoint tensor: the same row map and layout, values copied (bf16) or rounded RNE (fp16 / fp32)
+            if (d.src_dtype == 0) {
+                const bf16* sp = reinterpret_cast<const bf16*>(src) + lidx;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = gen_value(key, (unsigned long long)(lidx + j), d.scale, d.offset);
+                for (int j = 0; j < 8; ++j) v[j] = __bfloat162float(sp[j]);
+            } else if (d.src_dtype == 1) {
+                const __half* sp = reinterpret_cast<const __half*>(src) + lidx;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = __half2float(sp[j]);
+            } else {
+                const float* sp = reinterpret_cast<const float*>(src) + lidx;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = sp[j];
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = gen_value(key, (unsigned long long)(lidx + j), d.scale, d.offset);
+        }
         if (d.as_f32) {
             float* o = reinterpret_cast<float*>(out) + i * 8;
 #pragma unroll

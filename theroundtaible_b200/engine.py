@@ -124,6 +124,50 @@ def arch_config(model: str) -> RtConfig:
     return cfg
 
 
+def config_from_hf(hf) -> RtConfig:
+    """Architecture half of rt_config from a Hugging Face ``config.json`` (a dict, a PretrainedConfig, or the path of
+    a checkpoint directory / config file).  Llama and Qwen2 only; anything this backend has no kernel
+    for (o_proj / MLP biases, sliding windows, other rope types) is refused here rather than silently ignored."""
+    import json
+    import os
+    if isinstance(hf, (str, os.PathLike)):
+        path = os.fspath(hf)
+        if os.path.isdir(path):
+            path = os.path.join(path, "config.json")
+        with open(path) as f:
+            hf = json.load(f)
+    elif hasattr(hf, "to_dict"):
+        hf = hf.to_dict()
+    mt = hf.get("model_type")
+    if mt not in ("llama", "qwen2"):
+        raise EngineError(-1, f"model_type '{mt}' not found among the supported families (llama, qwen2)")
+    if mt == "llama" and (hf.get("attention_bias") or hf.get("mlp_bias")):
+        raise EngineError(-1, "llama checkpoints with attention_bias / mlp_bias are not supported")
+    if mt == "qwen2" and hf.get("use_sliding_window"):
+        raise EngineError(-1, "qwen2 sliding-window attention is not supported")
+    cfg = RtConfig()
+    cfg.struct_size = C.sizeof(RtConfig)
+    cfg.family = 0 if mt == "llama" else 1
+    cfg.layers, cfg.hidden = hf["num_hidden_layers"], hf["hidden_size"]
+    cfg.n_q = hf["num_attention_heads"]
+    cfg.n_kv = hf.get("num_key_value_heads") or cfg.n_q
+    cfg.head_dim = hf.get("head_dim") or cfg.hidden // cfg.n_q
+    cfg.ffn, cfg.vocab = hf["intermediate_size"], hf["vocab_size"]
+    cfg.tied = 1 if hf.get("tie_word_embeddings") else 0
+    cfg.qkv_bias = 1 if mt == "qwen2" else 0
+    cfg.rms_eps = hf.get("rms_norm_eps", 1e-6)
+    rope = hf.get("rope_parameters") or hf.get("rope_scaling") or {}
+    cfg.rope_theta = rope.get("rope_theta") or hf.get("rope_theta") or 10000.0
+    rtype = rope.get("rope_type") or rope.get("type") or "default"
+    if rtype == "llama3":
+        cfg.rope_factor = rope["factor"]
+        cfg.rope_low_freq, cfg.rope_high_freq = rope["low_freq_factor"], rope["high_freq_factor"]
+        cfg.rope_orig_ctx = rope["original_max_position_embeddings"]
+    elif rtype != "default":
+        raise EngineError(-1, f"rope type '{rtype}' is not supported (default and llama3 are)")
+    return cfg
+
+
 @dataclass
 class Generation:
     text: str
@@ -145,12 +189,19 @@ def _p(arr: np.ndarray, ctype):
 class Engine:
     """One engine per GPU.  Calls are serialised by the caller (the reference issues one execute() at a time)."""
 
-    def __init__(self, model: str, *, seed: int = 0, device: int = 0, max_batch: int = 8, max_ctx: int = 4096,
-                 kv_pool_bytes: int = 0, flags: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl_id: bytes | None = None):
+    def __init__(self, model, *, seed: int = 0, device: int = 0, max_batch: int = 8, max_ctx: int = 4096,
+                 kv_pool_bytes: int = 0, flags: int = 0, tp_rank: int = 0, tp_size: int = 1, nccl_id: bytes | None = None,
+                 weights_path: str | None = None):
+        """``model`` is a name rt_arch_by_name knows (seeded random-init weights unless ``weights_path`` is given) or an
+        RtConfig (e.g. from ``config_from_hf``).  ``weights_path``: a .safetensors file or a directory of them."""
         lib = load_library()
-        cfg = arch_config(model)
+        if isinstance(model, RtConfig):
+            cfg, model = model, "custom"
+        else:
+            cfg = arch_config(model)
         cfg.seed = seed
-        cfg.weights_path = None
+        self._weights_path = os.fspath(weights_path).encode() if weights_path else None    # must outlive rt_engine_create
+        cfg.weights_path = self._weights_path
         cfg.device = device
         self._nccl_id = C.create_string_buffer(nccl_id, 128) if nccl_id else None    # must outlive rt_engine_create
         cfg.tp_rank, cfg.tp_size = tp_rank, tp_size
@@ -165,6 +216,11 @@ class Engine:
         _check(lib.rt_model_info_get(self._h, C.byref(info)), self._h)
         self.info = info
         self.vocab = info.vocab
+
+    @classmethod
+    def from_pretrained(cls, path: str, **kw) -> "Engine":
+        """A Hugging Face checkpoint directory: ``config.json`` + ``*.safetensors`` (Llama / Qwen2)."""
+        return cls(config_from_hf(path), weights_path=path, **kw)
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:

@@ -80,12 +80,17 @@ def make_server(engine: Engine, model: str, host: str = "127.0.0.1", port: int =
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="llama-3.2-1b")
+    ap.add_argument("--checkpoint", default=None, help="Hugging Face checkpoint directory (config.json + *.safetensors); "
+                    "without it the model has seeded random weights")
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--port", type=int, default=11435)
     ap.add_argument("--max-ctx", type=int, default=16384)
     ap.add_argument("--max-new-tokens", type=int, default=512)
     args = ap.parse_args()
-    eng = Engine(args.model, device=args.device, max_batch=8, max_ctx=args.max_ctx)
+    if args.checkpoint:
+        eng = Engine.from_pretrained(args.checkpoint, device=args.device, max_batch=8, max_ctx=args.max_ctx)
+    else:
+        eng = Engine(args.model, device=args.device, max_batch=8, max_ctx=args.max_ctx)
     srv = make_server(eng, args.model, port=args.port, max_new_tokens=args.max_new_tokens)
     print(f"roundtable-b200 serving {args.model} on http://127.0.0.1:{args.port}", flush=True)
     srv.serve_forever()
