@@ -184,6 +184,57 @@ def cpu_baseline_leg(w):
                        f"prefill {t['prefill_s']:.2f}s decode {t['decode_s']:.2f}s")}
 
 
+def discuss_leg(w, model, device, rounds=5):
+    """SEQ mode on the REAL prompt layout: the restated turn loop (theroundtaible_b200/roundtable.py, reference
+    orchestrator.ts:347-456 + prompt.ts:60-105) drives one adapter per knight over ONE engine, `rounds` rounds, each
+    turn's prompt = template + transcript so far.  Run twice: cross-call prefix cache on (the adapter's default) and
+    off.  Reports wall time per round and the share of prompt tokens whose KV came from the cache."""
+    import random
+    from theroundtaible_b200 import B200LocalLlmAdapter
+    from theroundtaible_b200 import engine as E
+    from theroundtaible_b200 import roundtable as R
+    names = ["Merlin", "Gawain", "Percival", "Lancelot", "Galahad", "Bors", "Kay", "Tristan"][:w["knights"]]
+    knights = [R.KnightConfig(n, f"local-llm-{i}", ["analysis", "code review"], i) for i, n in enumerate(names)]
+    nt = w["new_tokens"]
+    out = {}
+    for label, flags in (("prefix_cache_on", E.RT_FLAG_PREFIX_CACHE), ("prefix_cache_off", 0)):
+        max_ctx = 3800 + rounds * len(knights) * (nt * 10 + 64) + nt      # a generated id detokenises to <= 10 bytes = 10 tokens
+        a = E.arch_config(model)
+        kv_tok = 2 * a.layers * a.n_kv * a.head_dim * 2
+        # room for every knight's last prompt to stay cached next to the running sequence
+        eng = E.Engine(model, seed=0, device=device, max_batch=2, max_ctx=max_ctx,
+                       kv_pool_bytes=(len(knights) + 1) * max_ctx * kv_tok, flags=flags)
+        adapters = {k.adapter: B200LocalLlmAdapter(f"b200://{device}", w["model"], k.name, max_new_tokens=nt, ignore_eos=True,
+                                                   engine=eng) for k in knights}
+        per_turn = []
+
+        def on_turn(turn, adapter):
+            g = adapter.last_generation
+            per_turn.append((turn.round, g.n_prompt_tokens, g.prefix_cached_tokens, g.prefill_ms, g.decode_ms, g.decode_steps, turn.wall_ms))
+        t0 = time.perf_counter()
+        res = R.run_discussion(adapters, knights, "Should the cache layer move in front of the API gateway?", max_rounds=rounds,
+                               rng=random.Random(1234), on_turn=on_turn)
+        wall = (time.perf_counter() - t0) * 1e3
+        eng.close()
+        errs = [f"{t.knight} r{t.round}: {t.error}" for t in res.turns if t.error]
+        if errs or len(per_turn) != rounds * len(knights):
+            raise RuntimeError(f"discussion incomplete ({len(per_turn)} turns): {errs[:2]}")
+        out[label] = {
+            "wall_ms": wall, "turns": len(per_turn),
+            "round_ms": [sum(t[6] for t in per_turn if t[0] == r) for r in range(1, rounds + 1)],
+            "prompt_tokens": sum(t[1] for t in per_turn), "prefix_cached_tokens": sum(t[2] for t in per_turn),
+            "hit_rate": sum(t[2] for t in per_turn) / max(1, sum(t[1] for t in per_turn)),
+            "prefill_ms": sum(t[3] for t in per_turn), "decode_ms": sum(t[4] for t in per_turn),
+            "decode_tok_per_s": sum(t[5] for t in per_turn) / (sum(t[4] for t in per_turn) * 1e-3),
+            "last_prompt_tokens": per_turn[-1][1],
+        }
+    out["note"] = (f"{len(knights)} knights x {rounds} rounds, {nt} new tokens per turn, byte-level tokenizer, synthetic template of the "
+                   "reference's size and placeholder layout; SEQ = what `roundtable discuss` issues.  Random weights emit ids outside the byte "
+                   "range, each detokenised as '<t12345>' and read back by the byte-level tokenizer as ~9 tokens, so the transcript grows "
+                   "~4.7k tokens per turn (about 8x a BPE server's): prompt and prefill figures are pessimistic by that factor")
+    return out
+
+
 # =====================================================================================================
 def run_b200(args, w):
     import numpy as np
@@ -305,6 +356,12 @@ def run_b200(args, w):
                 cpu = cpu_baseline_leg(w)
             except Exception as ex:  # noqa: BLE001
                 cpu = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+        discuss = None
+        if not args.no_discuss and tp == 1 and world == 1 and info.n_params < 3e9:
+            try:
+                discuss = discuss_leg(w, model, local)
+            except Exception as ex:  # noqa: BLE001
+                discuss = {"failed": repr(ex)}
         h2d = sum(len(t.encode()) + 3 for t in texts) * 4 + 4 * 96 * ((sum(len(t.encode()) + 3 for t in texts) + 31) // 32)
         d2h = w["knights"] * nt * 4
         line = {
@@ -332,7 +389,7 @@ def run_b200(args, w):
                         "note": "whole prefill phase (tcgen05 GEMMs + flash attention + norms), algorithmic FLOPs / CUDA-event time"},
             "extra": {"seq": {"decode_tok_per_s": seq_tok / (seq_dec_ms * 1e-3), "round_ms": seq_round_ms,
                               "note": "SEQ = one knight per call (B=1), what orchestrator.ts:361-442 issues"},
-                      "batch_round_ms": wall_ms_m / args.steps},
+                      "batch_round_ms": wall_ms_m / args.steps, "discuss": discuss},
         }
         print(json.dumps(line), flush=True)
     eng.close()
@@ -348,6 +405,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-discuss", action="store_true", help="skip the 5-round SEQ discussion leg (extra.discuss)")
     ap.add_argument("--tp", type=int, default=1, help="tensor-parallel degree (= torchrun ranks); default: replicas")
     ap.add_argument("--layers", type=int, default=0, help="truncate the model depth (stated in config.model)")
     args = ap.parse_args()

@@ -15,6 +15,7 @@ in INTEGRATION.md.
 """
 from __future__ import annotations
 
+import os
 import re
 from typing import Optional
 
@@ -88,6 +89,7 @@ class B200LocalLlmAdapter(BaseAdapter):
         # the adapter keeps each knight's prompt KV between turns: its next prompt extends the last one (prompt.ts:60-77)
         self._engine_args = dict(seed=seed, max_batch=max_batch, max_ctx=max_ctx, flags=RT_FLAG_PREFIX_CACHE)
         self._load_error: Optional[BaseException] = None
+        self.last_generation = None          # engine.Generation of the last execute(): token counts, timings, cache hits
 
     # -- engine life cycle ----------------------------------------------------------------------
     def _device(self) -> int:
@@ -98,7 +100,10 @@ class B200LocalLlmAdapter(BaseAdapter):
 
     def _get_engine(self) -> Engine:
         if self._engine is None:
-            self._engine = Engine(self.model, device=self._device(), **self._engine_args)
+            if os.path.isdir(self.model):    # `model` names a Hugging Face checkpoint directory instead of an architecture
+                self._engine = Engine.from_pretrained(self.model, device=self._device(), **self._engine_args)
+            else:
+                self._engine = Engine(self.model, device=self._device(), **self._engine_args)
         return self._engine
 
     # -- BaseAdapter ----------------------------------------------------------------------------
@@ -133,6 +138,7 @@ class B200LocalLlmAdapter(BaseAdapter):
         try:
             gen = self._get_engine().generate(prompt, max_new_tokens=self.max_new_tokens, ignore_eos=self.ignore_eos,
                                               deadline_ms=int(timeout))
+            self.last_generation = gen
             if not gen.text:
                 raise RuntimeError("Local LLM returned empty response")      # local-llm.ts:189-191
             return gen.text
