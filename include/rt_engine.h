@@ -86,8 +86,9 @@ typedef struct rt_config {
 typedef struct rt_sampling {
     int32_t max_new_tokens;      /* <= 0 -> 512 */
     float temperature;           /* 0 = greedy (argmax, lowest index wins ties) */
-    int32_t top_k;               /* reserved: must be 0 */
-    float top_p;                 /* reserved: must be 0 or 1 */
+    int32_t top_k;               /* 0 = off; with temperature > 0: keep the k highest logits (ties at the k-th kept) */
+    float top_p;                 /* 0 or 1 = off; with temperature > 0: keep the smallest set of highest-probability tokens
+                                    (after top_k) whose mass reaches top_p.  Single GPU only (csrc/sampler.cuh) */
     uint64_t seed;
     int32_t ignore_eos;
     int32_t reserved;
@@ -186,6 +187,12 @@ RT_API int rt_weights_export(rt_engine* e, int32_t tensor_id, uint16_t* out, int
 RT_API int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t K, int32_t T, int32_t device);
 /* y = rmsnorm(x) * w, rounded to bf16: x fp32 [T][H], w bf16 bits [H], y bf16 bits [T][H]. */
 RT_API int rt_k_rmsnorm(const float* x, const uint16_t* w, uint16_t* y, int32_t T, int32_t H, float eps, int32_t device);
+/* top-k / top-p sampling (csrc/sampler.cuh) on host logits [T][V] at the given decode step: tok_out[T] the drawn
+ * tokens, kept_out[T] (nullable) the size of the kept set, thresh_out[T] (nullable) the lowest kept logit (-inf when no
+ * filter is active).  Parity hook for oracle/sampling.py; no reference counterpart (local-llm.ts:162-165 sends none). */
+RT_API int rt_k_sample_topkp(const float* logits, int32_t T, int32_t V, float temperature, int32_t top_k, float top_p,
+                             uint64_t seed, int32_t step, int32_t* tok_out, int32_t* kept_out, float* thresh_out,
+                             int32_t device);
 /* Paged GQA decode attention on contiguous inputs: q bf16 [T][n_q][hd] (T query tokens of T
  * sequences), k/v bf16 [T][ctx][n_kv][hd], lens[T]; `shared` leading tokens are identical in all
  * sequences and are read once (cascade) when shared > 0.  out fp32 [T][n_q][hd]. */

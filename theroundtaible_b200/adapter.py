@@ -77,7 +77,8 @@ class B200LocalLlmAdapter(BaseAdapter):
 
     def __init__(self, endpoint: str, model: str, name: str, source: Optional[str] = None, timeout_ms: int = 120_000,
                  *, seed: int = 0, max_batch: int = 8, max_ctx: int = 16384, max_new_tokens: int = 512,
-                 ignore_eos: bool = False, engine: Optional[Engine] = None):
+                 ignore_eos: bool = False, engine: Optional[Engine] = None, temperature: float = 0.0, top_k: int = 0,
+                 top_p: float = 0.0, sampling_seed: int = 0):
         self.endpoint = re.sub(r"/+$", "", endpoint)          # local-llm.ts:17 strips trailing slashes
         self.model = model
         self.name = name
@@ -85,6 +86,8 @@ class B200LocalLlmAdapter(BaseAdapter):
         self.default_timeout = timeout_ms
         self.max_new_tokens = max_new_tokens
         self.ignore_eos = ignore_eos
+        # the reference request carries no sampling field (local-llm.ts:162-165); greedy unless the host opts in
+        self._sampling = dict(temperature=temperature, top_k=top_k, top_p=top_p, seed=sampling_seed)
         self._engine = engine
         # the adapter keeps each knight's prompt KV between turns: its next prompt extends the last one (prompt.ts:60-77)
         self._engine_args = dict(seed=seed, max_batch=max_batch, max_ctx=max_ctx, flags=RT_FLAG_PREFIX_CACHE)
@@ -137,7 +140,7 @@ class B200LocalLlmAdapter(BaseAdapter):
         timeout = self.default_timeout if timeout_ms is None else timeout_ms
         try:
             gen = self._get_engine().generate(prompt, max_new_tokens=self.max_new_tokens, ignore_eos=self.ignore_eos,
-                                              deadline_ms=int(timeout))
+                                              deadline_ms=int(timeout), **self._sampling)
             self.last_generation = gen
             if not gen.text:
                 raise RuntimeError("Local LLM returned empty response")      # local-llm.ts:189-191
@@ -152,7 +155,7 @@ class B200LocalLlmAdapter(BaseAdapter):
         timeout = self.default_timeout if timeout_ms is None else timeout_ms
         try:
             gens = self._get_engine().generate_batch(list(prompts), max_new_tokens=self.max_new_tokens,
-                                                     ignore_eos=self.ignore_eos, deadline_ms=int(timeout))
+                                                     ignore_eos=self.ignore_eos, deadline_ms=int(timeout), **self._sampling)
             return [g.text for g in gens]
         except Exception as ex:  # noqa: BLE001
             raise classify_error(ex, self.name) from ex

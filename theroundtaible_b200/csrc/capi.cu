@@ -7,6 +7,7 @@
 
 #include "engine.cuh"
 #include "kernels.cuh"
+#include "sampler.cuh"
 #include "weights.cuh"
 #include "prefill.cuh"
 
@@ -302,6 +303,30 @@ int rt_k_rmsnorm(const float* x, const uint16_t* w, uint16_t* y, int32_t T, int3
         rmsnorm_kernel<<<T, 256, 0, s.e.st>>>(dx, nullptr, dw, dy, H, H, eps);
         RT_CUDA(cudaGetLastError());
         RT_CUDA(cudaMemcpyAsync(y, dy, (size_t)T * H * 2, cudaMemcpyDeviceToHost, s.e.st));
+        RT_CUDA(cudaStreamSynchronize(s.e.st));
+    });
+}
+
+int rt_k_sample_topkp(const float* logits, int32_t T, int32_t V, float temperature, int32_t top_k, float top_p, uint64_t seed,
+                      int32_t step, int32_t* tok_out, int32_t* kept_out, float* thresh_out, int32_t device) {
+    return guard(nullptr, [&] {
+        RT_REQUIRE(logits && tok_out, "null argument");
+        RT_REQUIRE(T >= 1 && T <= MAX_SLOTS && V >= 1, "bad shape");
+        RT_REQUIRE(temperature > 0.f && top_k >= 0 && top_p >= 0.f && top_p <= 1.f, "need temperature > 0, top_k >= 0, 0 <= top_p <= 1");
+        Scratch s(device);
+        float* dl = s.alloc<float>((size_t)T * V, false);
+        int* dt = s.alloc<int>(T);
+        int* dk = s.alloc<int>(T);
+        float* dth = s.alloc<float>(T);
+        RT_CUDA(cudaMemcpyAsync(dl, logits, (size_t)T * V * 4, cudaMemcpyHostToDevice, s.e.st));
+        TopkpArgs k{};
+        k.logits = dl; k.ld = V; k.V = V; k.T = T; k.inv_temp = 1.0f / temperature; k.top_k = top_k; k.top_p = top_p;
+        k.seed = seed; k.step_const = step; k.next_tok = dt; k.kept_out = dk; k.thresh_out = dth;
+        topkp_sample_kernel<<<T, TOPKP_THREADS, 0, s.e.st>>>(k);
+        RT_CUDA(cudaGetLastError());
+        RT_CUDA(cudaMemcpyAsync(tok_out, dt, T * 4, cudaMemcpyDeviceToHost, s.e.st));
+        if (kept_out) RT_CUDA(cudaMemcpyAsync(kept_out, dk, T * 4, cudaMemcpyDeviceToHost, s.e.st));
+        if (thresh_out) RT_CUDA(cudaMemcpyAsync(thresh_out, dth, T * 4, cudaMemcpyDeviceToHost, s.e.st));
         RT_CUDA(cudaStreamSynchronize(s.e.st));
     });
 }

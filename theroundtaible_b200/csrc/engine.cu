@@ -16,6 +16,7 @@
 #include "gemv_stream.cuh"
 #include "kernels.cuh"
 #include "safetensors.h"
+#include "sampler.cuh"
 #include "tp_fused.cuh"
 #include "weights.cuh"
 
@@ -831,7 +832,20 @@ static void set_norm_scale(rt_engine* e, GemvArgs& g, bool direct) {
 // lm_head over the T rows of e->xn + sampling.  Single GPU: the projection's last CTA picks the winners and advances
 // the decode state.  Tensor parallel: vocab-parallel local winners -> all-gather -> tp_pick_kernel on every rank.
 static void lm_head_and_sample(rt_engine* e, int T, bool sample, bool advance, bool store_logits, float inv_temp,
-                               unsigned long long seed, bool direct_scale = false) {
+                               unsigned long long seed, bool direct_scale = false, int top_k = 0, float top_p = 0.f) {
+    // top-k / top-p: the projection only stores the logits; sampler.cuh filters and draws (one CTA per slot)
+    const bool filtered = sample && inv_temp > 0.f && ((top_k > 0 && top_k < e->vocab) || (top_p > 0.f && top_p < 1.f));
+    if (filtered) {
+        RT_REQUIRE(!e->tp, "top_k / top_p sampling is not available with tensor parallel (vocab-parallel logits)");
+        lm_head_and_sample(e, T, false, false, true, 0.f, seed, direct_scale);
+        TopkpArgs k{};
+        k.logits = e->logits; k.ld = e->vocab_l; k.V = e->vocab_l; k.T = T;
+        k.inv_temp = inv_temp; k.top_k = top_k; k.top_p = top_p; k.seed = seed; k.step_ptr = e->d_step;
+        k.next_tok = e->d_next_tok; k.done_counter = e->done_counter;
+        if (advance) { k.tok = e->d_tok; k.pos = e->d_pos; k.out_tokens = e->d_out_tokens; k.max_out = e->max_out; k.step_w = e->d_step; }
+        launch_pdl(e, topkp_sample_kernel, dim3(T), dim3(TOPKP_THREADS), 0, k);
+        return;
+    }
     GemvArgs gl{};
     gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = e->H; gl.T = T; gl.X = e->xn; gl.ldx = e->H;
     set_norm_scale(e, gl, direct_scale);
@@ -939,7 +953,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         }
     }
 
-    if ((o.sample || o.store_logits) && !(skip & 64)) lm_head_and_sample(e, T, o.sample, o.advance, o.store_logits, o.inv_temp, o.seed);
+    if ((o.sample || o.store_logits) && !(skip & 64)) lm_head_and_sample(e, T, o.sample, o.advance, o.store_logits, o.inv_temp, o.seed, false, o.top_k, o.top_p);
     RT_CUDA(cudaGetLastError());
 }
 
@@ -1083,7 +1097,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
                                         cudaMemcpyDeviceToDevice, e->st));
                 RT_CUDA(cudaMemcpyAsync(e->inv_rms + j, e->pf_inv_rms + rows[j], sizeof(float), cudaMemcpyDeviceToDevice, e->st));
             }
-            lm_head_and_sample(e, T, sample, false, store, base.inv_temp, base.seed, true);
+            lm_head_and_sample(e, T, sample, false, store, base.inv_temp, base.seed, true, base.top_k, base.top_p);
         };
         if (logits_out) {
             for (int r0 = 0; r0 < S; r0 += MAX_SLOTS) {
@@ -1112,7 +1126,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
 static void ensure_graph(rt_engine* e, const StepOpts& o) {
     const StepOpts& g = e->graph_opts;
     if (e->graph_exec && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks && g.n_sh == o.n_sh && g.n_own == o.n_own &&
-        g.n_shared_tiles == o.n_shared_tiles && g.inv_temp == o.inv_temp && g.seed == o.seed)
+        g.n_shared_tiles == o.n_shared_tiles && g.inv_temp == o.inv_temp && g.seed == o.seed && g.top_k == o.top_k && g.top_p == o.top_p)
         return;
     if (e->graph_exec) {
         cudaGraphExecDestroy(e->graph_exec);
@@ -1145,7 +1159,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     rt_sampling s{};
     if (sp) s = *sp;
     if (s.max_new_tokens <= 0) s.max_new_tokens = 512;
-    RT_REQUIRE(s.top_k == 0 && (s.top_p == 0.f || s.top_p == 1.f), "top_k / top_p sampling is not available");
+    RT_REQUIRE(s.top_k >= 0 && s.top_p >= 0.f && s.top_p <= 1.f, "top_k must be >= 0 and top_p within [0, 1]");
     RT_REQUIRE(s.temperature >= 0.f, "temperature must be >= 0");
     for (int i = 0; i < n; ++i) {
         RT_REQUIRE(lens[i] >= 1, "empty prompt");
@@ -1204,6 +1218,8 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     plan_chunks(max_len, 0, base, e->hd);   // prefill slabs: no cascade phase
     base.inv_temp = s.temperature > 0.f ? 1.0f / s.temperature : 0.f;
     base.seed = s.seed;
+    base.top_k = s.top_k;
+    base.top_p = s.top_p;
 
     // ---- prefill ----
     const char* prof_phase = getenv("RT_PROFILE_PHASE");     // ncu --profile-from-start off: "prefill" | "decode"

@@ -34,6 +34,8 @@ struct StepOpts {
     int n_partials_max = 1;    // most partials any (slot, head) will have (fused merge capacity check)
     float inv_temp = 0.f;
     unsigned long long seed = 0;
+    int top_k = 0;             // sampler.cuh; only with inv_temp > 0
+    float top_p = 0.f;
 };
 
 struct rt_engine {

@@ -56,7 +56,7 @@ class RtModelInfo(C.Structure):
 EXPORTS = ("rt_arch_by_name", "rt_engine_create", "rt_engine_destroy", "rt_last_error", "rt_model_info_get",
            "rt_generate", "rt_generate_batch", "rt_generate_ids", "rt_seq_reset", "rt_step_logits", "rt_result_free",
            "rt_tokenize_chat", "rt_detokenize", "rt_nccl_unique_id", "rt_weights_export", "rt_k_gemv", "rt_k_rmsnorm",
-           "rt_k_attention", "rt_k_gemv_bench", "rt_k_attention_noalloc", "rt_k_gemm_tc5")
+           "rt_k_attention", "rt_k_gemv_bench", "rt_k_attention_noalloc", "rt_k_gemm_tc5", "rt_k_sample_topkp")
 
 _lib = None
 
@@ -107,6 +107,8 @@ def load_library():
     lib.rt_k_attention.argtypes = [C.POINTER(C.c_uint16)] * 3 + [C.POINTER(i32), C.POINTER(C.c_float)] + [i32] * 8
     lib.rt_k_gemv_bench.argtypes = [i32, i32, i32, i32, i32, C.POINTER(C.c_double)]
     lib.rt_k_gemm_tc5.argtypes = [C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.POINTER(C.c_float), i32, i32, i32, i32]
+    lib.rt_k_sample_topkp.argtypes = [C.POINTER(C.c_float), i32, i32, C.c_float, i32, C.c_float, C.c_uint64, i32,
+                                      C.POINTER(i32), C.POINTER(i32), C.POINTER(C.c_float), i32]
     lib.rt_k_attention_noalloc.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]
     _lib = lib
     return lib
@@ -241,8 +243,8 @@ class Engine:
 
     # ---- generation ---------------------------------------------------------------------------
     @staticmethod
-    def _sampling(max_new_tokens, temperature, seed, ignore_eos):
-        return RtSampling(max_new_tokens, temperature, 0, 0.0, seed, 1 if ignore_eos else 0, 0)
+    def _sampling(max_new_tokens, temperature, seed, ignore_eos, top_k=0, top_p=0.0):
+        return RtSampling(max_new_tokens, temperature, top_k, top_p, seed, 1 if ignore_eos else 0, 0)
 
     def _collect(self, res, n):
         out = []
@@ -255,23 +257,25 @@ class Engine:
             self._lib.rt_result_free(C.byref(res[i]))
         return out
 
-    def generate_ids(self, prompts, max_new_tokens=64, temperature=0.0, seed=0, ignore_eos=True, deadline_ms=0):
+    def generate_ids(self, prompts, max_new_tokens=64, temperature=0.0, seed=0, ignore_eos=True, deadline_ms=0,
+                     top_k=0, top_p=0.0):
         n = len(prompts)
         arrs = [np.ascontiguousarray(p, dtype=np.int32) for p in prompts]
         ptrs = (C.POINTER(C.c_int32) * n)(*[_p(a, C.c_int32) for a in arrs])
         lens = (C.c_int32 * n)(*[len(a) for a in arrs])
         res = (RtResult * n)()
-        s = self._sampling(max_new_tokens, temperature, seed, ignore_eos)
+        s = self._sampling(max_new_tokens, temperature, seed, ignore_eos, top_k, top_p)
         _check(self._lib.rt_generate_ids(self._h, ptrs, lens, n, C.byref(s), deadline_ms, res), self._h)
         return self._collect(res, n)
 
-    def generate_batch(self, prompts, max_new_tokens=0, temperature=0.0, seed=0, ignore_eos=False, deadline_ms=0):
+    def generate_batch(self, prompts, max_new_tokens=0, temperature=0.0, seed=0, ignore_eos=False, deadline_ms=0,
+                       top_k=0, top_p=0.0):
         n = len(prompts)
         raw = [p.encode("utf-8") for p in prompts]
         ptrs = (C.c_char_p * n)(*raw)
         lens = (C.c_size_t * n)(*[len(b) for b in raw])
         res = (RtResult * n)()
-        s = self._sampling(max_new_tokens, temperature, seed, ignore_eos)
+        s = self._sampling(max_new_tokens, temperature, seed, ignore_eos, top_k, top_p)
         _check(self._lib.rt_generate_batch(self._h, ptrs, lens, n, C.byref(s), deadline_ms, res), self._h)
         return self._collect(res, n)
 
@@ -350,6 +354,17 @@ def k_attention(q_bits, k_bits, v_bits, lens, shared: int = 0, chunk: int = 64, 
     _check(load_library().rt_k_attention(_p(q, C.c_uint16), _p(k, C.c_uint16), _p(v, C.c_uint16), _p(ln, C.c_int32),
                                          _p(out, C.c_float), T, ctx, n_q, n_kv, hd, shared, chunk, device))
     return out
+
+
+def k_sample_topkp(logits: np.ndarray, temperature: float, top_k: int = 0, top_p: float = 0.0, seed: int = 0, step: int = 0,
+                   device: int = 0):
+    """(tokens [T], kept-set sizes [T], thresholds [T]) of csrc/sampler.cuh on host logits [T][V]."""
+    logits = np.ascontiguousarray(logits, dtype=np.float32)
+    T, V = logits.shape
+    tok, kept, th = np.zeros(T, np.int32), np.zeros(T, np.int32), np.zeros(T, np.float32)
+    _check(load_library().rt_k_sample_topkp(_p(logits, C.c_float), T, V, temperature, top_k, top_p, seed, step,
+                                            _p(tok, C.c_int32), _p(kept, C.c_int32), _p(th, C.c_float), device))
+    return tok, kept, th
 
 
 def k_gemm_tc5(a_bits: np.ndarray, w_bits: np.ndarray, device: int = 0) -> np.ndarray:

@@ -32,8 +32,14 @@ def make_server(engine: Engine, model: str, host: str = "127.0.0.1", port: int =
         msgs = body.get("messages") or []
         if not msgs or not isinstance(msgs[-1], dict) or "content" not in msgs[-1]:
             raise ValueError("messages[-1].content missing")
+        # the reference adapter sends none of these (local-llm.ts:162-165) -> greedy, `max_new_tokens`; other OpenAI /
+        # Ollama clients may: honour the fields this backend has a kernel for
+        opts = body.get("options") if isinstance(body.get("options"), dict) else body
+        kw = dict(max_new_tokens=int(body.get("max_tokens") or opts.get("num_predict") or max_new_tokens),
+                  temperature=float(opts.get("temperature") or 0.0), top_k=int(opts.get("top_k") or 0),
+                  top_p=float(opts.get("top_p") or 0.0), seed=int(opts.get("seed") or 0))
         with lock:
-            return engine.generate(str(msgs[-1]["content"]), max_new_tokens=max_new_tokens, ignore_eos=ignore_eos).text
+            return engine.generate(str(msgs[-1]["content"]), ignore_eos=ignore_eos, **kw).text
 
     class Handler(BaseHTTPRequestHandler):
         protocol_version = "HTTP/1.1"
