@@ -51,6 +51,50 @@ __device__ __forceinline__ uint4 ld_stream16(const void* p) {
     return r;
 }
 
+// ---- optional in-kernel timeline (build with RT_NVCC_EXTRA=-DRT_TRACE; scripts/trace_timeline.py reads the dump) ----
+#ifdef RT_TRACE
+struct RtTraceRec { unsigned long long t; int tag; int cta; };
+static __device__ RtTraceRec* g_rt_trace = nullptr;
+static __device__ unsigned g_rt_trace_n = 0;
+constexpr unsigned RT_TRACE_CAP = 1u << 22;
+__device__ __forceinline__ void rt_trace(int tag) {
+    if (threadIdx.x == 0 && g_rt_trace) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        const unsigned i = atomicAdd(&g_rt_trace_n, 1u);
+        if (i < RT_TRACE_CAP) g_rt_trace[i] = {t, tag, (int)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z))};
+    }
+}
+#define RT_TR(tag) rt_trace(tag)
+#else
+#define RT_TR(tag)
+#endif
+
+// ---- weight stream pipelining through L2 -----------------------------------------------------------------------
+// A decode step is a chain of short HBM-bound kernels; between and inside some of them (attention on a short
+// context, the split-KV merge, every kernel's tail) HBM idles.  A kernel may therefore be handed a region of a LATER
+// kernel's weights: its CTAs each ask the memory system to pull one slice of it into the 126 MB L2
+// (cp.async.bulk.prefetch.L2: fire and forget, no destination, no completion to wait on), so that the weight stream
+// keeps flowing and the later kernel starts on L2 hits.
+struct L2Prefetch {
+    const void* ptr;
+    unsigned long long bytes;      // 0 = none
+};
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+// called by ONE thread of CTA `cta` of `n_cta`
+__device__ __forceinline__ void l2_prefetch_slice(const L2Prefetch& pf, int cta, int n_cta) {
+    if (pf.bytes == 0ull) return;
+    const unsigned long long per = ((pf.bytes + n_cta - 1) / n_cta + 127ull) & ~127ull;
+    const unsigned long long off = per * (unsigned long long)cta;
+    if (off >= pf.bytes) return;
+    unsigned long long n = pf.bytes - off < per ? pf.bytes - off : per;
+    n &= ~15ull;
+    const char* base = reinterpret_cast<const char*>(pf.ptr) + off;
+    for (unsigned long long o = 0; o < n; o += 32768ull) l2_prefetch_bulk(base + o, (unsigned)(n - o < 32768ull ? n - o : 32768ull));
+}
+
 // mma.sync m16n8k16 bf16 x bf16 -> fp32 (legacy tensor path; used only where the batch dimension is
 // 8..32 wide and the kernel is HBM-bound: decode GEMV and decode attention)
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,

@@ -336,6 +336,31 @@ void load_weights(rt_engine* e) {
     RT_CUDA(cudaStreamSynchronize(e->st));
 }
 
+#ifdef RT_TRACE
+// timeline dump (RT_TRACE_FILE): records of {globaltimer ns, tag, cta} written by thread 0 of every CTA
+static void trace_begin() {
+    RtTraceRec* buf = nullptr;
+    cudaMalloc(&buf, (size_t)RT_TRACE_CAP * sizeof(RtTraceRec));
+    unsigned zero = 0;
+    cudaMemcpyToSymbol(g_rt_trace_n, &zero, sizeof zero);
+    cudaMemcpyToSymbol(g_rt_trace, &buf, sizeof buf);
+}
+static void trace_end(const char* path) {
+    RtTraceRec* buf = nullptr;
+    unsigned n = 0;
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(&buf, g_rt_trace, sizeof buf);
+    cudaMemcpyFromSymbol(&n, g_rt_trace_n, sizeof n);
+    n = std::min(n, RT_TRACE_CAP);
+    std::vector<RtTraceRec> h(n);
+    cudaMemcpy(h.data(), buf, (size_t)n * sizeof(RtTraceRec), cudaMemcpyDeviceToHost);
+    if (FILE* f = fopen(path, "wb")) { fwrite(h.data(), sizeof(RtTraceRec), n, f); fclose(f); }
+    RtTraceRec* null = nullptr;
+    cudaMemcpyToSymbol(g_rt_trace, &null, sizeof null);
+    cudaFree(buf);
+}
+#endif
+
 // ---- launch helpers -----------------------------------------------------------------------------------
 // Every kernel of the step is launched with the programmatic-stream-serialization attribute (PDL): its CTAs may
 // become resident while the previous kernel drains, issue their first weight loads, and block in
@@ -591,6 +616,8 @@ void engine_init(rt_engine* e) {
     e->done_counter = dalloc<int>(e, 1);
     RT_CUDA(cudaMemsetAsync(e->done_counter, 0, sizeof(int), e->st));
     e->use_pdl = getenv("RT_NO_PDL") == nullptr;
+    e->pf_attn_bytes = (long long)env_int("RT_PF_ATTN_MB", 0) << 20;
+    e->pf_tail_bytes = (long long)env_int("RT_PF_TAIL_MB", 0) << 20;
     e->lm_ctas = e->vocab_l / 16;
     e->cta_max = zalloc_f((size_t)e->lm_ctas * 32);
     e->cta_idx = dalloc<int>(e, (size_t)e->lm_ctas * 32);
@@ -900,6 +927,12 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t; g.slot_seq = e->d_seq; g.slot_pos = e->d_pos;
         g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq; g.Q = e->qb; g.Kp = kp; g.Vp = vp;
         g.n_q = e->nq_l; g.n_kv = e->nkv_l; g.hd = hd;
+        // weight stream pipelining through L2 (common.cuh): what each kernel of the layer asks for ahead of its consumer
+        const size_t wo_bytes = (size_t)H * e->nq_l * hd * sizeof(bf16), wgu_bytes = (size_t)2 * e->F_l * H * sizeof(bf16);
+        const size_t wd_bytes = (size_t)H * e->F_l * sizeof(bf16), wqkv_bytes = (size_t)e->qkv_rows * H * sizeof(bf16);
+        const size_t attn_budget = (size_t)e->pf_attn_bytes, tail = (size_t)e->pf_tail_bytes;
+        const size_t pf_wo = std::min(wo_bytes, attn_budget), pf_wgu = std::min(wgu_bytes, attn_budget - pf_wo);
+        g.late_launch = env_int("RT_QKV_LATE_LAUNCH", 0);
         if (!(skip & 2)) gemv_dispatch<EPI_QKV>(e, g);
 
         AttnArgs a{};
@@ -908,6 +941,13 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         a.T = T; a.n_q = e->nq_l; a.n_kv = e->nkv_l; a.chunk_pages = o.chunk_pages; a.n_shared_tiles = o.n_shared_tiles;
         a.part_o = e->part_o; a.part_ml = e->part_ml; a.max_chunks = MAX_CHUNKS;
         a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd));
+        // Attention may set up its indices and fetch KV pages of older tokens before its PDL wait when nothing it reads
+        // there can still be in flight: inside the decode graph (a graph launch starts after the previous one, whose
+        // sampler advanced slot_pos, has completed), or after a QKV projection that releases it late (gemv.cuh).
+        static const int attn_early = env_int("RT_ATTN_EARLY", 1), late = env_int("RT_QKV_LATE_LAUNCH", 0);
+        a.early = attn_early && !(skip & 2) && (o.in_graph || late);
+        a.pf[0] = {w.wo, pf_wo};
+        a.pf[1] = {w.wgu, pf_wgu};
         if (!(skip & 4)) {
             // version 2 (CTA-shared page ring) is correct but measured slower in round 1 (profiles/r1_summary.md): opt-in
             static const int attn_v2 = env_int("RT_ATTN_V2", 0);
@@ -927,6 +967,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
 
         GemvArgs go{};
         go.W = w.wo; go.X = e->attn_bf; go.N = H; go.K = e->nq_l * hd; go.ldx = e->nq_l * hd; go.T = T;
+        if (pf_wgu < wgu_bytes) go.pf = {reinterpret_cast<const char*>(w.wgu) + pf_wgu, std::min(tail, wgu_bytes - pf_wgu)};
         if (!e->tp) {
             go.out = e->x; go.ldo = H;
             go.norm_w = w.norm2; go.xn_out = e->xn; go.ss_out = e->ss_part;
@@ -939,11 +980,14 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         gu.W = w.wgu; gu.N = 2 * e->F_l; gu.K = H; gu.T = T; gu.X = e->xn; gu.ldx = H;
         set_norm_scale(e, gu, false);
         gu.out_bf = e->act_bf; gu.ldob = e->F_l;
+        gu.pf = {w.wdown, std::min(tail, wd_bytes)};
         if (!(skip & 16)) gemv_dispatch<EPI_SWIGLU>(e, gu);
 
         GemvArgs gd{};
         gd.W = w.wdown; gd.X = e->act_bf; gd.N = H; gd.K = e->F_l; gd.ldx = e->F_l; gd.T = T;
         const bf16* next_norm = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;   // feeds the next layer's QKV, or the lm_head
+        if (l + 1 < e->L) gd.pf = {e->layers[l + 1].wqkv, std::min(tail, wqkv_bytes)};
+        else gd.pf = {e->lm_head, std::min(tail, (size_t)e->vocab_l * H * sizeof(bf16))};
         if (!e->tp) {
             gd.out = e->x; gd.ldo = H;
             gd.norm_w = next_norm; gd.xn_out = e->xn; gd.ss_out = e->ss_part;
@@ -1136,7 +1180,9 @@ static void ensure_graph(rt_engine* e, const StepOpts& o) {
     cudaGraph_t graph = nullptr;
     RT_CUDA(cudaStreamBeginCapture(e->st, cudaStreamCaptureModeThreadLocal));
     try {
-        engine_forward(e, o);
+        StepOpts og = o;
+        og.in_graph = true;
+        engine_forward(e, og);
     } catch (...) {
         cudaStreamEndCapture(e->st, &graph);
         if (graph) cudaGraphDestroy(graph);
@@ -1276,6 +1322,9 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
 
     const bool prof = getenv("RT_PROFILE_DECODE") != nullptr || (prof_phase && !strcmp(prof_phase, "decode"));
     if (prof) cudaProfilerStart();
+#ifdef RT_TRACE
+    if (getenv("RT_TRACE_FILE")) { RT_CUDA(cudaStreamSynchronize(e->st)); trace_begin(); }
+#endif
     RT_CUDA(cudaEventRecord(e->ev[2], e->st));
     while (steps_done < n_steps) {
         const int burst = std::min(16, n_steps - steps_done);
@@ -1307,6 +1356,9 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     RT_CUDA(cudaEventRecord(e->ev[3], e->st));
     RT_CUDA(cudaStreamSynchronize(e->st));
     if (prof) cudaProfilerStop();
+#ifdef RT_TRACE
+    if (const char* tf = getenv("RT_TRACE_FILE")) trace_end(tf);
+#endif
     float pre_ms = 0.f, dec_ms = 0.f;
     RT_CUDA(cudaEventElapsedTime(&pre_ms, e->ev[0], e->ev[1]));
     RT_CUDA(cudaEventElapsedTime(&dec_ms, e->ev[2], e->ev[3]));

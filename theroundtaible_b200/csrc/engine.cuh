@@ -34,6 +34,7 @@ struct StepOpts {
     int n_partials_max = 1;    // most partials any (slot, head) will have (fused merge capacity check)
     float inv_temp = 0.f;
     unsigned long long seed = 0;
+    bool in_graph = false;     // the step is being captured into the decode graph (consecutive steps fully serialised)
     int top_k = 0;             // sampler.cuh; only with inv_temp > 0
     float top_p = 0.f;
 };
@@ -83,6 +84,8 @@ struct rt_engine {
     float *x = nullptr, *qkv = nullptr, *delta = nullptr, *logits = nullptr;
     bf16 *xn = nullptr, *qb = nullptr, *attn_bf = nullptr, *act_bf = nullptr;
     float *part_o = nullptr, *part_ml = nullptr;
+    long long pf_attn_bytes = 0;   // weights pulled into L2 while a layer's attention runs (RT_PF_ATTN_MB)
+    long long pf_tail_bytes = 0;   // head of the NEXT projection's weights each projection asks for at its tail (RT_PF_TAIL_MB)
     float* ss_part = nullptr;      // [H/16][32] per-tile partial sums of x^2 (split RMSNorm, gemv.cuh)
     float* inv_rms = nullptr;      // [32] r per slot when a whole row was available (tensor parallel, prefill rows)
     float* pf_inv_rms = nullptr;   // [pf_cap]

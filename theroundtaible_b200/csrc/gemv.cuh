@@ -59,6 +59,8 @@ struct GemvArgs {
     float* cta_max;
     int* cta_idx;
     int row_offset;
+    int late_launch;          // QKV only: griddepcontrol.launch_dependents after the wait instead of at the start
+    L2Prefetch pf;            // a later kernel's weights: each CTA asks for its slice once its own stream is issued
     float inv_temp;
     unsigned long long seed;
     const int* step_ptr;
@@ -131,6 +133,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[mt][nt][i] = 0.f;
 
+    RT_TR(EPI * 10 + 0);
     // ---- first batch of weight loads: independent of the previous kernel, issued before the PDL wait ----
     uint4 av[U][MT][2];
 #pragma unroll
@@ -147,8 +150,46 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             }
         }
     }
-    griddep_launch();
+    // The QKV projection releases its dependent (the attention kernel) only AFTER its own wait: whatever that kernel
+    // does before ITS wait (index setup, KV pages of older tokens) then runs with every kernel before this one complete.
+    if (!(EPI == EPI_QKV && a.late_launch)) griddep_launch();
     griddep_wait();
+    if (EPI == EPI_QKV && a.late_launch) griddep_launch();
+    RT_TR(EPI * 10 + 1);
+
+    // ---- inputs of this thread's FIRST epilogue element, fetched now so that their L2 round trips (two dependent ones
+    // for the QKV epilogue: position -> rope table / page table) hide behind the weight stream ----
+    float pre_f0 = 0.f, pre_f1 = 0.f, pre_f2 = 0.f, pre_f3 = 0.f;
+    bf16* pre_dst = nullptr;
+    if (EPI == EPI_RESID) {
+        const int e = threadIdx.x;
+        const int r = e % (MT * 16), sl = e / (MT * 16), n = row0 + r;
+        if (e < MT * 16 * NT * 8 && sl < a.T && n < a.N) {
+            pre_f0 = a.out[(size_t)sl * a.ldo + n];
+            if (a.norm_w) pre_f1 = __bfloat162float(a.norm_w[n]);
+        }
+    } else if (EPI == EPI_QKV) {
+        const int e = threadIdx.x;
+        const int r = e % (MT * 8), sl = e / (MT * 8);
+        const int mt = r >> 3, rr = r & 7, n = row0 + mt * 16;
+        if (e < MT * 8 * NT * 8 && sl < a.T && n < a.N) {
+            const int half = a.hd >> 1;
+            if (a.bias) { pre_f2 = a.bias[n + rr]; pre_f3 = a.bias[n + rr + 8]; }
+            const int head = n / a.hd;
+            const int d = ((n % a.hd) >> 4) * 8 + rr;
+            const int pos = a.slot_pos[sl];
+            pre_f0 = 1.f;
+            if (head < a.n_q + a.n_kv) { pre_f0 = a.cos_t[(size_t)pos * half + d]; pre_f1 = a.sin_t[(size_t)pos * half + d]; }
+            if (head < a.n_q) {
+                pre_dst = a.Q + (size_t)sl * (a.n_q * a.hd) + (size_t)head * a.hd + d;
+            } else {
+                const bool is_k = head < a.n_q + a.n_kv;
+                const int kvh = head - a.n_q - (is_k ? 0 : a.n_kv);
+                const int page = a.page_table[(size_t)a.slot_seq[sl] * a.pt_stride + pos / KV_PAGE];
+                pre_dst = (is_k ? a.Kp : a.Vp) + (((size_t)page * a.n_kv + kvh) * KV_PAGE + (pos % KV_PAGE)) * a.hd + d;
+            }
+        }
+    }
 
     // RMSNorm scale of every slot (used in the epilogue only: these loads overlap the weight stream)
     if (a.ss_in || a.inv_rms) {
@@ -178,7 +219,9 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
                 const int slot = nt * 8 + g;
-                if (kb < kb1) {
+                // rows of unused slots are never fetched: every CTA reads the SAME activation rows, which makes the few
+                // L2 slices holding them the hot spot of a short kernel (measured: scripts/probes/gridbar.cu mode 2)
+                if (kb < kb1 && slot < a.T) {
                     xv[u][nt] = *reinterpret_cast<const uint4*>(a.X + (size_t)slot * a.ldx + ko);
                 } else {
                     xv[u][nt] = make_uint4(0, 0, 0, 0);
@@ -215,6 +258,11 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         }
     }
 
+    // this CTA's own weights are in: ask for its slice of a later kernel's (the reduction, the epilogue and the gap
+    // before the next launch then overlap with HBM traffic instead of leaving it idle)
+    if (threadIdx.x == 0) l2_prefetch_slice(a.pf, blockIdx.x, gridDim.x);
+    RT_TR(EPI * 10 + 2);
+
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
@@ -238,6 +286,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         res[tile][rr + 8][cc + 1] = s.w;
     }
     __syncthreads();
+    RT_TR(EPI * 10 + 3);
 
     if (EPI == EPI_STORE) {
         for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
@@ -255,10 +304,11 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             const int n = row0 + r;
             if (s < a.T && n < a.N) {
                 float* o = a.out + (size_t)s * a.ldo + n;
-                const float v = *o + res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                const bool first = e == (int)threadIdx.x;
+                const float v = (first ? pre_f0 : *o) + res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
                 *o = v;
                 if (a.norm_w) {
-                    a.xn_out[(size_t)s * a.N + n] = __float2bfloat16_rn(v * __bfloat162float(a.norm_w[n]));
+                    a.xn_out[(size_t)s * a.N + n] = __float2bfloat16_rn(v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])));
                     res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] = v;
                 }
             }
@@ -302,6 +352,13 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             if (s < a.T && n < a.N) {
                 float x1 = res[mt * NT + (s >> 3)][rr][s & 7] * s_rn[s];
                 float x2 = res[mt * NT + (s >> 3)][rr + 8][s & 7] * s_rn[s];
+                if (e == (int)threadIdx.x) {          // inputs fetched before the weight stream (see above)
+                    x1 += pre_f2;
+                    x2 += pre_f3;
+                    pre_dst[0] = __float2bfloat16_rn(x1 * pre_f0 - x2 * pre_f1);
+                    pre_dst[half] = __float2bfloat16_rn(x2 * pre_f0 + x1 * pre_f1);
+                    continue;
+                }
                 if (a.bias) {
                     x1 += a.bias[n + rr];
                     x2 += a.bias[n + rr + 8];
@@ -409,4 +466,5 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             }
         }
     }
+    RT_TR(EPI * 10 + 4);
 }

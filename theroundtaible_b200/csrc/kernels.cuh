@@ -213,6 +213,9 @@ struct AttnArgs {
     float* part_o;              // [T][n_q][max_chunks][hd]
     float* part_ml;             // [T][n_q][max_chunks][2]
     int max_chunks;
+    L2Prefetch pf[2];           // later kernels' weights to pull into L2 while this kernel runs (common.cuh)
+    int early;                  // 1 = index setup and old KV pages before the PDL wait (needs a producer that releases
+                                // this kernel only after its own wait: the engine's QKV projection does)
     float scale_log2;           // log2(e)/sqrt(hd)
     // version 2 (attn_decode2.cuh): exact 1-D grid = n_kv * (grid_nsh + T * grid_nown) CTAs, no empty CTAs
     int grid_nsh, grid_nown;
@@ -250,15 +253,29 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, HD == 128 ? 2 : 4) attn_decod
     constexpr int STAGE_BYTES = 2 * KV_PAGE * HD * 2;
     constexpr int KT = HD / 16;  // k-steps for QK^T; pairs of 8-wide d tiles for PV
 
+    RT_TR(50);
     griddep_launch();
-    griddep_wait();
+    if (threadIdx.x == 0) {     // weights do not depend on the previous kernel: before the PDL wait
+        const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z), n_cta = gridDim.x * gridDim.y * gridDim.z;
+        l2_prefetch_slice(a.pf[0], cta, n_cta);
+        l2_prefetch_slice(a.pf[1], cta, n_cta);
+    }
+    // ---- everything that does not depend on the QKV projection of THIS layer runs before the PDL wait: the index
+    // setup and the cp.async of KV pages that hold only OLDER tokens (their HBM latency hides behind that projection).
+    // Safe because the QKV kernel releases this one only after its own wait (gemv.cuh), i.e. with every earlier kernel
+    // -- the previous step's sampler, which advanced slot_pos, included -- complete.  `a.early` = 0 turns it off.
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
     const int h = blockIdx.y;
     const int G = a.n_q / a.n_kv;
     const int c = blockIdx.x * ATTN_WARPS + warp;
     const int C = a.chunk_pages * KV_PAGE;
+    if (!a.early) griddep_wait();
     const int sh = (a.n_shared_tiles > 0 && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
     const int nsh_chunks = (sh + C - 1) / C;
+    // keys below the lowest position any slot holds in this step were written by earlier steps
+    int min_pos = lane < a.T ? a.slot_pos[lane] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) min_pos = min(min_pos, __shfl_xor_sync(0xffffffffu, min_pos, o));
 
     int key0, key1, pidx, seq;
     int row_slot[2], row_head[2];
@@ -293,6 +310,28 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, HD == 128 ? 2 : 4) attn_decod
     }
     if (key0 >= key1) return;  // warp-uniform
 
+    const uint32_t sbase = smem_u32(smem_raw) + warp * (ATTN_STAGES * STAGE_BYTES);
+    const int* pt = a.page_table + (size_t)seq * a.pt_stride;
+    const int page0 = key0 / KV_PAGE;
+    const int npages = (key1 - key0 + KV_PAGE - 1) / KV_PAGE;
+    const size_t page_stride = (size_t)a.n_kv * KV_PAGE * HD;
+    const size_t head_off = (size_t)h * KV_PAGE * HD;
+
+    // ring prologue, old pages first (uncommitted: they join the first group committed below, which is waited for no
+    // later than they are needed)
+    unsigned early_mask = 0u;
+    if (a.early) {
+#pragma unroll
+        for (int s = 0; s < ATTN_STAGES - 1; ++s) {
+            if (s < npages && (page0 + s + 1) * KV_PAGE <= min_pos) {
+                attn_issue_page<HD>(sbase + s * STAGE_BYTES, a.Kp, a.Vp, (size_t)pt[page0 + s] * page_stride + head_off, lane);
+                early_mask |= 1u << s;
+            }
+        }
+        griddep_wait();
+    }
+    RT_TR(51);
+
     // Q fragments (A operand), loaded once
     uint32_t qa[KT][4];
     {
@@ -307,16 +346,10 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, HD == 128 ? 2 : 4) attn_decod
         }
     }
 
-    const uint32_t sbase = smem_u32(smem_raw) + warp * (ATTN_STAGES * STAGE_BYTES);
-    const int* pt = a.page_table + (size_t)seq * a.pt_stride;
-    const int page0 = key0 / KV_PAGE;
-    const int npages = (key1 - key0 + KV_PAGE - 1) / KV_PAGE;
-    const size_t page_stride = (size_t)a.n_kv * KV_PAGE * HD;
-    const size_t head_off = (size_t)h * KV_PAGE * HD;
-
 #pragma unroll
     for (int s = 0; s < ATTN_STAGES - 1; ++s) {
-        if (s < npages) attn_issue_page<HD>(sbase + s * STAGE_BYTES, a.Kp, a.Vp, (size_t)pt[page0 + s] * page_stride + head_off, lane);
+        if (s < npages && !(early_mask & (1u << s)))
+            attn_issue_page<HD>(sbase + s * STAGE_BYTES, a.Kp, a.Vp, (size_t)pt[page0 + s] * page_stride + head_off, lane);
         cp_async_commit();
     }
 
@@ -434,7 +467,7 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, HD == 128 ? 2 : 4) attn_decod
             *reinterpret_cast<float2*>(po + d * 8 + 2 * q) = make_float2(o[d][2 * r], o[d][2 * r + 1]);
         if (q == 0) *reinterpret_cast<float2*>(a.part_ml + base * 2) = make_float2(m_run[r], l_run[r]);
     }
-
+    RT_TR(54);
 }
 
 struct MergeArgs {
@@ -476,8 +509,10 @@ static __global__ void attn_merge_kernel(const MergeArgs a) {
 // i = warp, warp+4, ... in batches of 16 independent loads; the 4 warp sums are added in fixed order.
 template <int HD>
 static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs a) {
+    RT_TR(60);
     griddep_launch();
     griddep_wait();
+    RT_TR(61);
     constexpr int VD = HD / 32;
     __shared__ float sacc[4][HD];
     __shared__ float sL[4];
@@ -540,6 +575,7 @@ static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs
         if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * HD + threadIdx.x] = __float2bfloat16_rn(o);
         if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * HD + threadIdx.x] = o;
     }
+    RT_TR(64);
 }
 
 // Tensor parallel: every rank holds the local winners (score, token id) of all ranks after an all-gather; pick the
