@@ -425,14 +425,22 @@ int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
     // rows per CTA: the smallest 16*MT that fits the whole matrix into ONE wave of resident CTAs (2 per SM with 8 warps,
     // 1 per SM with 16 warps); matrices that need several waves anyway take 32-row CTAs, the lm_head 64-row CTAs
     const int tiles = a.N / 16;
-    const int capacity = e->sm_count * (gemv_warps(a.K) == 16 ? 1 : 2);
+    static const int cap16 = env_int("RT_GEMV_CAP16", 1);
+    const int capacity = e->sm_count * (gemv_warps(a.K) == 16 ? cap16 : 2);
     const int mt_max = 4 / NT;
     int mt = 1;
     while (mt < mt_max && (tiles + mt - 1) / mt > capacity) mt <<= 1;
     if ((tiles + mt - 1) / mt > capacity) mt = std::min(mt_max, tiles >= 4096 ? 4 : 2);
     while (mt > 1 && a.N % (16 * mt) != 0) mt >>= 1;
     if (force_mt && force_mt * NT <= 4 && a.N % (16 * force_mt) == 0) mt = force_mt;
-    const int grid = cdiv(a.N, 16 * mt);
+    int grid = cdiv(a.N, 16 * mt);
+    // more row groups than resident CTAs: a persistent grid of one full wave walks them (gemv.cuh), requesting the next
+    // group's first weights before the current group's reduction and epilogue
+    static const int persist = env_int("RT_GEMV_PERSIST", 1), persist_mt = env_int("RT_GEMV_PMT", 0);
+    if (persist && grid > capacity) {
+        if (persist_mt && persist_mt * NT <= 4 && a.N % (16 * persist_mt) == 0) mt = persist_mt;
+        grid = std::min(cdiv(a.N, 16 * mt), capacity);
+    }
     if (NT == 1) {
         if (mt == 4) gemv_pick_warps<EPI, 1, 4>(e, a, grid);
         else if (mt == 2) gemv_pick_warps<EPI, 1, 2>(e, a, grid);

@@ -111,51 +111,83 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     __shared__ int s_last;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
-    const int tile0 = blockIdx.x * MT;
-    const int row0 = tile0 * 16;
+    // A CTA owns the row groups tile0, tile0 + gridDim.x*MT, ... (one group when the grid covers the matrix: the usual
+    // single-wave case; several for the matrices with more tiles than two CTAs per SM can hold at once -- lm_head, the
+    // 8B+ gate/up -- where the host launches a persistent grid and the first weights of the NEXT group are requested
+    // before this group's reduction and epilogue, so the weight stream never pauses at a group boundary).
+    int tile0 = blockIdx.x * MT;
+    int row0 = tile0 * 16;
+    const int n_tiles = a.N >> 4;
     const int nkb = a.K >> 5;
     const int kb0 = (warp * nkb) / NW, kb1 = ((warp + 1) * nkb) / NW;
 
     // lane's byte offset inside a 512-byte half: piece (q*8 + g)
     const bf16* wbase[MT];
+    uint4 av[U][MT][2];
+    auto first_batch = [&](int t0) {
 #pragma unroll
-    for (int mt = 0; mt < MT; ++mt) {
-        int tile = tile0 + mt;
-        tile = tile * 16 < a.N ? tile : (a.N / 16 - 1);
-        wbase[mt] = a.W + (size_t)tile * nkb * 512 + (q * 8 + g) * 8;
-    }
+        for (int mt = 0; mt < MT; ++mt) {
+            int tile = t0 + mt;
+            tile = tile < n_tiles ? tile : (n_tiles - 1);
+            wbase[mt] = a.W + (size_t)tile * nkb * 512 + (q * 8 + g) * 8;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int kb = kb0 + u;
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+                if (kb < kb1) {
+                    av[u][mt][0] = ld_stream16(wbase[mt] + (size_t)kb * 512);
+                    av[u][mt][1] = ld_stream16(wbase[mt] + (size_t)kb * 512 + 256);
+                } else {
+                    av[u][mt][0] = make_uint4(0, 0, 0, 0);
+                    av[u][mt][1] = make_uint4(0, 0, 0, 0);
+                }
+            }
+        }
+    };
 
     float acc[MT][NT][4];
-#pragma unroll
-    for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) acc[mt][nt][i] = 0.f;
 
     RT_TR(EPI * 10 + 0);
     // ---- first batch of weight loads: independent of the previous kernel, issued before the PDL wait ----
-    uint4 av[U][MT][2];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-        const int kb = kb0 + u;
-#pragma unroll
-        for (int mt = 0; mt < MT; ++mt) {
-            if (kb < kb1) {
-                av[u][mt][0] = ld_stream16(wbase[mt] + (size_t)kb * 512);
-                av[u][mt][1] = ld_stream16(wbase[mt] + (size_t)kb * 512 + 256);
-            } else {
-                av[u][mt][0] = make_uint4(0, 0, 0, 0);
-                av[u][mt][1] = make_uint4(0, 0, 0, 0);
-            }
-        }
-    }
+    first_batch(tile0);
     // The QKV projection releases its dependent (the attention kernel) only AFTER its own wait: whatever that kernel
     // does before ITS wait (index setup, KV pages of older tokens) then runs with every kernel before this one complete.
     if (!(EPI == EPI_QKV && a.late_launch)) griddep_launch();
     griddep_wait();
     if (EPI == EPI_QKV && a.late_launch) griddep_launch();
     RT_TR(EPI * 10 + 1);
+
+    // RMSNorm scale of every slot (used in the epilogue only: these loads overlap the weight stream)
+    if (a.ss_in || a.inv_rms) {
+        for (int s = warp; s < NT * 8; s += NW) {
+            float v = 0.f;
+            if (s < a.T) {
+                if (a.inv_rms) {
+                    v = lane == 0 ? a.inv_rms[s] : 0.f;
+                } else {
+                    for (int p = lane; p < a.n_parts_in; p += 32) v += a.ss_in[p * 32 + s];
+                }
+            }
+            v = warp_sum(v);
+            if (lane == 0) s_rn[s] = s >= a.T ? 0.f : (a.inv_rms ? v : 1.0f / sqrtf(v / (float)a.K + a.eps));
+        }
+    } else if (threadIdx.x < NT * 8) {
+        s_rn[threadIdx.x] = 1.0f;
+    }
+
+    // LOGITS: arg-max candidate of this CTA over all its row groups (threads < NT*8)
+    float cand_best = -INFINITY;
+    int cand_idx = 0x7fffffff;
+
+    for (;;) {
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[mt][nt][i] = 0.f;
 
     // ---- inputs of this thread's FIRST epilogue element, fetched now so that their L2 round trips (two dependent ones
     // for the QKV epilogue: position -> rope table / page table) hide behind the weight stream ----
@@ -189,24 +221,6 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 pre_dst = (is_k ? a.Kp : a.Vp) + (((size_t)page * a.n_kv + kvh) * KV_PAGE + (pos % KV_PAGE)) * a.hd + d;
             }
         }
-    }
-
-    // RMSNorm scale of every slot (used in the epilogue only: these loads overlap the weight stream)
-    if (a.ss_in || a.inv_rms) {
-        for (int s = warp; s < NT * 8; s += NW) {
-            float v = 0.f;
-            if (s < a.T) {
-                if (a.inv_rms) {
-                    v = lane == 0 ? a.inv_rms[s] : 0.f;
-                } else {
-                    for (int p = lane; p < a.n_parts_in; p += 32) v += a.ss_in[p * 32 + s];
-                }
-            }
-            v = warp_sum(v);
-            if (lane == 0) s_rn[s] = s >= a.T ? 0.f : (a.inv_rms ? v : 1.0f / sqrtf(v / (float)a.K + a.eps));
-        }
-    } else if (threadIdx.x < NT * 8) {
-        s_rn[threadIdx.x] = 1.0f;
     }
 
     for (int kbb = kb0; kbb < kb1; kbb += U) {
@@ -260,7 +274,10 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 
     // this CTA's own weights are in: ask for its slice of a later kernel's (the reduction, the epilogue and the gap
     // before the next launch then overlap with HBM traffic instead of leaving it idle)
-    if (threadIdx.x == 0) l2_prefetch_slice(a.pf, blockIdx.x, gridDim.x);
+    const int next_tile0 = tile0 + (int)gridDim.x * MT;
+    const bool more = next_tile0 < n_tiles;          // block-uniform
+    if (more) first_batch(next_tile0);               // in flight during this group's reduction and epilogue
+    else if (threadIdx.x == 0) l2_prefetch_slice(a.pf, blockIdx.x, gridDim.x);
     RT_TR(EPI * 10 + 2);
 
 #pragma unroll
@@ -395,8 +412,6 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         }
         if (threadIdx.x < NT * 8) {
             const int s = threadIdx.x;
-            float best = -INFINITY;
-            int bi = 0x7fffffff;
             if (s < a.T) {
                 const int step = (a.inv_temp > 0.f && a.step_ptr) ? *a.step_ptr : 0;
                 for (int r = 0; r < MT * 16; ++r) {
@@ -404,11 +419,21 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                     if (n >= a.N) break;
                     float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] * s_rn[s];
                     if (a.inv_temp > 0.f) v = v * a.inv_temp + gumbel_noise(a.seed, step, s, a.row_offset + n);
-                    if (v > best) { best = v; bi = a.row_offset + n; }
+                    if (v > cand_best) { cand_best = v; cand_idx = a.row_offset + n; }      // rows ascend: lowest index wins ties
                 }
             }
-            a.cta_max[blockIdx.x * 32 + s] = best;
-            a.cta_idx[blockIdx.x * 32 + s] = bi;
+        }
+    }
+    if (!more) break;
+    tile0 = next_tile0;
+    row0 = tile0 * 16;
+    __syncthreads();                                 // red / res are reused by the next group
+    }
+
+    if (EPI == EPI_LOGITS) {
+        if (threadIdx.x < NT * 8) {
+            a.cta_max[blockIdx.x * 32 + threadIdx.x] = cand_best;
+            a.cta_idx[blockIdx.x * 32 + threadIdx.x] = cand_idx;
         }
         if (a.next_tok) {
             // the LAST CTA to publish its candidates picks the winners (lowest index wins ties, like torch.argmax)
