@@ -432,6 +432,9 @@ int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
     while (mt < mt_max && (tiles + mt - 1) / mt > capacity) mt <<= 1;
     if ((tiles + mt - 1) / mt > capacity) mt = std::min(mt_max, tiles >= 4096 ? 4 : 2);
     while (mt > 1 && a.N % (16 * mt) != 0) mt >>= 1;
+    // experiment: instead of growing the CTA until one wave covers the matrix, keep small row groups and walk them
+    static const int pmode = env_int("RT_GEMV_PMODE", 0);
+    if (pmode && tiles > capacity && pmode * NT <= 4 && a.N % (16 * pmode) == 0) mt = pmode;
     if (force_mt && force_mt * NT <= 4 && a.N % (16 * force_mt) == 0) mt = force_mt;
     int grid = cdiv(a.N, 16 * mt);
     // more row groups than resident CTAs: a persistent grid of one full wave walks them (gemv.cuh), requesting the next
