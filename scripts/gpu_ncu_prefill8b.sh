@@ -1,0 +1,8 @@
+#!/bin/bash
+# launch list of the prefill phase of config 3 (8B, 8,192 shared + 5 x 128 own tokens): one profiler pass
+mkdir -p gpurun_out
+export RT_PROFILE_PHASE=prefill
+python profiles/decode_probe.py llama-3.1-8b 2 5 8192 128 > gpurun_out/probe_plain.log 2>&1 || { echo "plain run failed"; exit 1; }
+tail -1 gpurun_out/probe_plain.log
+ncu --profile-from-start off --clock-control none --csv --log-file gpurun_out/r1c_launches_prefill_config3.csv --metrics gpu__time_duration.sum,launch__registers_per_thread python profiles/decode_probe.py llama-3.1-8b 2 5 8192 128 > gpurun_out/ncu_pf8b.log 2>&1
+echo "rc=$?"; tail -1 gpurun_out/ncu_pf8b.log

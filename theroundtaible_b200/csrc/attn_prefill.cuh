@@ -14,6 +14,12 @@
 #include "kernels.cuh"
 #include "prefill.cuh"
 
+// softmax weights P as bf16 hi + lo (two MMAs, as the decode kernel does) or as one bf16 (-DPFA_P_HILO=0: what most
+// flash-attention kernels feed the tensor core).  Measured on config 3: 261 vs 251 ms of prefill; with one bf16 the
+// typical logit error of the tiny hd-128 model rises from < 3e-3 to 3.4e-3 of max|logit| (bar: 1e-2), so hi + lo stays.
+#ifndef PFA_P_HILO
+#define PFA_P_HILO 1
+#endif
 constexpr int PFA_STAGES = 2;
 constexpr int PFA_TILE_PAGES = 4;
 
@@ -95,69 +101,81 @@ __global__ void __launch_bounds__(128) attn_prefill_kernel(const PfAttnArgs a) {
         cp_async_wait<1>();
         __syncthreads();
         const uint32_t stage = sbase + (tile % PFA_STAGES) * STAGE_BYTES;
-#pragma unroll 1
-        for (int pp = 0; pp < PFA_TILE_PAGES; ++pp) {
-            const int kbase = (tile * PFA_TILE_PAGES + pp) * KV_PAGE;
-            if (kbase >= warp_limit) break;                          // causal: nothing left for this warp (warp-uniform)
-            const uint32_t sK = stage + pp * PAGE_BYTES;
-            const uint32_t sV = sK + KV_PAGE * HD * 2;
-            float s[2][4];
+        // One online-softmax step per TILE (64 keys), not per page: the running max / rescale of the 16 x HD output
+        // fragment is amortised over 4 pages.  Pages at or beyond the warp's causal limit are skipped (warp-uniform).
+        const int kb_tile = tile * PFA_TILE_PAGES * KV_PAGE;
+        const int npg = kb_tile >= warp_limit ? 0 : min(PFA_TILE_PAGES, (warp_limit - kb_tile + KV_PAGE - 1) / KV_PAGE);
+        if (npg > 0) {
+            float s[PFA_TILE_PAGES][2][4];
 #pragma unroll
-            for (int j = 0; j < 2; ++j)
+            for (int pp = 0; pp < PFA_TILE_PAGES; ++pp) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) s[j][i] = 0.f;
-            {
-                const int m = lane >> 3, i8 = lane & 7;
-                const int key = (m >> 1) * 8 + i8;
+                for (int j = 0; j < 2; ++j)
 #pragma unroll
-                for (int t = 0; t < KT; ++t) {
-                    const int chunk = 2 * t + (m & 1);
-                    uint32_t r0, r1, r2, r3;
-                    ldmatrix_x4(r0, r1, r2, r3, sK + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
-                    mma_bf16_16816(s[0], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r0, r1);
-                    mma_bf16_16816(s[1], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r2, r3);
+                    for (int i = 0; i < 4; ++i) s[pp][j][i] = 0.f;
+                if (pp < npg) {
+                    const uint32_t sK = stage + pp * PAGE_BYTES;
+                    const int m = lane >> 3, i8 = lane & 7;
+                    const int key = (m >> 1) * 8 + i8;
+#pragma unroll
+                    for (int t = 0; t < KT; ++t) {
+                        const int chunk = 2 * t + (m & 1);
+                        uint32_t r0, r1, r2, r3;
+                        ldmatrix_x4(r0, r1, r2, r3, sK + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
+                        mma_bf16_16816(s[pp][0], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r0, r1);
+                        mma_bf16_16816(s[pp][1], qa[t][0], qa[t][1], qa[t][2], qa[t][3], r2, r3);
+                    }
                 }
             }
             float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
-            for (int j = 0; j < 2; ++j)
+            for (int pp = 0; pp < PFA_TILE_PAGES; ++pp)
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int key = kbase + j * 8 + 2 * q + (i & 1);
-                    const float v = key < row_limit[i >> 1] ? s[j][i] * a.scale_log2 : -INFINITY;
-                    s[j][i] = v;
-                    mx[i >> 1] = fmaxf(mx[i >> 1], v);
-                }
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int key = kb_tile + pp * KV_PAGE + j * 8 + 2 * q + (i & 1);
+                        const float v = (pp < npg && key < row_limit[i >> 1]) ? s[pp][j][i] * a.scale_log2 : -INFINITY;
+                        s[pp][j][i] = v;
+                        mx[i >> 1] = fmaxf(mx[i >> 1], v);
+                    }
             float alpha[2];
 #pragma unroll
             for (int r = 0; r < 2; ++r) {
                 mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
                 mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
-                const float mn = fmaxf(m_run[r], mx[r]);   // finite from page 0 on: key 0 is visible to every row
+                const float mn = fmaxf(m_run[r], mx[r]);   // finite from tile 0 on: key 0 is visible to every row
                 alpha[r] = exp2f(m_run[r] - mn);
                 m_run[r] = mn;
                 l_run[r] *= alpha[r];
             }
 #pragma unroll
-            for (int j = 0; j < 2; ++j)
+            for (int pp = 0; pp < PFA_TILE_PAGES; ++pp)
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float pv = exp2f(s[j][i] - m_run[i >> 1]);
-                    s[j][i] = pv;
-                    l_run[i >> 1] += pv;
-                }
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float pv = exp2f(s[pp][j][i] - m_run[i >> 1]);
+                        s[pp][j][i] = pv;
+                        l_run[i >> 1] += pv;
+                    }
 #pragma unroll
             for (int d = 0; d < HD / 8; ++d) {
                 o[d][0] *= alpha[0]; o[d][1] *= alpha[0];
                 o[d][2] *= alpha[1]; o[d][3] *= alpha[1];
             }
-            const uint32_t pa0 = pack_bf16(s[0][0], s[0][1]), pa1 = pack_bf16(s[0][2], s[0][3]);
-            const uint32_t pa2 = pack_bf16(s[1][0], s[1][1]), pa3 = pack_bf16(s[1][2], s[1][3]);
-            const uint32_t pl0 = pack_bf16(s[0][0] - bf16lo(pa0), s[0][1] - bf16hi(pa0));
-            const uint32_t pl1 = pack_bf16(s[0][2] - bf16lo(pa1), s[0][3] - bf16hi(pa1));
-            const uint32_t pl2 = pack_bf16(s[1][0] - bf16lo(pa2), s[1][1] - bf16hi(pa2));
-            const uint32_t pl3 = pack_bf16(s[1][2] - bf16lo(pa3), s[1][3] - bf16hi(pa3));
-            {
+#pragma unroll
+            for (int pp = 0; pp < PFA_TILE_PAGES; ++pp) {
+                if (pp >= npg) continue;
+                const uint32_t sV = stage + pp * PAGE_BYTES + KV_PAGE * HD * 2;
+                const uint32_t pa0 = pack_bf16(s[pp][0][0], s[pp][0][1]), pa1 = pack_bf16(s[pp][0][2], s[pp][0][3]);
+                const uint32_t pa2 = pack_bf16(s[pp][1][0], s[pp][1][1]), pa3 = pack_bf16(s[pp][1][2], s[pp][1][3]);
+#if PFA_P_HILO
+                const uint32_t pl0 = pack_bf16(s[pp][0][0] - bf16lo(pa0), s[pp][0][1] - bf16hi(pa0));
+                const uint32_t pl1 = pack_bf16(s[pp][0][2] - bf16lo(pa1), s[pp][0][3] - bf16hi(pa1));
+                const uint32_t pl2 = pack_bf16(s[pp][1][0] - bf16lo(pa2), s[pp][1][1] - bf16hi(pa2));
+                const uint32_t pl3 = pack_bf16(s[pp][1][2] - bf16lo(pa3), s[pp][1][3] - bf16hi(pa3));
+#endif
                 const int m = lane >> 3, i8 = lane & 7;
                 const int key = (m & 1) * 8 + i8;
 #pragma unroll
@@ -166,9 +184,11 @@ __global__ void __launch_bounds__(128) attn_prefill_kernel(const PfAttnArgs a) {
                     uint32_t r0, r1, r2, r3;
                     ldmatrix_x4_trans(r0, r1, r2, r3, sV + key * (HD * 2) + ((chunk ^ attn_swz<HD>(key)) << 4));
                     mma_bf16_16816(o[2 * dp], pa0, pa1, pa2, pa3, r0, r1);
-                    mma_bf16_16816(o[2 * dp], pl0, pl1, pl2, pl3, r0, r1);
                     mma_bf16_16816(o[2 * dp + 1], pa0, pa1, pa2, pa3, r2, r3);
+#if PFA_P_HILO
+                    mma_bf16_16816(o[2 * dp], pl0, pl1, pl2, pl3, r0, r1);
                     mma_bf16_16816(o[2 * dp + 1], pl0, pl1, pl2, pl3, r2, r3);
+#endif
                 }
             }
         }

@@ -1096,6 +1096,9 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
                 }
             s0 = s1;
         }
+        // longest first: an item walks the keys 0 .. position of its last token, so the late tokens of a long prompt are
+        // the heavy items; issuing them first keeps the last wave of CTAs short
+        std::stable_sort(hw, hw + n_items, [&](const int4& x, const int4& y) { return hp[x.x] + x.y > hp[y.x] + y.y; });
         RT_CUDA(cudaMemcpyAsync(e->pf_tok, ht, S * sizeof(int), cudaMemcpyHostToDevice, e->st));
         RT_CUDA(cudaMemcpyAsync(e->pf_seq, hs, S * sizeof(int), cudaMemcpyHostToDevice, e->st));
         RT_CUDA(cudaMemcpyAsync(e->pf_pos, hp, S * sizeof(int), cudaMemcpyHostToDevice, e->st));
