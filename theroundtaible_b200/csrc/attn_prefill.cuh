@@ -20,11 +20,14 @@
 #ifndef PFA_P_HILO
 #define PFA_P_HILO 1
 #endif
+#ifndef PFA_MIN_CTAS
+#define PFA_MIN_CTAS 3
+#endif
 constexpr int PFA_STAGES = 2;
 constexpr int PFA_TILE_PAGES = 4;
 
 template <int HD>
-__global__ void __launch_bounds__(128) attn_prefill_kernel(const PfAttnArgs a) {
+__global__ void __launch_bounds__(128, PFA_MIN_CTAS) attn_prefill_kernel(const PfAttnArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int PAGE_BYTES = 2 * KV_PAGE * HD * 2;              // K + V of one page of one head
     constexpr int STAGE_BYTES = PFA_TILE_PAGES * PAGE_BYTES;

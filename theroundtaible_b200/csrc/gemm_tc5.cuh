@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
     volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - smem_u32(smem)));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m_blk = blockIdx.y, n_blk = blockIdx.x;
+    const int m_blk = blockIdx.x, n_blk = blockIdx.y;
     const int num_kb = a.K / G5_BK;
 
     if (threadIdx.x == 0) {

@@ -29,7 +29,11 @@ void launch_gemm5(cudaStream_t st, bool pdl, const CUtensorMap& ma, const CUtens
     const size_t smem = gemm5_smem_bytes(BN);
     RT_CUDA(cudaFuncSetAttribute(gemm_tc5_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(cdiv(a.N, BN), cdiv(a.S, G5_BM));
+    // token blocks fastest: the CTAs in flight (one per SM, dispatched in x-then-y order) then cover ALL token blocks of a
+    // few weight-row blocks, so a weight tile comes from HBM once and from L2 for the other token blocks, and the
+    // activations (<= 2,048 x K, L2-resident) are what every CTA shares.  Weight blocks fastest re-streamed an 8B
+    // gate/up matrix (235 MB > L2) from HBM once per token block.
+    cfg.gridDim = dim3(cdiv(a.S, G5_BM), cdiv(a.N, BN));
     cfg.blockDim = dim3(192);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
