@@ -1,0 +1,8 @@
+#!/bin/bash
+# one full-set capture of the prefill attention kernel on the config-3 shape (8B, head_dim 128, 8k keys)
+mkdir -p gpurun_out
+export RT_PROFILE_PHASE=prefill
+python profiles/decode_probe.py llama-3.1-8b 2 5 8192 128 > gpurun_out/probe_plain.log 2>&1 || { echo "plain run failed"; exit 1; }
+tail -1 gpurun_out/probe_plain.log
+ncu --profile-from-start off --clock-control none --set full --import-source on -k regex:attn_prefill -s 100 -c 2 -o gpurun_out/r1c_pfattn8b python profiles/decode_probe.py llama-3.1-8b 2 5 8192 128 > gpurun_out/ncu_pfattn.log 2>&1
+echo "rc=$?"; tail -1 gpurun_out/ncu_pfattn.log

@@ -13,6 +13,7 @@
 #include <memory>
 
 #include "attn_decode2.cuh"
+#include "attn_decode3.cuh"
 #include "gemv_stream.cuh"
 #include "kernels.cuh"
 #include "safetensors.h"
@@ -499,6 +500,34 @@ void rt_attn_host_setup() {
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(128)));
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(64)));
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(32)));
+    RT_CUDA(cudaFuncSetAttribute(attn_decode3_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, a3_smem_bytes<128>()));
+    RT_CUDA(cudaFuncSetAttribute(attn_decode3_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, a3_smem_bytes<64>()));
+    RT_CUDA(cudaFuncSetAttribute(attn_decode3_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, a3_smem_bytes<32>()));
+}
+
+// version 3 (attn_decode3.cuh): one cluster of `cs` CTAs per (slot, kv head), partials merged through distributed shared
+// memory; PDL attribute and cluster dimension on the same launch
+template <int HD>
+static void attn3_launch_hd(rt_engine* e, const Attn3Args& a, int cs) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(cs, a.n_kv, a.T);
+    cfg.blockDim = dim3(A3_WARPS * 32);
+    cfg.dynamicSmemBytes = a3_smem_bytes<HD>();
+    cfg.stream = e->st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = e->use_pdl ? 2 : 1;
+    RT_CUDA(cudaLaunchKernelEx(&cfg, attn_decode3_kernel<HD>, a));
+    e->launches++;
+}
+void rt_attn3_host_launch(rt_engine* e, const Attn3Args& a, int hd, int cs) {
+    if (hd == 128) attn3_launch_hd<128>(e, a, cs);
+    else if (hd == 64) attn3_launch_hd<64>(e, a, cs);
+    else attn3_launch_hd<32>(e, a, cs);
 }
 
 template <int HD, int NWARP>
@@ -964,6 +993,13 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
             static const int attn_v2 = env_int("RT_ATTN_V2", 0);
             a.grid_nsh = o.n_shared_tiles > 0 ? o.n_sh : 0;
             a.grid_nown = o.n_own;
+            if (o.attn3_cs > 0 && T <= 8) {
+                Attn3Args a3{};
+                a3.Q = a.Q; a3.ldq = a.ldq; a3.Kp = kp; a3.Vp = vp; a3.page_table = a.page_table; a3.pt_stride = a.pt_stride;
+                a3.slot_seq = a.slot_seq; a3.slot_pos = a.slot_pos; a3.T = T; a3.n_q = a.n_q; a3.n_kv = a.n_kv;
+                a3.scale_log2 = a.scale_log2; a3.out = e->attn_bf; a3.ldo = e->nq_l * hd; a3.early = a.early;
+                rt_attn3_host_launch(e, a3, hd, o.attn3_cs);
+            } else {
             if (attn_v2 && o.n_shared_tiles <= 4) rt_attn2_host_launch(e, a, hd, o.n_chunks);
             else rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
             MergeArgs m{};
@@ -974,6 +1010,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
             if (hd == 128) launch_pdl(e, attn_merge2_kernel<128>, mg, dim3(128), 0, m);
             else if (hd == 64) launch_pdl(e, attn_merge2_kernel<64>, mg, dim3(128), 0, m);
             else launch_pdl(e, attn_merge2_kernel<32>, mg, dim3(128), 0, m);
+            }
         }
 
         GemvArgs go{};
@@ -1026,6 +1063,14 @@ static void plan_chunks(int max_len, int shared_len, StepOpts& o, int hd = 64) {
     o.n_own = n_own;
     if (n_sh + n_own + 1 > MAX_CHUNKS) throw RtError(RT_ERR_INVALID, "attention split exceeds MAX_CHUNKS");
     o.n_partials_max = n_sh + n_own;
+    // short contexts: the cluster-merged kernel (no merge launch, no cascade); <= RT_ATTN3_PPW pages per warp
+    static const int a3_on = env_int("RT_ATTN_V3", 1), a3_ppw = env_int("RT_ATTN3_PPW", 4);
+    o.attn3_cs = 0;
+    if (a3_on && total_pages <= 8 * A3_WARPS * a3_ppw) {
+        int cs = 1;
+        while (cs * A3_WARPS * a3_ppw < total_pages) cs <<= 1;
+        o.attn3_cs = cs;
+    }
 }
 
 static void check_deadline(double t0, uint64_t deadline_ms) {
@@ -1184,7 +1229,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
 static void ensure_graph(rt_engine* e, const StepOpts& o) {
     const StepOpts& g = e->graph_opts;
     if (e->graph_exec && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks && g.n_sh == o.n_sh && g.n_own == o.n_own &&
-        g.n_shared_tiles == o.n_shared_tiles && g.inv_temp == o.inv_temp && g.seed == o.seed && g.top_k == o.top_k && g.top_p == o.top_p)
+        g.n_shared_tiles == o.n_shared_tiles && g.attn3_cs == o.attn3_cs && g.inv_temp == o.inv_temp && g.seed == o.seed && g.top_k == o.top_k && g.top_p == o.top_p)
         return;
     if (e->graph_exec) {
         cudaGraphExecDestroy(e->graph_exec);

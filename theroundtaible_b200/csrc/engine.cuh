@@ -34,6 +34,7 @@ struct StepOpts {
     int n_partials_max = 1;    // most partials any (slot, head) will have (fused merge capacity check)
     float inv_temp = 0.f;
     unsigned long long seed = 0;
+    int attn3_cs = 0;          // > 0: cluster-merged decode attention (attn_decode3.cuh) with this cluster size
     bool in_graph = false;     // the step is being captured into the decode graph (consecutive steps fully serialised)
     int top_k = 0;             // sampler.cuh; only with inv_temp > 0
     float top_p = 0.f;
