@@ -1065,8 +1065,13 @@ static void plan_chunks(int max_len, int shared_len, StepOpts& o, int hd = 64) {
     o.n_partials_max = n_sh + n_own;
     // short contexts: the cluster-merged kernel (no merge launch, no cascade); <= RT_ATTN3_PPW pages per warp
     static const int a3_on = env_int("RT_ATTN_V3", 1), a3_ppw = env_int("RT_ATTN3_PPW", 4);
+    // ... and while what the knights would re-read of a shared prefix (version 3 has no cascade phase) stays small:
+    // (T - 1) x shared pages x page bytes per kv head <= RT_ATTN3_REDUNDANT_KB (measured: config 2, 3 knights x 1k shared
+    // at head_dim 64 = 0.5 MB: version 3 is 9 % faster per step; config 4, 8 knights x 2k at head_dim 128 = 7 MB: 3 % slower)
+    static const int a3_red_kb = env_int("RT_ATTN3_REDUNDANT_KB", 2048);
+    const long long redundant = (long long)std::max(o.T - 1, 0) * (shared_len / KV_PAGE) * (2ll * KV_PAGE * hd * 2);
     o.attn3_cs = 0;
-    if (a3_on && total_pages <= 8 * A3_WARPS * a3_ppw) {
+    if (a3_on && total_pages <= 8 * A3_WARPS * a3_ppw && redundant <= (long long)a3_red_kb * 1024) {
         int cs = 1;
         while (cs * A3_WARPS * a3_ppw < total_pages) cs <<= 1;
         o.attn3_cs = cs;
