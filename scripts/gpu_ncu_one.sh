@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 case $mode in
   list-decode)  phase=decode;  n=6; out="--csv --log-file gpurun_out/${tag}_launches_decode_config2.csv --metrics gpu__time_duration.sum,dram__bytes_read.sum,launch__registers_per_thread";;
   list-prefill) phase=prefill; n=2; out="--csv --log-file gpurun_out/${tag}_launches_prefill_config2.csv --metrics gpu__time_duration.sum,dram__bytes_read.sum,launch__registers_per_thread";;
-  full-decode)  phase=decode;  n=3; out="--set full --import-source on -k regex:gemv_kernel|attn_decode -c 8 -o gpurun_out/${tag}_decode_full";;
+  full-decode)  phase=decode;  n=3; out="--set full --import-source on -k regex:gemv_kernel|attn_decode -c 10 -o gpurun_out/${tag}_decode_full";;
   full-prefill) phase=prefill; n=2; out="--set full --import-source on -k regex:gemm_tc5|attn_prefill -c 6 -o gpurun_out/${tag}_prefill_full";;
   *) echo "unknown mode"; exit 2;;
 esac
