@@ -271,3 +271,70 @@ def test_adapter_execute_returns_nonempty_text_and_round_batches():
     texts = ad.execute_round([head + n for n in ("Claude", "Gemini", "GPT")])
     assert len(texts) == 3 and all(len(t) > 0 for t in texts)
     assert texts[0] == ad.execute(head + "Claude") or True            # SEQ and BATCH agree up to tie-breaks
+
+
+def test_config2_architecture_full_depth_llama32_1b():
+    """BASELINE.json configs[1] names Llama-3.2-1B: the FULL 16-layer architecture (llama3 rope scaling, 32/8 heads, tied
+    128,256-token head) against the oracle: teacher-forced logits through both kernel paths, then 3 knights sharing a
+    prefix, greedy, under the margin-aware rule.
+
+    Tolerance, as measured (scripts/parity_probe_1b.py): with random N(0, 0.02) weights the logits of
+    this model are small (max |logit| ~ 4 over 128k entries) and the bf16 rounding of the activations -- the numerics
+    contract itself -- moves them by 1.5-2.1e-2 of max |logit| (oracle with vs without that rounding); two evaluation
+    orders of the SAME contract (the engine's prefill and decode kernels) differ by up to 1.3e-2.  The 1e-2 bar that the
+    tiny, 0.5B and truncated-depth models meet is therefore AT the rounding-noise floor here.  What is asserted: the RMS
+    error over the vocabulary stays below 3e-3 of max |logit|, the worst single logit below 1.5e-2, and the engine sits
+    closer to the oracle than the oracle's own rounding sits to exact activations."""
+    a = ARCHS["llama-3.2-1b"]
+    oracle = OracleModel(a, 0, max_pos=256)
+    rng = np.random.default_rng(1234 + 2)
+    ids = rng.integers(0, a.vocab, 72)
+    ref = oracle.forward(ids, KVState(), round_act=True).numpy()
+    exact_act = oracle.forward(ids, KVState(), round_act=False).numpy()
+    scale = np.abs(ref).max(-1)
+    floor = (np.abs(ref - exact_act).max(-1) / scale).max()
+    with E.Engine("llama-3.2-1b", seed=0, max_batch=3, max_ctx=256) as eng:
+        eng.seq_reset()
+        got1 = eng.step_logits(ids, mode=1)
+        eng.seq_reset()
+        got0 = eng.step_logits(ids[:40], mode=0)
+        for got, want, sc in ((got1, ref, scale), (got0, ref[:40], scale[:40])):
+            worst = (np.abs(got - want).max(-1) / sc).max()
+            rms = (np.sqrt(((got - want) ** 2).mean(-1)) / sc).max()
+            assert rms <= 3e-3, rms
+            assert worst <= 1.5e-2 and worst < floor, (worst, floor)
+        prompts = [ids[:48].tolist() + rng.integers(0, a.vocab, 10 + i).tolist() for i in range(3)]
+        gens = eng.generate_ids(prompts, max_new_tokens=24)
+    bound = 1.5e-2 * float(np.abs(ref).max())
+    ties = sum(_greedy_compare(g.tokens, oracle, p, 24, err_bound=bound) for p, g in zip(prompts, gens))
+    assert ties <= 4
+
+
+def test_config2_full_size_properties():
+    """BASELINE config 2 at its full size (3 knights, Llama-3.2-1B, 1,024 shared + 64 own prompt tokens) is beyond what
+    the CPU oracle finishes in seconds, so it is checked through properties that do not need it: a round is
+    bit-reproducible; a sequence's tokens do not depend on which other knights share its batch or on whether its prefix
+    came from the shared pages, the cross-call cache or its own prefill (up to one near-tie); every generated id is a
+    valid token and the counts add up."""
+    w = dict(knights=3, shared=1024, own=64, new=48)
+    rng = np.random.default_rng(1234 + 2)
+    with E.Engine("llama-3.2-1b", seed=0, max_batch=3, max_ctx=2048) as eng:
+        vocab = eng.vocab
+        common = rng.integers(0, vocab, w["shared"]).tolist()
+        prompts = [common + rng.integers(0, vocab, w["own"]).tolist() for _ in range(w["knights"])]
+        a = eng.generate_ids(prompts, max_new_tokens=w["new"])
+        b = eng.generate_ids(prompts, max_new_tokens=w["new"])
+        assert [g.tokens for g in a] == [g.tokens for g in b]                       # run-to-run bit-identical
+        assert all(len(g.tokens) == w["new"] and all(0 <= t < vocab for t in g.tokens) for g in a)
+        assert [g.prefix_shared_tokens for g in a] == [0, 1024, 1024] and a[0].n_prompt_tokens == 1088
+        solo = [eng.generate_ids([p], max_new_tokens=w["new"])[0] for p in prompts]        # SEQ: one knight per call
+    same = sum(x.tokens == y.tokens for x, y in zip(a, solo))
+    assert same >= 2, [next((i for i, (s, t) in enumerate(zip(x.tokens, y.tokens)) if s != t), None) for x, y in zip(a, solo)]
+    with E.Engine("llama-3.2-1b", seed=0, max_batch=3, max_ctx=2048, flags=E.RT_FLAG_PREFIX_CACHE) as eng:
+        first = eng.generate_ids([prompts[0]], max_new_tokens=w["new"])[0]
+        again = eng.generate_ids([prompts[0]], max_new_tokens=w["new"])[0]
+        other = eng.generate_ids([prompts[1]], max_new_tokens=w["new"])[0]
+    assert first.prefix_cached_tokens == 0 and again.prefix_cached_tokens >= 1072 and other.prefix_cached_tokens == 1024
+    assert first.tokens == solo[0].tokens                                           # the cache flag alone changes nothing
+    assert again.tokens == first.tokens                                             # KV from the cache == KV recomputed
+    assert sum(x == y for x, y in zip(other.tokens, solo[1].tokens)) >= w["new"] - 1 or other.tokens[:8] == solo[1].tokens[:8]
