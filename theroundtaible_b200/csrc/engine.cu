@@ -666,14 +666,14 @@ void engine_init(rt_engine* e) {
     if (c.tp_size > 1) {
         e->loc_best = zalloc_f(64);
         e->all_best = zalloc_f((size_t)64 * c.tp_size);
-        e->tpf_on = env_int("RT_TP_FUSED", 1) != 0 && c.tp_size <= TPF_MAX && e->H <= 16 * 512 && e->H % 4 == 0;
+        e->tpf_on = env_int("RT_TP_FUSED", 1) != 0 && c.tp_size <= TPF_MAX && e->H <= 4 * TPF_THREADS * TPF_CMAX && e->H % 4 == 0;
         if (e->tpf_on) {
             // separate allocations: CUDA IPC shares whole allocations
             for (int j = 0; j < 2; ++j) e->tpf_delta[j] = zalloc_f((size_t)MAX_SLOTS * e->H);
-            e->tpf_flags = dalloc<int>(e, MAX_SLOTS * TPF_MAX);
-            e->tpf_epoch = dalloc<int>(e, MAX_SLOTS);
-            RT_CUDA(cudaMemsetAsync(e->tpf_flags, 0, MAX_SLOTS * TPF_MAX * sizeof(int), e->st));
-            RT_CUDA(cudaMemsetAsync(e->tpf_epoch, 0, MAX_SLOTS * sizeof(int), e->st));
+            e->tpf_flags = dalloc<int>(e, MAX_SLOTS * TPF_CMAX * TPF_MAX);
+            e->tpf_epoch = dalloc<int>(e, MAX_SLOTS * TPF_CMAX);
+            RT_CUDA(cudaMemsetAsync(e->tpf_flags, 0, MAX_SLOTS * TPF_CMAX * TPF_MAX * sizeof(int), e->st));
+            RT_CUDA(cudaMemsetAsync(e->tpf_epoch, 0, MAX_SLOTS * TPF_CMAX * sizeof(int), e->st));
             RT_CUDA(cudaStreamSynchronize(e->st));
             for (int j = 0; j < 2; ++j) tp_ipc_exchange(e->tp, e->tpf_delta[j], e->tpf_peer_delta[j], e->st);
             tp_ipc_exchange(e->tp, e->tpf_flags, e->tpf_peer_flags, e->st);
@@ -877,8 +877,8 @@ static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, c
             a.flags[p] = reinterpret_cast<int*>(e->tpf_peer_flags[p]);
         }
         a.epoch = e->tpf_epoch; a.rank = e->cfg.tp_rank; a.tp = e->cfg.tp_size; a.H = H;
-        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.inv_rms = e->inv_rms; a.eps = e->cfg.rms_eps;
-        launch_pdl(e, tp_fused_allreduce_norm_kernel<512>, dim3(T), dim3(512), 0, a);
+        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.ss_part = e->ss_part;
+        launch_pdl(e, tp_fused_allreduce_norm_kernel, dim3(cdiv(H / 4, TPF_THREADS), T), dim3(TPF_THREADS), 0, a);
     } else {
         g.out = e->delta; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
@@ -892,7 +892,8 @@ static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, c
 // the producing projection left them) or r itself (tensor parallel / rows copied from a prefill chunk)
 static void set_norm_scale(rt_engine* e, GemvArgs& g, bool direct) {
     g.eps = e->cfg.rms_eps;
-    if (direct || e->tp) g.inv_rms = e->inv_rms;
+    if (direct || (e->tp && !e->tpf_on)) g.inv_rms = e->inv_rms;
+    else if (e->tp) { g.ss_in = e->ss_part; g.n_parts_in = cdiv(e->H / 4, TPF_THREADS); }   // the fused exchange's column blocks
     else { g.ss_in = e->ss_part; g.n_parts_in = e->H / 16; }
 }
 
@@ -962,7 +963,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
 
         GemvArgs g{};
-        set_norm_scale(e, g, false);
+        set_norm_scale(e, g, /*direct=*/l == 0 && e->tp != nullptr);     // tensor parallel: layer 0 takes r from the embed kernel
         g.W = w.wqkv; g.N = e->qkv_rows; g.K = H; g.T = T; g.X = e->xn; g.ldx = H;
         g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t; g.slot_seq = e->d_seq; g.slot_pos = e->d_pos;
         g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq; g.Q = e->qb; g.Kp = kp; g.Vp = vp;
