@@ -393,14 +393,17 @@ int env_int(const char* name, int dflt) {
 }
 
 // 16 warps only for very long rows (down-projection, K = FFN >= 8192): measured on B200 (scripts/gemv_tune*.py)
-inline int gemv_warps(int K) {
-    static const int force = env_int("RT_GEMV_NW", 0);
-    return force ? force : (K >= 8192 ? 16 : 8);
+// 16 warps split a long K (each warp then issues enough batches to hide the latency of the others) -- and also a
+// matrix with fewer row tiles than SMs (tensor-parallel QKV / O shards): with one CTA on most SMs, twice the warps means
+// twice the loads in flight per SM
+inline int gemv_warps(int K, int tiles = 1 << 30) {
+    static const int force = env_int("RT_GEMV_NW", 0), few = env_int("RT_GEMV_NW16_TILES", 0);
+    return force ? force : ((K >= 8192 || (tiles <= few && K >= 2048)) ? 16 : 8);
 }
 
 template <int EPI, int NT, int MT>
 void gemv_pick_warps(rt_engine* e, const GemvArgs& a, int grid) {
-    if (gemv_warps(a.K) == 16) gemv_launch<EPI, NT, MT, 16>(e, a, grid);
+    if (gemv_warps(a.K, a.N / 16) == 16) gemv_launch<EPI, NT, MT, 16>(e, a, grid);
     else gemv_launch<EPI, NT, MT, 8>(e, a, grid);
 }
 
@@ -427,7 +430,7 @@ int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
     // 1 per SM with 16 warps); matrices that need several waves anyway take 32-row CTAs, the lm_head 64-row CTAs
     const int tiles = a.N / 16;
     static const int cap16 = env_int("RT_GEMV_CAP16", 1);
-    const int capacity = e->sm_count * (gemv_warps(a.K) == 16 ? cap16 : 2);
+    const int capacity = e->sm_count * (gemv_warps(a.K, a.N / 16) == 16 ? cap16 : 2);
     const int mt_max = 4 / NT;
     int mt = 1;
     while (mt < mt_max && (tiles + mt - 1) / mt > capacity) mt <<= 1;
