@@ -13,8 +13,10 @@ from theroundtaible_b200 import engine as E
 pytestmark = pytest.mark.gpu
 
 
-def _rank_main(rank, tp, nccl_id, name, seed, prompts, n_new, mode, q):
+def _rank_main(rank, tp, nccl_id, name, seed, prompts, n_new, mode, q, env=None):
     try:
+        import os
+        os.environ.update(env or {})
         torch.cuda.set_device(rank)
         with E.Engine(name, seed=seed, device=rank, max_batch=len(prompts), max_ctx=256, tp_rank=rank, tp_size=tp,
                       nccl_id=nccl_id) as eng:
@@ -28,8 +30,9 @@ def _rank_main(rank, tp, nccl_id, name, seed, prompts, n_new, mode, q):
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 # tiny-qwen has 7 q heads x 32 dims per rank: not a multiple of 64, so its prompts take the slab path (mode 0)
-@pytest.mark.parametrize("name,mode", [("tiny-llama", 1), ("tiny-qwen", 0)])
-def test_tp2_generation_and_logits_match_oracle(name, mode):
+# third case: the opt-in push variant of the exchange (projection epilogue stores into the peers, RT_TP_PUSH=1)
+@pytest.mark.parametrize("name,mode,env", [("tiny-llama", 1, None), ("tiny-qwen", 0, None), ("tiny-llama", 1, {"RT_TP_PUSH": "1"})])
+def test_tp2_generation_and_logits_match_oracle(name, mode, env):
     a = ARCHS[name]
     rng = np.random.default_rng(11)
     common = rng.integers(0, a.vocab, 48).tolist()
@@ -37,7 +40,7 @@ def test_tp2_generation_and_logits_match_oracle(name, mode):
     nccl_id = E.nccl_unique_id()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_rank_main, args=(r, 2, nccl_id, name, 4, prompts, 20, mode, q)) for r in range(2)]
+    procs = [ctx.Process(target=_rank_main, args=(r, 2, nccl_id, name, 4, prompts, 20, mode, q, env)) for r in range(2)]
     for p in procs:
         p.start()
     res = {}

@@ -680,6 +680,19 @@ void engine_init(rt_engine* e) {
             RT_CUDA(cudaStreamSynchronize(e->st));
             for (int j = 0; j < 2; ++j) tp_ipc_exchange(e->tp, e->tpf_delta[j], e->tpf_peer_delta[j], e->st);
             tp_ipc_exchange(e->tp, e->tpf_flags, e->tpf_peer_flags, e->st);
+            // push variant (partials stored into the peers by the projection epilogue): measured SLOWER than the pull kernel
+            // (config 4: TP=2 875 vs 886 tok/s, TP=4 1,154 vs 1,217: every producer CTA pays a system-scope fence), kept opt-in
+            e->tpp_on = env_int("RT_TP_PUSH", 0) != 0;
+            if (e->tpp_on) {
+                for (int j = 0; j < 2; ++j) e->tpp_recv[j] = zalloc_f((size_t)c.tp_size * MAX_SLOTS * e->H);
+                e->tpp_cnt = dalloc<unsigned long long>(e, 2);
+                e->tpp_expect = dalloc<unsigned long long>(e, (size_t)2 * MAX_SLOTS * TPF_CMAX);
+                RT_CUDA(cudaMemsetAsync(e->tpp_cnt, 0, 2 * sizeof(unsigned long long), e->st));
+                RT_CUDA(cudaMemsetAsync(e->tpp_expect, 0, (size_t)2 * MAX_SLOTS * TPF_CMAX * sizeof(unsigned long long), e->st));
+                RT_CUDA(cudaStreamSynchronize(e->st));
+                for (int j = 0; j < 2; ++j) tp_ipc_exchange(e->tp, e->tpp_recv[j], e->tpp_peer_recv[j], e->st);
+                tp_ipc_exchange(e->tp, e->tpp_cnt, e->tpp_peer_cnt, e->st);
+            }
             // nobody may raise a flag before every rank has cleared its own: one more collective as a barrier
             tp_allreduce_sum_f32(e->tp, e->loc_best, 64, e->st);
             RT_CUDA(cudaStreamSynchronize(e->st));
@@ -725,6 +738,10 @@ void engine_free(rt_engine* e) {
     if (e->tp && e->tpf_on) {
         for (int j = 0; j < 2; ++j) tp_ipc_close(e->tp, e->tpf_peer_delta[j]);
         tp_ipc_close(e->tp, e->tpf_peer_flags);
+        if (e->tpp_on) {
+            for (int j = 0; j < 2; ++j) tp_ipc_close(e->tp, e->tpp_peer_recv[j]);
+            tp_ipc_close(e->tp, e->tpp_peer_cnt);
+        }
     }
     tp_destroy(e->tp);
     e->tp = nullptr;
@@ -871,7 +888,20 @@ void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* p
 // Fused path: ONE kernel pulls every rank's partial over NVLink peer memory (tp_fused.cuh); otherwise NCCL + rmsnorm.
 static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, const bf16* norm_w) {
     const int H = e->H;
-    if (e->tpf_on) {
+    if (e->tpp_on) {
+        const int tp = e->cfg.tp_size;
+        for (int p = 0; p < tp; ++p) {
+            g.push_dst[p] = reinterpret_cast<float*>(e->tpp_peer_recv[site][p]);
+            g.push_cnt[p] = reinterpret_cast<unsigned long long*>(e->tpp_peer_cnt[p]) + site;
+        }
+        g.push_tp = tp; g.push_rank = e->cfg.tp_rank;
+        const int grid = gemv_dispatch<EPI_PUSH>(e, g);
+        TpPushArgs a{};
+        a.recv = e->tpp_recv[site]; a.cnt = e->tpp_cnt + site; a.expect = e->tpp_expect + (size_t)site * MAX_SLOTS * TPF_CMAX;
+        a.arrivals = (unsigned long long)tp * grid; a.tp = tp; a.H = H; a.T = T;
+        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.ss_part = e->ss_part;
+        launch_pdl(e, tp_push_reduce_norm_kernel, dim3(cdiv(H / 4, TPF_THREADS), MAX_SLOTS), dim3(TPF_THREADS), 0, a);
+    } else if (e->tpf_on) {
         g.out = e->tpf_delta[site]; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
         TpFusedArgs a{};

@@ -121,6 +121,14 @@ struct rt_engine {
     int *tpf_flags = nullptr, *tpf_epoch = nullptr;
     void* tpf_peer_delta[2][8] = {};
     void* tpf_peer_flags[8] = {};
+    // push variant of the exchange (tp_fused.cuh, gemv.cuh EPI_PUSH): per call site a receive buffer [tp][32][H] and an
+    // arrival counter on every rank, both mapped into every process
+    bool tpp_on = false;
+    float* tpp_recv[2] = {nullptr, nullptr};
+    unsigned long long* tpp_cnt = nullptr;             // [2]
+    unsigned long long* tpp_expect = nullptr;          // [2][32][TPF_CMAX], local only
+    void* tpp_peer_recv[2][8] = {};
+    void* tpp_peer_cnt[8] = {};
 
     // cached decode graph
     cudaGraphExec_t graph_exec = nullptr;

@@ -25,7 +25,7 @@
 #pragma once
 #include "common.cuh"
 
-enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4 };
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4, EPI_PUSH = 5 };
 
 constexpr int KV_PAGE = 16;
 
@@ -59,6 +59,12 @@ struct GemvArgs {
     float* cta_max;
     int* cta_idx;
     int row_offset;
+    // EPI_PUSH (tensor parallel, row-parallel projections): the fp32 partial sums go straight into EVERY rank's receive
+    // buffer [tp][32 slots][N] (slot `push_rank` of it) with P2P stores over NVLink, and every CTA then adds 1 to every
+    // rank's arrival counter (tp_fused.cuh: the consumer waits for tp x gridDim.x arrivals and reads LOCAL memory)
+    float* push_dst[8];
+    unsigned long long* push_cnt[8];
+    int push_tp, push_rank;
     int late_launch;          // QKV only: griddepcontrol.launch_dependents after the wait instead of at the start
     L2Prefetch pf;            // a later kernel's weights: each CTA asks for its slice once its own stream is issued
     float inv_temp;
@@ -315,6 +321,18 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 a.out[(size_t)s * a.ldo + n] = v;
             }
         }
+    } else if (EPI == EPI_PUSH) {
+        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
+            const int r = e % (MT * 16), s = e / (MT * 16);
+            const int n = row0 + r;
+            if (s < a.T && n < a.N) {
+                const float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                const size_t off = ((size_t)a.push_rank * 32 + s) * a.N + n;
+#pragma unroll
+                for (int p = 0; p < 8; ++p)
+                    if (p < a.push_tp) a.push_dst[p][off] = v;
+            }
+        }
     } else if (EPI == EPI_RESID) {
         for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
             const int r = e % (MT * 16), s = e / (MT * 16);
@@ -430,6 +448,13 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     __syncthreads();                                 // red / res are reused by the next group
     }
 
+    if (EPI == EPI_PUSH) {
+        // all of this CTA's partials are on their way: make them visible system-wide, then tell every rank
+        __threadfence_system();
+        __syncthreads();
+        if ((int)threadIdx.x < a.push_tp)
+            asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(a.push_cnt[threadIdx.x]), "l"(1ull) : "memory");
+    }
     if (EPI == EPI_LOGITS) {
         if (threadIdx.x < NT * 8) {
             a.cta_max[blockIdx.x * 32 + threadIdx.x] = cand_best;
