@@ -35,6 +35,7 @@ struct StepOpts {
     float inv_temp = 0.f;
     unsigned long long seed = 0;
     int attn3_cs = 0;          // > 0: cluster-merged decode attention (attn_decode3.cuh) with this cluster size
+    bool qkv_late = false;     // QKV projections release their dependent after their own wait (multi-step graphs)
     bool in_graph = false;     // the step is being captured into the decode graph (consecutive steps fully serialised)
     int top_k = 0;             // sampler.cuh; only with inv_temp > 0
     float top_p = 0.f;
@@ -131,9 +132,10 @@ struct rt_engine {
     void* tpp_peer_cnt[8] = {};
 
     // cached decode graph
-    cudaGraphExec_t graph_exec = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;       // one decode step
+    cudaGraphExec_t graph_exec_multi = nullptr; // graph_steps consecutive decode steps (no launch gap between them)
     StepOpts graph_opts{};
-    int graph_nodes = 0;
+    int graph_nodes = 0, graph_steps = 1;
 
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 
