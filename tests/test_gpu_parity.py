@@ -338,3 +338,23 @@ def test_config2_full_size_properties():
     assert first.tokens == solo[0].tokens                                           # the cache flag alone changes nothing
     assert again.tokens == first.tokens                                             # KV from the cache == KV recomputed
     assert sum(x == y for x, y in zip(other.tokens, solo[1].tokens)) >= w["new"] - 1 or other.tokens[:8] == solo[1].tokens[:8]
+
+
+def test_opt_in_decode_variants_reproduce_the_default_tokens(monkeypatch):
+    """Switchable variants of the decode step that are kept for measurement (profiles/r1_summary.md) must not change
+    results: several steps per CUDA-graph launch (with the late QKV release) replay the same kernels in the same order."""
+    a = ARCHS["tiny-llama-hd128"]
+    rng = np.random.default_rng(5)
+    common = rng.integers(0, a.vocab, 70).tolist()
+    prompts = [common + rng.integers(0, a.vocab, 7 + i).tolist() for i in range(3)]
+
+    def run():
+        with E.Engine("tiny-llama-hd128", seed=2, max_batch=3, max_ctx=256) as eng:
+            return [g.tokens for g in eng.generate_ids(prompts, max_new_tokens=40)]
+    base = run()
+    monkeypatch.setenv("RT_GRAPH_STEPS", "8")
+    assert run() == base                                       # same kernels, same order: bit-identical
+    monkeypatch.delenv("RT_GRAPH_STEPS")
+    oracle = OracleModel(a, 2, max_pos=256)
+    for p, t in zip(prompts, base):
+        _greedy_compare(t, oracle, p, 40, err_bound=REL_TOL * 2.5)
