@@ -362,6 +362,14 @@ def run_b200(args, w):
                 discuss = discuss_leg(w, model, local)
             except Exception as ex:  # noqa: BLE001
                 discuss = {"failed": repr(ex)}
+        # DRAM traffic of one step as ncu saw it (committed capture of the same workload), next to the algorithmic bytes
+        traffic = None
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1c_traffic.json"))).get(args.workload)
+            if tr and tp == 1 and not args.layers:
+                traffic = tr["dram_read_bytes_per_step"]
+        except Exception:  # noqa: BLE001
+            pass
         h2d = sum(len(t.encode()) + 3 for t in texts) * 4 + 4 * 96 * ((sum(len(t.encode()) + 3 for t in texts) + 31) // 32)
         d2h = w["knights"] * nt * 4
         line = {
@@ -375,7 +383,7 @@ def run_b200(args, w):
                        "model": model,
                        "prefill_ms_per_round": pre_ms_m / args.steps, "decode_ms_per_token_step": step_ms},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "of": "decode step (one CUDA-graph launch)",
+                         "traffic": traffic, "peak_source": peak_src, "of": "decode step (one CUDA-graph launch)",
                          "algorithmic_bytes_per_launch": bytes_step,
                          "dominant_kernel": {"name": "gemv_tc_kernel (gate/up projection)", "ms": gu_ms, "achieved": gu_gbs,
                                              "frac": gu_gbs / peak}},
