@@ -91,7 +91,7 @@ struct rt_engine {
     float* ss_part = nullptr;      // [H/16][32] per-tile partial sums of x^2 (split RMSNorm, gemv.cuh)
     float* inv_rms = nullptr;      // [32] r per slot when a whole row was available (tensor parallel, prefill rows)
     float* pf_inv_rms = nullptr;   // [pf_cap]
-    int* done_counter = nullptr;   // arrival counter of the residual projections' fused RMSNorm tail
+    int* done_counter = nullptr;   // arrival counter of the sampler tails (lm_head, top-k/top-p)
     bool use_pdl = true;
     bool use_stream = false;       // persistent TMA-fed stream-K projection kernel (gemv_stream.cuh)
     float* gs_scratch = nullptr;   // [SMs][16][32] stream-K partial tiles
