@@ -727,6 +727,14 @@ void engine_init(rt_engine* e) {
             pf_make_map_w(&e->map_w[4 * l + 2], e->layers[l].wgu, 2 * e->F_l, e->H, PF_BN);
             pf_make_map_w(&e->map_w[4 * l + 3], e->layers[l].wdown, e->H, e->F_l, PF_BN);
         }
+        // tcgen05 prefill attention (attn_prefill_tc5.cuh): head_dim 128, a q-head group that fits 128 rows
+        e->pfa_tc5 = env_int("RT_PFA_TC5", 0) != 0 && e->hd == 128 && e->G <= 16;
+        if (e->pfa_tc5) {
+            pf_make_map_q3(&e->map_q3, e->pf_q, e->pf_cap, e->nq_l, e->G, 128 / e->G);
+            const long long rows = (long long)e->L * e->n_pages * e->nkv_l * KV_PAGE;
+            pf_make_map_kv(&e->map_kpool, e->kpool, rows);
+            pf_make_map_kv(&e->map_vpool, e->vpool, rows);
+        }
     }
     RT_CUDA(cudaStreamSynchronize(e->st));
 }
@@ -1159,7 +1167,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
                            const std::vector<int>& want_first, const StepOpts& base, double t0, uint64_t deadline_ms,
                            float* logits_out = nullptr) {
     const int n = (int)tok.size(), H = e->H, hd = e->hd;
-    const int BT = std::max(1, 64 / e->G);
+    const int BT = e->pfa_tc5 ? 128 / e->G : std::max(1, 64 / e->G);
     const bool pdl = e->use_pdl;
     for (int c0 = 0; c0 < n; c0 += e->pf_cap) {
         const int S = std::min(e->pf_cap, n - c0);
@@ -1207,7 +1215,11 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             a.Q = e->pf_q; a.Kp = kp; a.Vp = vp; a.page_table = e->d_page_table; a.pt_stride = e->max_pages_per_seq;
             a.tok_pos = e->pf_pos; a.work = e->pf_work; a.n_q = e->nq_l; a.n_kv = e->nkv_l;
             a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd)); a.out = e->pf_attn;
-            pf_attention(e->st, pdl, hd, n_items, a);
+            if (e->pfa_tc5)
+                pf_attention_tc5(e->st, pdl, n_items, e->map_q3, e->map_kpool, e->map_vpool, e->d_page_table, e->max_pages_per_seq, e->pf_pos,
+                                 e->pf_work, e->nq_l, e->nkv_l, e->G, BT, e->n_pages, l, a.scale_log2, e->pf_attn);
+            else
+                pf_attention(e->st, pdl, hd, n_items, a);
             e->launches++;
 
             Gemm5Args go{};

@@ -109,6 +109,8 @@ struct rt_engine {
     int4* pf_work = nullptr;
     int* pf_host = nullptr;        // pinned staging: tok, seq, pos (pf_cap each) + work items
     PfTensorMap map_xn{}, map_attn{}, map_act{};
+    PfTensorMap map_q3{}, map_kpool{}, map_vpool{};   // tcgen05 prefill attention (head_dim 128, opt-in)
+    bool pfa_tc5 = false;
     std::vector<PfTensorMap> map_w;   // per layer: qkv, o, gate/up, down
 
     // tensor parallel
