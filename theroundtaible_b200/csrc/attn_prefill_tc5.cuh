@@ -11,9 +11,10 @@
 //   warp 1   MMA issuer: S = Q K^T (M=128, N=128, K=128: 8 tcgen05.mma, both operands K-major) into TMEM columns 0..127;
 //            after the softmax warps have written P: O_tile = P V (M=128, N=128, K=128 keys: A = P K-major from shared
 //            memory, B = V MN-major -- V lies [key][dim], contiguous along N) into TMEM columns 128..255.
-//   warps 2-5  one query row per thread (TMEM lane = row): read S (two passes: max, then exp2), causal mask, online
-//            softmax, P as bf16 into shared memory in the 128-byte-swizzled K-major layout, then O = O * alpha + O_tile
-//            with O kept in registers (no read-modify-write of TMEM), final normalisation and 256-byte row stores.
+//   warps 2-9  softmax: TMEM lane = query row, the two warps of a lane quadrant take half a row each (64 keys, 64 dims):
+//            read S once, causal mask, online softmax with a LAZY maximum (O in TMEM is rescaled only when the maximum
+//            grew by more than 2^8), P as bf16 hi + lo into shared memory in the 128-byte-swizzled K-major layout;
+//            at the end O / l as 128-byte row stores.
 // mbarriers: q_full, kv_full[2], kv_empty[2], s_full, s_free, p_full, p_free, o_full, o_free.
 #pragma once
 #include "gemm_tc5.cuh"
@@ -24,7 +25,8 @@ constexpr int P5_Q_BYTES = 2 * P5_HALF_BYTES;        // 32 KB
 constexpr int P5_KV_STAGE = 4 * P5_HALF_BYTES;       // K halves + V halves = 64 KB
 constexpr int P5_P_BYTES = 2 * P5_HALF_BYTES;        // 32 KB
 constexpr int P5_STAGES = 2;
-constexpr size_t p5_smem_bytes() { return (size_t)P5_Q_BYTES + P5_STAGES * P5_KV_STAGE + 2 * P5_P_BYTES + 1024 + 256; }   // P hi + P lo
+constexpr int P5_THREADS = 320;                       // TMA warp, MMA warp, 8 softmax warps
+constexpr size_t p5_smem_bytes() { return (size_t)P5_Q_BYTES + P5_STAGES * P5_KV_STAGE + 2 * P5_P_BYTES + 1024 + 256 + 1024; }   // P hi + P lo
 
 struct Pf5Args {
     const int* page_table;
@@ -42,6 +44,22 @@ __device__ __forceinline__ void p5_tma_3d(uint32_t dst, const CUtensorMap* map, 
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
                  "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
                  : "memory");
+}
+// polling wait (mbarrier.test_wait never suspends the thread): the hand-offs of this kernel sit on the critical path of
+// every key tile, and try_wait's suspend / wake-up granularity showed up as microseconds of bubbles per tile
+__device__ __forceinline__ void p5_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred P1;\n\t"
+            "mbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, P1;\n\t"
+            "}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
 }
 __device__ __forceinline__ void p5_mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -64,7 +82,7 @@ __device__ __forceinline__ void tc5_st32(uint32_t taddr, const float (&v)[32]) {
 }
 __device__ __forceinline__ void p5_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__global__ void __launch_bounds__(192, 1) attn_prefill_tc5_kernel(const __grid_constant__ CUtensorMap map_q,
+__global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const __grid_constant__ CUtensorMap map_q,
                                                                   const __grid_constant__ CUtensorMap map_k,
                                                                   const __grid_constant__ CUtensorMap map_v, const Pf5Args a) {
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -74,7 +92,7 @@ __global__ void __launch_bounds__(192, 1) attn_prefill_tc5_kernel(const __grid_c
     const uint32_t s_p = s_kv + P5_STAGES * P5_KV_STAGE;
     const uint32_t bars = s_p + 2 * P5_P_BYTES;
     const uint32_t b_q = bars, b_kvf = bars + 8, b_kve = bars + 24, b_sf = bars + 40, b_sfree = bars + 48, b_pf = bars + 56,
-                   b_pfree = bars + 64, b_of = bars + 72, b_ofree = bars + 80, tmem_slot = bars + 88;
+                   b_pfree = bars + 64, b_of = bars + 72, b_ofree = bars + 80, tmem_slot = bars + 88, xchg = bars + 128;
     unsigned char* gen = smem + (sbase - smem_u32(smem));           // generic pointer to the aligned base
     volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - sbase));
 
@@ -85,11 +103,11 @@ __global__ void __launch_bounds__(192, 1) attn_prefill_tc5_kernel(const __grid_c
     if (threadIdx.x == 0) {
         mbar_init(b_q, 1);
         for (int s = 0; s < P5_STAGES; ++s) { mbar_init(b_kvf + 8 * s, 1); mbar_init(b_kve + 8 * s, 1); }
-        mbar_init(b_sf, 1); mbar_init(b_sfree, 4); mbar_init(b_pf, 4); mbar_init(b_pfree, 1); mbar_init(b_of, 1);
+        mbar_init(b_sf, 1); mbar_init(b_sfree, 8); mbar_init(b_pf, 8); mbar_init(b_pfree, 1); mbar_init(b_of, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // stale shared memory must never reach the PV product as NaN: pages a tile does not load stay whatever they were
-    for (int i = threadIdx.x; i < (P5_Q_BYTES + P5_STAGES * P5_KV_STAGE) / 16; i += 192)
+    for (int i = threadIdx.x; i < (P5_Q_BYTES + P5_STAGES * P5_KV_STAGE) / 16; i += P5_THREADS)
         reinterpret_cast<uint4*>(gen)[i] = make_uint4(0u, 0u, 0u, 0u);
     p5_fence_async_smem();
     if (warp == 1) {
@@ -117,7 +135,7 @@ __global__ void __launch_bounds__(192, 1) attn_prefill_tc5_kernel(const __grid_c
             for (int c = 0; c < 2; ++c) p5_tma_3d(s_q + c * P5_HALF_BYTES, &map_q, b_q, c * 64, h * a.G, tok0);
             for (int j = 0; j < n_tiles; ++j) {
                 const int s = j & 1;
-                mbar_wait(b_kve + 8 * s, ((j >> 1) & 1) ^ 1);
+                p5_wait(b_kve + 8 * s, ((j >> 1) & 1) ^ 1);
                 const int npg = min(P5_KEYS / KV_PAGE, n_pages - j * (P5_KEYS / KV_PAGE));
                 mbar_expect_tx(b_kvf + 8 * s, (uint32_t)npg * 8192u);
                 const uint32_t st = s_kv + s * P5_KV_STAGE;
@@ -136,15 +154,15 @@ __global__ void __launch_bounds__(192, 1) attn_prefill_tc5_kernel(const __grid_c
             // instruction descriptors: D = f32, A = B = bf16, M = 128, N = 128; bit 16 = B is MN-major (V is [key][dim])
             const uint32_t idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             const uint32_t idesc_pv = idesc_qk | (1u << 16);
-            mbar_wait(b_q, 0);
+            p5_wait(b_q, 0);
             // software pipeline: S(j) = Q K_j^T is issued BEFORE O += P(j-1) V_(j-1), so the tensor pipe works on the next
             // scores while the softmax warps turn the previous ones into P
             for (int j = 0; j <= n_tiles; ++j) {
                 if (j < n_tiles) {
                     const int s = j & 1;
                     const uint32_t st = s_kv + s * P5_KV_STAGE;
-                    mbar_wait(b_kvf + 8 * s, (j >> 1) & 1);
-                    mbar_wait(b_sfree, (j & 1) ^ 1);
+                    p5_wait(b_kvf + 8 * s, (j >> 1) & 1);
+                    p5_wait(b_sfree, (j & 1) ^ 1);
                     tc5_fence_after();
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {         // 2 halves of the head dimension x 4 k16 steps
@@ -157,7 +175,7 @@ __global__ void __launch_bounds__(192, 1) attn_prefill_tc5_kernel(const __grid_c
                 if (j > 0) {
                     const int i = j - 1, s = i & 1;
                     const uint32_t st = s_kv + s * P5_KV_STAGE;
-                    mbar_wait(b_pf, i & 1);
+                    p5_wait(b_pf, i & 1);
                     tc5_fence_after();
 #pragma unroll
                     for (int k = 0; k < 16; ++k) {        // P hi then P lo; 128 keys = 8 k16 steps each
@@ -174,82 +192,113 @@ __global__ void __launch_bounds__(192, 1) attn_prefill_tc5_kernel(const __grid_c
             }
         }
     } else {
-        const int quad = warp & 3;
+        // 8 softmax warps: TMEM lane quadrant = warp % 4 (hardware rule), and the two warps of a quadrant split a row's
+        // 128 keys (and the 128 output dims) in halves; they agree on the row maximum through shared memory once per tile
+        const int quad = warp & 3, half = (warp - 2) >> 2;
         const int r = quad * 32 + lane;                    // query row = TMEM lane
         const int t = r / a.G, g = r % a.G;
         const bool row_ok = t < ntok;
         const int limit = row_ok ? pos0 + t + 1 : 1;       // keys [0, limit) are visible
+        int warp_min_limit = limit;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) warp_min_limit = min(warp_min_limit, __shfl_xor_sync(0xffffffffu, warp_min_limit, o));
         const uint32_t trow = tmem + ((uint32_t)(quad * 32) << 16);
         unsigned char* p_row = gen + (s_p - sbase) + r * 128;
+        float* xch = reinterpret_cast<float*>(gen + (xchg - sbase));          // [2][128] exchange of half-row values
         // m_used: the maximum the stored O and l are expressed in.  It follows the running maximum lazily: O is rescaled
         // (TMEM load, multiply, store) only when the maximum has grown by more than 2^8 since, which after the first tiles
         // is rare; until then P simply carries a factor <= 256, exact in fp32 and harmless in bf16.
         float m_used = -INFINITY, l_run = 0.f;
         for (int j = 0; j < n_tiles; ++j) {
-            const int kb = j * P5_KEYS;
-            mbar_wait(b_sf, j & 1);
+            const int kb = j * P5_KEYS + half * 64;
+            p5_wait(b_sf, j & 1);
             tc5_fence_after();
-            float sv[128];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) tc5_ld32(trow + c * 32, *reinterpret_cast<float(*)[32]>(&sv[c * 32]));
-            tc5_fence_before();
-            __syncwarp();
-            if (lane == 0) p5_mbar_arrive(b_sfree);          // S is in registers: the next QK^T may overwrite it
+            // Two passes over this warp's 64 score columns in chunks of 32 (one tcgen05.ld each), with the chunk loops NOT
+            // unrolled: fully unrolled the tile body was ~25 KB of code and the single warp per scheduler stalled on
+            // instruction fetch (ncu: 31 % of its cycles).
             float mx = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                float v[32];
+                tc5_ld32(trow + half * 64 + c * 32, v);
 #pragma unroll
-            for (int i = 0; i < 128; ++i) {
-                sv[i] = (kb + i < limit) ? sv[i] * a.scale_log2 : -INFINITY;
-                mx = fmaxf(mx, sv[i]);
+                for (int i = 0; i < 32; ++i)
+                    if (kb + c * 32 + i < limit) mx = fmaxf(mx, v[i] * a.scale_log2);
             }
+            xch[half * 128 + r] = mx;
+            asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+            mx = fmaxf(mx, xch[(half ^ 1) * 128 + r]);
+            asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");     // both have read before the next tile writes
             const bool grow = mx > m_used + 8.0f;            // also true on the first tile (m_used = -inf)
-            if (__any_sync(0xffffffffu, grow)) {
+            if (__any_sync(0xffffffffu, grow)) {             // same decision in both warps of the quadrant: same rows, same mx
                 const float m_new = grow ? mx : m_used;
                 const float f = (j > 0) ? exp2f(m_used - m_new) : 1.0f;   // 1 for rows that keep their maximum
                 if (j > 0) {
-                    mbar_wait(b_of, (j - 1) & 1);            // every product issued so far has landed in O
+                    p5_wait(b_of, (j - 1) & 1);              // every product issued so far has landed in O
                     tc5_fence_after();
 #pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
+                    for (int c = 0; c < 2; ++c) {
                         float v[32];
-                        tc5_ld32(trow + 128 + c * 32, v);
+                        tc5_ld32(trow + 128 + half * 64 + c * 32, v);
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] *= f;
-                        tc5_st32(trow + 128 + c * 32, v);
+                        tc5_st32(trow + 128 + half * 64 + c * 32, v);
                     }
                     tc5_fence_before();
                     l_run *= f;
                 }
                 m_used = m_new;
             }
-            mbar_wait(b_pfree, (j & 1) ^ 1);                 // the previous tile's PV product has read P
+            p5_wait(b_pfree, (j & 1) ^ 1);                   // the previous tile's PV product has read P
             float lsum = 0.f;
-#pragma unroll
-            for (int ch = 0; ch < 16; ++ch) {                // 8 keys = one 16-byte chunk of the row
-                uint32_t wh[4], wl[4];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float p0 = exp2f(sv[ch * 8 + 2 * e] - m_used), p1 = exp2f(sv[ch * 8 + 2 * e + 1] - m_used);
-                    wh[e] = pack_bf16(p0, p1);
-                    wl[e] = pack_bf16(p0 - bf16lo(wh[e]), p1 - bf16hi(wh[e]));
-                    lsum += p0 + p1;
+            const float neg_m = -m_used;
+            const bool diag = kb + 64 > warp_min_limit;      // some key of this warp's 64 is hidden from some row (warp-uniform)
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                float v[32];
+                tc5_ld32(trow + half * 64 + c * 32, v);
+                if (c == 1) {                                // S is consumed: the next QK^T may overwrite it
+                    tc5_fence_before();
+                    __syncwarp();
+                    if (lane == 0) p5_mbar_arrive(b_sfree);
                 }
-                const int off = (ch >> 3) * P5_HALF_BYTES + (((ch & 7) ^ (r & 7)) << 4);
-                *reinterpret_cast<uint4*>(p_row + off) = make_uint4(wh[0], wh[1], wh[2], wh[3]);
-                *reinterpret_cast<uint4*>(p_row + P5_P_BYTES + off) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
+                if (diag) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) v[i] = (kb + c * 32 + i < limit) ? v[i] : -INFINITY;
+                }
+#pragma unroll
+                for (int ch = 0; ch < 4; ++ch) {             // 8 keys = one 16-byte chunk of the row
+                    uint32_t wh[4], wl[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int i0 = ch * 8 + 2 * e;
+                        const float p0 = exp2f(fmaf(v[i0], a.scale_log2, neg_m)), p1 = exp2f(fmaf(v[i0 + 1], a.scale_log2, neg_m));
+                        wh[e] = pack_bf16(p0, p1);
+                        wl[e] = pack_bf16(p0 - bf16lo(wh[e]), p1 - bf16hi(wh[e]));
+                        lsum += p0 + p1;
+                    }
+                    const int off = half * P5_HALF_BYTES + (((c * 4 + ch) ^ (r & 7)) << 4);
+                    *reinterpret_cast<uint4*>(p_row + off) = make_uint4(wh[0], wh[1], wh[2], wh[3]);
+                    *reinterpret_cast<uint4*>(p_row + P5_P_BYTES + off) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
+                }
             }
             l_run += lsum;
             p5_fence_async_smem();
             __syncwarp();
             if (lane == 0) p5_mbar_arrive(b_pf);
         }
-        mbar_wait(b_of, (n_tiles - 1) & 1);
+        // row sum = the two halves' partial sums
+        xch[half * 128 + r] = l_run;
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+        l_run += xch[(half ^ 1) * 128 + r];
+        p5_wait(b_of, (n_tiles - 1) & 1);
         tc5_fence_after();
         const float inv = 1.0f / l_run;
-        bf16* dst = a.out + (size_t)(tok0 + t) * ((size_t)a.n_q * 128) + (size_t)(h * a.G + g) * 128;
+        bf16* dst = a.out + (size_t)(tok0 + t) * ((size_t)a.n_q * 128) + (size_t)(h * a.G + g) * 128 + half * 64;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
             float v[32];
-            tc5_ld32(trow + 128 + c * 32, v);
+            tc5_ld32(trow + 128 + half * 64 + c * 32, v);
             if (row_ok) {
 #pragma unroll
                 for (int i = 0; i < 32; i += 8) {

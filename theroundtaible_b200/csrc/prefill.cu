@@ -152,7 +152,7 @@ void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap&
     RT_CUDA(cudaFuncSetAttribute(attn_prefill_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(n_items);
-    cfg.blockDim = dim3(192);
+    cfg.blockDim = dim3(P5_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute at[1];
