@@ -362,13 +362,14 @@ def test_opt_in_decode_variants_reproduce_the_default_tokens(monkeypatch):
 
 @pytest.mark.parametrize("name", ["tiny-llama-hd128", "tiny-qwen-hd128"])
 def test_tcgen05_prefill_attention_matches_oracle_and_the_mma_sync_kernel(name, monkeypatch):
-    """RT_PFA_TC5=1 selects the tcgen05 prefill attention (attn_prefill_tc5.cuh: S and O in TMEM, K/V pages by TMA from the
+    """Head_dim 128 takes the tcgen05 prefill attention by default (RT_PFA_TC5=0 selects the mma.sync kernel) (attn_prefill_tc5.cuh: S and O in TMEM, K/V pages by TMA from the
     paged pool, G = 4 and G = 5 head groups -> 128 and 125 query rows per CTA).  Same bar as the mma.sync kernel, in one
     call and in a continued sequence (second call attends to pages the first one wrote)."""
     g = np.load(os.path.join(GOLD, f"hf_{name}.npz"))
     a, seed, ids = ARCHS[name], int(g["seed"]), g["ids"]
     ref = OracleModel(a, seed, max_pos=256).forward(ids, KVState(), round_kv=True, round_act=True).numpy()
     scale = np.abs(ref).max(-1)
+    monkeypatch.setenv("RT_PFA_TC5", "0")
     with E.Engine(name, seed=seed, max_batch=1, max_ctx=256) as eng:
         eng.seq_reset()
         base = eng.step_logits(ids, mode=1)

@@ -728,7 +728,7 @@ void engine_init(rt_engine* e) {
             pf_make_map_w(&e->map_w[4 * l + 3], e->layers[l].wdown, e->H, e->F_l, PF_BN);
         }
         // tcgen05 prefill attention (attn_prefill_tc5.cuh): head_dim 128, a q-head group that fits 128 rows
-        e->pfa_tc5 = env_int("RT_PFA_TC5", 0) != 0 && e->hd == 128 && e->G <= 16;
+        e->pfa_tc5 = env_int("RT_PFA_TC5", 1) != 0 && e->hd == 128 && e->G <= 16;   // RT_PFA_TC5=0: the mma.sync kernel
         if (e->pfa_tc5) {
             pf_make_map_q3(&e->map_q3, e->pf_q, e->pf_cap, e->nq_l, e->G, 128 / e->G);
             const long long rows = (long long)e->L * e->n_pages * e->nkv_l * KV_PAGE;
