@@ -1,8 +1,8 @@
-// Causal prefill attention on the 5th-generation tensor cores (tcgen05 / TMEM / TMA), head_dim 128, sm_100a only.
+// Causal prefill attention on the 5th-generation tensor cores (tcgen05 / TMEM / TMA), head_dim 128 or 64, sm_100a only.
 //
 // No reference counterpart (/root/reference/src/adapters/local-llm.ts:159 delegates generation to an external server);
-// SURVEY.md 8(a-K) row "prefill causal attention".  Default for head_dim 128; RT_PFA_TC5=0 selects the mma.sync kernel of
-// attn_prefill.cuh (which also serves head_dim 32 / 64).
+// SURVEY.md 8(a-K) row "prefill causal attention".  Default for head_dim 128 (RT_PFA_TC5=0: the mma.sync kernel of
+// attn_prefill.cuh, which serves head_dim 32 / 64; RT_PFA_TC5=2 also takes head_dim 64 here -- correct, no faster).
 //
 // One CTA = up to 128 query rows of one kv head: BT = 128 / G consecutive tokens of a segment x the G q-heads of the group
 // (row = token * G + head-in-group), walking the keys 0 .. position of its last token in tiles of 128 keys (8 KV pages).
@@ -26,12 +26,11 @@
 
 constexpr int P5_KEYS = 128;                         // keys per tile
 constexpr int P5_HALF_BYTES = 128 * 128;             // 128 rows x 64 bf16 (one 128-byte swizzle row each)
-constexpr int P5_Q_BYTES = 2 * P5_HALF_BYTES;        // 32 KB
-constexpr int P5_KV_STAGE = 4 * P5_HALF_BYTES;       // K halves + V halves = 64 KB
-constexpr int P5_P_BYTES = 2 * P5_HALF_BYTES;        // 32 KB
+constexpr int P5_P_BYTES = 2 * P5_HALF_BYTES;        // 32 KB (128 rows x 128 keys)
+// head_dim 128: Q 32 KB, a K/V stage 64 KB;  head_dim 64: Q 16 KB, a stage 32 KB
 constexpr int P5_STAGES = 2;
 constexpr int P5_THREADS = 320;                       // TMA warp, MMA warp, 8 softmax warps
-constexpr size_t p5_smem_bytes() { return (size_t)P5_Q_BYTES + P5_STAGES * P5_KV_STAGE + 2 * P5_P_BYTES + 1024 + 256 + 1024; }   // P hi + P lo
+constexpr size_t p5_smem_bytes(int hd) { return (size_t)(hd / 64) * P5_HALF_BYTES * (1 + 2 * P5_STAGES) + 2 * P5_P_BYTES + 1024 + 256 + 1024; }   // P hi + P lo
 
 struct Pf5Args {
     const int* page_table;
@@ -87,10 +86,13 @@ __device__ __forceinline__ void tc5_st32(uint32_t taddr, const float (&v)[32]) {
 }
 __device__ __forceinline__ void p5_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+template <int HD>
 __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const __grid_constant__ CUtensorMap map_q,
                                                                   const __grid_constant__ CUtensorMap map_k,
                                                                   const __grid_constant__ CUtensorMap map_v, const Pf5Args a) {
     extern __shared__ __align__(1024) unsigned char smem[];
+    constexpr int NH = HD / 64;                          // 64-dim halves of the head dimension (one 128-byte swizzle row each)
+    constexpr int P5_Q_BYTES = NH * P5_HALF_BYTES, P5_KV_STAGE = 2 * NH * P5_HALF_BYTES;
     const uint32_t sbase = (smem_u32(smem) + 1023u) & ~1023u;
     const uint32_t s_q = sbase;
     const uint32_t s_kv = s_q + P5_Q_BYTES;
@@ -135,21 +137,21 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const _
     if (warp == 0) {
         if (lane == 0) {
             const int* pt = a.page_table + (size_t)seq * a.pt_stride;
-            const uint32_t q_bytes = 2u * 64u * (uint32_t)a.G * (uint32_t)a.BT * 2u;
+            const uint32_t q_bytes = (uint32_t)NH * 64u * (uint32_t)a.G * (uint32_t)a.BT * 2u;
             mbar_expect_tx(b_q, q_bytes);
-            for (int c = 0; c < 2; ++c) p5_tma_3d(s_q + c * P5_HALF_BYTES, &map_q, b_q, c * 64, h * a.G, tok0);
+            for (int c = 0; c < NH; ++c) p5_tma_3d(s_q + c * P5_HALF_BYTES, &map_q, b_q, c * 64, h * a.G, tok0);
             for (int j = 0; j < n_tiles; ++j) {
                 const int s = j & 1;
                 p5_wait(b_kve + 8 * s, ((j >> 1) & 1) ^ 1);
                 const int npg = min(P5_KEYS / KV_PAGE, n_pages - j * (P5_KEYS / KV_PAGE));
-                mbar_expect_tx(b_kvf + 8 * s, (uint32_t)npg * 8192u);
+                mbar_expect_tx(b_kvf + 8 * s, (uint32_t)npg * (uint32_t)(NH * 4096));
                 const uint32_t st = s_kv + s * P5_KV_STAGE;
                 for (int p = 0; p < npg; ++p) {
                     const int page = pt[j * (P5_KEYS / KV_PAGE) + p];
                     const int row = ((a.layer * a.n_pages_pool + page) * a.n_kv + h) * KV_PAGE;
-                    for (int c = 0; c < 2; ++c) {
+                    for (int c = 0; c < NH; ++c) {
                         tma_load_2d(st + c * P5_HALF_BYTES + p * (KV_PAGE * 128), &map_k, b_kvf + 8 * s, c * 64, row);
-                        tma_load_2d(st + (2 + c) * P5_HALF_BYTES + p * (KV_PAGE * 128), &map_v, b_kvf + 8 * s, c * 64, row);
+                        tma_load_2d(st + (NH + c) * P5_HALF_BYTES + p * (KV_PAGE * 128), &map_v, b_kvf + 8 * s, c * 64, row);
                     }
                 }
             }
@@ -158,7 +160,7 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const _
         if (lane == 0) {
             // instruction descriptors: D = f32, A = B = bf16, M = 128, N = 128; bit 16 = B is MN-major (V is [key][dim])
             const uint32_t idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-            const uint32_t idesc_pv = idesc_qk | (1u << 16);
+            const uint32_t idesc_pv = (idesc_qk & ~(0x3Fu << 17)) | ((uint32_t)(HD >> 3) << 17) | (1u << 16);   // N = head_dim
             p5_wait(b_q, 0);
             // software pipeline: S(j) = Q K_j^T is issued BEFORE O += P(j-1) V_(j-1), so the tensor pipe works on the next
             // scores while the softmax warps turn the previous ones into P
@@ -170,7 +172,7 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const _
                     p5_wait(b_sfree, (j & 1) ^ 1);
                     tc5_fence_after();
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {         // 2 halves of the head dimension x 4 k16 steps
+                    for (int k = 0; k < 4 * NH; ++k) {    // halves of the head dimension x 4 k16 steps
                         const uint64_t adesc = tc5_smem_desc(s_q + (k >> 2) * P5_HALF_BYTES + (k & 3) * 32, 16, 1024, 2);
                         const uint64_t bdesc = tc5_smem_desc(st + (k >> 2) * P5_HALF_BYTES + (k & 3) * 32, 16, 1024, 2);
                         tc5_mma_bf16(tmem, adesc, bdesc, idesc_qk, k > 0 ? 1u : 0u);
@@ -187,7 +189,7 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const _
                         const int kk = k & 7;
                         const uint64_t adesc = tc5_smem_desc(s_p + (k >> 3) * P5_P_BYTES + (kk >> 2) * P5_HALF_BYTES + (kk & 3) * 32, 16, 1024, 2);
                         // V, MN-major: 64-dim blocks P5_HALF_BYTES apart (LBO), 8-key groups 1024 B apart (SBO), 16 keys per step
-                        const uint64_t bdesc = tc5_smem_desc(st + 2 * P5_HALF_BYTES + kk * (16 * 128), P5_HALF_BYTES, 1024, 2);
+                        const uint64_t bdesc = tc5_smem_desc(st + NH * P5_HALF_BYTES + kk * (16 * 128), P5_HALF_BYTES, 1024, 2);
                         tc5_mma_bf16(tmem + 128, adesc, bdesc, idesc_pv, (i > 0 || k > 0) ? 1u : 0u);
                     }
                     tc5_commit(b_of);                     // O includes tile i
@@ -242,12 +244,12 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const _
                     p5_wait(b_of, (j - 1) & 1);              // every product issued so far has landed in O
                     tc5_fence_after();
 #pragma unroll 1
-                    for (int c = 0; c < 2; ++c) {
+                    for (int c = 0; c < NH; ++c) {
                         float v[32];
-                        tc5_ld32(trow + 128 + half * 64 + c * 32, v);
+                        tc5_ld32(trow + 128 + half * (HD / 2) + c * 32, v);
 #pragma unroll
                         for (int i = 0; i < 32; ++i) v[i] *= f;
-                        tc5_st32(trow + 128 + half * 64 + c * 32, v);
+                        tc5_st32(trow + 128 + half * (HD / 2) + c * 32, v);
                     }
                     tc5_fence_before();
                     l_run *= f;
@@ -299,11 +301,11 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5_kernel(const _
         p5_wait(b_of, (n_tiles - 1) & 1);
         tc5_fence_after();
         const float inv = 1.0f / l_run;
-        bf16* dst = a.out + (size_t)(tok0 + t) * ((size_t)a.n_q * 128) + (size_t)(h * a.G + g) * 128 + half * 64;
+        bf16* dst = a.out + (size_t)(tok0 + t) * ((size_t)a.n_q * HD) + (size_t)(h * a.G + g) * HD + half * (HD / 2);
 #pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
+        for (int c = 0; c < NH; ++c) {
             float v[32];
-            tc5_ld32(trow + 128 + half * 64 + c * 32, v);
+            tc5_ld32(trow + 128 + half * (HD / 2) + c * 32, v);
             if (row_ok) {
 #pragma unroll
                 for (int i = 0; i < 32; i += 8) {

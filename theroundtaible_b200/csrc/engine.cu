@@ -728,12 +728,15 @@ void engine_init(rt_engine* e) {
             pf_make_map_w(&e->map_w[4 * l + 3], e->layers[l].wdown, e->H, e->F_l, PF_BN);
         }
         // tcgen05 prefill attention (attn_prefill_tc5.cuh): head_dim 128, a q-head group that fits 128 rows
-        e->pfa_tc5 = env_int("RT_PFA_TC5", 1) != 0 && e->hd == 128 && e->G <= 16;   // RT_PFA_TC5=0: the mma.sync kernel
+        // head_dim 64 also runs (RT_PFA_TC5=2) but gains nothing measurable: the kernel is softmax-paced and a 64-dim head
+        // only halves its MMA work (30k-token 1B prompt: 378 vs 391 ms)
+        const int tc5 = env_int("RT_PFA_TC5", 1);
+        e->pfa_tc5 = tc5 != 0 && (e->hd == 128 || (e->hd == 64 && tc5 == 2)) && e->G <= 16;   // RT_PFA_TC5=0: the mma.sync kernel
         if (e->pfa_tc5) {
-            pf_make_map_q3(&e->map_q3, e->pf_q, e->pf_cap, e->nq_l, e->G, 128 / e->G);
+            pf_make_map_q3(&e->map_q3, e->pf_q, e->pf_cap, e->nq_l, e->G, 128 / e->G, e->hd);
             const long long rows = (long long)e->L * e->n_pages * e->nkv_l * KV_PAGE;
-            pf_make_map_kv(&e->map_kpool, e->kpool, rows);
-            pf_make_map_kv(&e->map_vpool, e->vpool, rows);
+            pf_make_map_kv(&e->map_kpool, e->kpool, rows, e->hd);
+            pf_make_map_kv(&e->map_vpool, e->vpool, rows, e->hd);
         }
     }
     RT_CUDA(cudaStreamSynchronize(e->st));
@@ -1217,7 +1220,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd)); a.out = e->pf_attn;
             if (e->pfa_tc5)
                 pf_attention_tc5(e->st, pdl, n_items, e->map_q3, e->map_kpool, e->map_vpool, e->d_page_table, e->max_pages_per_seq, e->pf_pos,
-                                 e->pf_work, e->nq_l, e->nkv_l, e->G, BT, e->n_pages, l, a.scale_log2, e->pf_attn);
+                                 e->pf_work, e->nq_l, e->nkv_l, e->G, BT, e->n_pages, l, a.scale_log2, e->pf_attn, hd);
             else
                 pf_attention(e->st, pdl, hd, n_items, a);
             e->launches++;

@@ -118,9 +118,9 @@ void pf_attention(cudaStream_t st, bool pdl, int hd, int n_items, const PfAttnAr
 // ---- tcgen05 prefill attention (head_dim 128) ------------------------------------------------------------------
 // Q: bf16 [tokens][n_q][128] viewed as (128 dims, n_q heads, tokens); box = 64 dims x G heads x BT tokens, 128-byte swizzle:
 // lands as rows (token, head-in-group) of 128 bytes = the K-major operand of the QK^T product
-void pf_make_map_q3(PfTensorMap* out, const void* base, int tokens, int n_q, int G, int BT) {
-    const cuuint64_t dims[3] = {128, (cuuint64_t)n_q, (cuuint64_t)tokens};
-    const cuuint64_t strides[2] = {128 * 2, (cuuint64_t)n_q * 128 * 2};
+void pf_make_map_q3(PfTensorMap* out, const void* base, int tokens, int n_q, int G, int BT, int hd) {
+    const cuuint64_t dims[3] = {(cuuint64_t)hd, (cuuint64_t)n_q, (cuuint64_t)tokens};
+    const cuuint64_t strides[2] = {(cuuint64_t)hd * 2, (cuuint64_t)n_q * hd * 2};
     const cuuint32_t box[3] = {64, (cuuint32_t)G, (cuuint32_t)BT};
     const cuuint32_t es[3] = {1, 1, 1};
     const CUresult r = encode_fn()(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims,
@@ -130,9 +130,9 @@ void pf_make_map_q3(PfTensorMap* out, const void* base, int tokens, int n_q, int
 }
 // K or V pool of all layers: bf16 [rows][128], rows = ((layer * pages + page) * kv heads + head) * 16 + key; box = one page of
 // one head, half the head dimension
-void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows) {
-    const cuuint64_t dims[2] = {128, (cuuint64_t)rows};
-    const cuuint64_t strides[1] = {128 * 2};
+void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows, int hd) {
+    const cuuint64_t dims[2] = {(cuuint64_t)hd, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)hd * 2};
     const cuuint32_t box[2] = {64, KV_PAGE};
     const cuuint32_t es[2] = {1, 1};
     const CUresult r = encode_fn()(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
@@ -143,13 +143,14 @@ void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows) {
 
 void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
                       const int* page_table, int pt_stride, const int* tok_pos, const int4* work, int n_q, int n_kv, int G, int BT,
-                      int n_pages_pool, int layer, float scale_log2, bf16* out) {
+                      int n_pages_pool, int layer, float scale_log2, bf16* out, int hd) {
     if (n_items <= 0) return;
     Pf5Args a{};
     a.page_table = page_table; a.pt_stride = pt_stride; a.tok_pos = tok_pos; a.work = work; a.n_q = n_q; a.n_kv = n_kv; a.G = G; a.BT = BT;
     a.n_pages_pool = n_pages_pool; a.layer = layer; a.scale_log2 = scale_log2; a.out = out;
-    const size_t smem = p5_smem_bytes();
-    RT_CUDA(cudaFuncSetAttribute(attn_prefill_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = p5_smem_bytes(hd);
+    auto kern = hd == 128 ? attn_prefill_tc5_kernel<128> : attn_prefill_tc5_kernel<64>;
+    RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(n_items);
     cfg.blockDim = dim3(P5_THREADS);
@@ -160,6 +161,6 @@ void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap&
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
-    RT_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_tc5_kernel, reinterpret_cast<const CUtensorMap&>(mq), reinterpret_cast<const CUtensorMap&>(mk),
+    RT_CUDA(cudaLaunchKernelEx(&cfg, kern, reinterpret_cast<const CUtensorMap&>(mq), reinterpret_cast<const CUtensorMap&>(mk),
                                reinterpret_cast<const CUtensorMap&>(mv), a));
 }

@@ -52,11 +52,11 @@ void pf_attention(cudaStream_t st, bool pdl, int hd, int n_items, const PfAttnAr
 
 // tcgen05 variant (attn_prefill_tc5.cuh, head_dim 128): Q as a 3-D map (dims, heads, tokens), K/V pools as 2-D maps
 struct Pf5Args;
-void pf_make_map_q3(PfTensorMap* out, const void* base, int tokens, int n_q, int G, int BT);
-void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows);
+void pf_make_map_q3(PfTensorMap* out, const void* base, int tokens, int n_q, int G, int BT, int hd);
+void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows, int hd);
 void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
                       const int* page_table, int pt_stride, const int* tok_pos, const int4* work, int n_q, int n_kv, int G, int BT,
-                      int n_pages_pool, int layer, float scale_log2, bf16* out);
+                      int n_pages_pool, int layer, float scale_log2, bf16* out, int hd);
 void pf_make_map_a(PfTensorMap* out, const void* base, int rows, int K);
 void pf_make_map_w(PfTensorMap* out, const void* base, int N, int K, int BN);
 void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const PfTensorMap& mw, const Gemm5Args& a);
