@@ -5,7 +5,8 @@
 //
 //   C[S][N] = A[S][K] * W[N][K]^T      A: bf16 activations, row-major, S tokens;  W: bf16 weights, CM layout
 //
-// One CTA computes a 128 x BN tile (tokens x weight rows):
+// A persistent CTA (one per SM) walks 128 x BN tiles (tokens x weight rows), token blocks fastest, with two accumulators in TMEM
+// so that a tile's epilogue runs under the next tile's MMAs.  Per tile:
 //   warp 0   TMA producer: per 64-wide k-block one 2-D tensor-map load of the A tile (SWIZZLE_128B, K-major) and
 //            one 4-D tensor-map load of the W tile.  The CM layout of gemv.cuh stores 8-row x 16-byte core matrices
 //            contiguously, and the 4-D box (256 elems, 2 k-blocks, 2 halves, BN/16 tiles) lands them in shared memory
@@ -15,7 +16,8 @@
 //            tcgen05.commit releases the shared-memory stage / signals the epilogue.  Also owns TMEM alloc/dealloc.
 //   warps 2-5 epilogue: tcgen05.ld 32x32b.x32 (thread = token row, 32 consecutive weight rows), fused
 //            bias + RoPE + KV-page write | residual add | SwiGLU, 16-byte stores.
-// 4-stage mbarrier pipeline (full/empty), 48 KB per stage at BN = 256.
+// 4-stage mbarrier pipeline (full/empty), 48 KB per stage at BN = 256; it keeps running across tile boundaries.  Accumulator
+// hand-over: tmem_full[2] (tcgen05.commit) / tmem_free[2] (one arrival per epilogue warp).
 #pragma once
 #include <cuda.h>
 
@@ -103,12 +105,17 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
     const uint32_t sbase = (smem_u32(smem) + 1023u) & ~1023u;
     const uint32_t bar_full = sbase + G5_STAGES * STAGE;        // 8 bytes each
     const uint32_t bar_empty = bar_full + 8 * G5_STAGES;
-    const uint32_t bar_tmem = bar_empty + 8 * G5_STAGES;
-    const uint32_t tmem_slot = bar_tmem + 8;
+    const uint32_t bar_tmem = bar_empty + 8 * G5_STAGES;          // accumulator full [2]
+    const uint32_t bar_tfree = bar_tmem + 16;                     // accumulator drained by the epilogue [2]
+    const uint32_t tmem_slot = bar_tfree + 16;
     volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - smem_u32(smem)));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m_blk = blockIdx.x, n_blk = blockIdx.y;
+    // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ... in token-block-fastest order, with TWO accumulators in
+    // TMEM (2 x BN columns) so that the epilogue of a tile (TMEM loads, fused math, global stores) runs under the MMAs of the
+    // next one, and the TMA ring never drains between tiles.
+    const int m_blocks = (a.S + G5_BM - 1) / G5_BM, n_blocks = (a.N + BN - 1) / BN;
+    const int n_tiles = m_blocks * n_blocks;
     const int num_kb = a.K / G5_BK;
 
     if (threadIdx.x == 0) {
@@ -116,11 +123,11 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
         }
-        mbar_init(bar_tmem, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(bar_tmem + 8 * s, 1); mbar_init(bar_tfree + 8 * s, 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(BN));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(2 * BN));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     tc5_fence_before();
@@ -133,40 +140,55 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % G5_STAGES;
-                const uint32_t ph = (kb / G5_STAGES) & 1;
-                mbar_wait(bar_empty + 8 * s, ph ^ 1);
-                mbar_expect_tx(bar_full + 8 * s, STAGE);
-                tma_load_2d(sbase + s * STAGE, &map_a, bar_full + 8 * s, kb * G5_BK, m_blk * G5_BM);
-                tma_load_4d(sbase + s * STAGE + A_BYTES, &map_w, bar_full + 8 * s, 0, kb * 2, 0, n_blk * (BN / 16));
+            int it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % G5_STAGES;
+                    const uint32_t ph = (it / G5_STAGES) & 1;
+                    mbar_wait(bar_empty + 8 * s, ph ^ 1);
+                    mbar_expect_tx(bar_full + 8 * s, STAGE);
+                    tma_load_2d(sbase + s * STAGE, &map_a, bar_full + 8 * s, kb * G5_BK, m_blk * G5_BM);
+                    tma_load_4d(sbase + s * STAGE + A_BYTES, &map_w, bar_full + 8 * s, 0, kb * 2, 0, n_blk * (BN / 16));
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             // instruction descriptor: D=f32 [4,6)=1, A=bf16 [7,10)=1, B=bf16 [10,13)=1, K-major both, N>>3 [17,23), M>>4 [24,29)
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(G5_BM >> 4) << 24);
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % G5_STAGES;
-                const uint32_t ph = (kb / G5_STAGES) & 1;
-                mbar_wait(bar_full + 8 * s, ph);
+            int it = 0, lt = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+                const int acc = lt & 1;
+                mbar_wait(bar_tfree + 8 * acc, ((lt >> 1) & 1) ^ 1);          // the epilogue has drained this accumulator
                 tc5_fence_after();
-                const uint32_t sa = sbase + s * STAGE, sb = sa + A_BYTES;
+                const uint32_t d = tmem_d + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % G5_STAGES;
+                    const uint32_t ph = (it / G5_STAGES) & 1;
+                    mbar_wait(bar_full + 8 * s, ph);
+                    tc5_fence_after();
+                    const uint32_t sa = sbase + s * STAGE, sb = sa + A_BYTES;
 #pragma unroll
-                for (int j = 0; j < G5_BK / 16; ++j) {
-                    const uint64_t adesc = tc5_smem_desc(sa + j * 32, 16, 1024, 2);      // 128B swizzle, K-major
-                    const uint64_t bdesc = tc5_smem_desc(sb + j * 256, 128, 1024, 0);    // no swizzle, K-major (CM)
-                    tc5_mma_bf16(tmem_d, adesc, bdesc, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+                    for (int j = 0; j < G5_BK / 16; ++j) {
+                        const uint64_t adesc = tc5_smem_desc(sa + j * 32, 16, 1024, 2);      // 128B swizzle, K-major
+                        const uint64_t bdesc = tc5_smem_desc(sb + j * 256, 128, 1024, 0);    // no swizzle, K-major (CM)
+                        tc5_mma_bf16(d, adesc, bdesc, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+                    }
+                    tc5_commit(bar_empty + 8 * s);      // frees the stage once these MMAs have read it
                 }
-                tc5_commit(bar_empty + 8 * s);      // frees the stage once these MMAs have read it
+                tc5_commit(bar_tmem + 8 * acc);         // accumulator complete
             }
-            tc5_commit(bar_tmem);                   // accumulator complete
         }
     } else {
         // ---- epilogue: warps 2..5 own TMEM lane quadrants (warp % 4) ----
         const int quad = warp & 3;
+        int lt = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
+        const int m_blk = tile % m_blocks, n_blk = tile / m_blocks;
+        const int acc = lt & 1;
         const int m = m_blk * G5_BM + quad * 32 + lane;
-        mbar_wait(bar_tmem, 0);
+        mbar_wait(bar_tmem + 8 * acc, (lt >> 1) & 1);
         tc5_fence_after();
         const bool row_ok = m < a.S;
         int pos = 0, seq = 0;
@@ -177,7 +199,7 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
             float v[32];
-            tc5_ld32(tmem_d + ((uint32_t)(quad * 32) << 16) + c * 32, v);
+            tc5_ld32(tmem_d + ((uint32_t)(quad * 32) << 16) + acc * BN + c * 32, v);
             const int n0 = n_blk * BN + c * 32;
             if (!row_ok || n0 >= a.N) continue;
             if (a.row_scale) {
@@ -254,11 +276,14 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
             }
         }
         tc5_fence_before();
+        __syncwarp();
+        if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_tfree + 8 * acc) : "memory");
+        }   // tiles
     }
     __syncthreads();
     if (warp == 1) {
         tc5_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(BN));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "n"(2 * BN));
     }
 }
 

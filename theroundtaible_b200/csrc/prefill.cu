@@ -35,7 +35,10 @@ void launch_gemm5(cudaStream_t st, bool pdl, const CUtensorMap& ma, const CUtens
     // few weight-row blocks, so a weight tile comes from HBM once and from L2 for the other token blocks, and the
     // activations (<= 2,048 x K, L2-resident) are what every CTA shares.  Weight blocks fastest re-streamed an 8B
     // gate/up matrix (235 MB > L2) from HBM once per token block.
-    cfg.gridDim = dim3(cdiv(a.S, G5_BM), cdiv(a.N, BN));
+    // persistent: one CTA per SM walks the tiles (token blocks fastest, see above) with two accumulators in TMEM
+    static int sm_count = 0;
+    if (!sm_count) { int dev = 0; RT_CUDA(cudaGetDevice(&dev)); RT_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev)); }
+    cfg.gridDim = dim3(std::min(cdiv(a.S, G5_BM) * cdiv(a.N, BN), sm_count));
     cfg.blockDim = dim3(192);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
