@@ -77,6 +77,10 @@ typedef struct rt_config {
     int32_t max_ctx;             /* tokens per sequence (prompt + generated) */
     int64_t kv_pool_bytes;       /* 0 = size for max_batch * max_ctx */
     int32_t flags;               /* RT_FLAG_* */
+    int32_t n_eos;               /* end-of-sequence ids in eos_ids (0..3); 0 = the byte tokenizer's <eos> (id 2), which is
+                                    what the seeded weights are used with.  A checkpoint's ids come from its config.json /
+                                    generation_config.json (Llama-3: 128001, 128009; Qwen2.5: 151645, 151643) */
+    int32_t eos_ids[3];
     int32_t reserved;
 } rt_config;
 
@@ -88,7 +92,8 @@ typedef struct rt_sampling {
     float temperature;           /* 0 = greedy (argmax, lowest index wins ties) */
     int32_t top_k;               /* 0 = off; with temperature > 0: keep the k highest logits (ties at the k-th kept) */
     float top_p;                 /* 0 or 1 = off; with temperature > 0: keep the smallest set of highest-probability tokens
-                                    (after top_k) whose mass reaches top_p.  Single GPU only (csrc/sampler.cuh) */
+                                    (after top_k) whose mass reaches top_p (csrc/sampler.cuh; under tensor parallel the
+                                    vocab-parallel logits are all-gathered and every rank draws the same token) */
     uint64_t seed;
     int32_t ignore_eos;
     int32_t reserved;
@@ -146,7 +151,11 @@ RT_API int rt_model_info_get(const rt_engine* e, rt_model_info* out);
 
 /* SEQ path -- one prompt, what `roundtable discuss` really issues (one execute() per knight per
  * round, src/orchestrator.ts:442).  Replaces: POST /v1/chat/completions (local-llm.ts:150-199) /
- * POST /api/chat (local-llm.ts:95-144).  `deadline_ms` = timeoutMs of execute() (0 = none). */
+ * POST /api/chat (local-llm.ts:95-144).  `deadline_ms` = timeoutMs of execute() (0 = none); under tensor parallel
+ * every rank must pass the same value (the ranks agree on "stop" collectively, so none is left spinning).
+ * The two text entry points use the built-in byte-level tokenizer and therefore refuse (RT_ERR_INVALID) an engine
+ * created from a checkpoint (rt_config.weights_path): its vocabulary is not the byte tokenizer's; drive such an
+ * engine with rt_generate_ids and the checkpoint's own tokenizer. */
 RT_API int rt_generate(rt_engine* e, const char* prompt_utf8, size_t len, const rt_sampling* s,
                        uint64_t deadline_ms, rt_result* out);
 
@@ -183,7 +192,8 @@ RT_API int rt_nccl_unique_id(void* out128);
  * 6 down,7 in_norm,8 post_norm,9 q_bias,10 k_bias,11 v_bias}).  Proves the GPU generator equals the oracle's. */
 RT_API int rt_weights_export(rt_engine* e, int32_t tensor_id, uint16_t* out, int64_t n_elems);
 
-/* y[t][n] = sum_k W[n][k] * x[t][k]; W bf16 bits [N][K], x bf16 bits [T][K], y fp32 [T][N]; T <= 32. */
+/* y[t][n] = sum_k W[n][k] * x[t][k]; W bf16 bits [N][K], x FP16 bits [T][K] (projection inputs are fp16 in this engine:
+ * DESIGN.md 3 "numerics"), y fp32 [T][N]; T <= 32.  The product is exact in both operands, the sum is fp32. */
 RT_API int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t K, int32_t T, int32_t device);
 /* y = rmsnorm(x) * w, rounded to bf16: x fp32 [T][H], w bf16 bits [H], y bf16 bits [T][H]. */
 RT_API int rt_k_rmsnorm(const float* x, const uint16_t* w, uint16_t* y, int32_t T, int32_t H, float eps, int32_t device);
@@ -199,12 +209,13 @@ RT_API int rt_k_sample_topkp(const float* logits, int32_t T, int32_t V, float te
 RT_API int rt_k_attention(const uint16_t* q, const uint16_t* k, const uint16_t* v, const int32_t* lens,
                           float* out, int32_t T, int32_t ctx, int32_t n_q, int32_t n_kv, int32_t hd,
                           int32_t shared, int32_t chunk, int32_t device);
-/* Prefill projection on the tcgen05 tensor cores: c[s][n] = sum_k a[s][k] * w[n][k]; a bf16 bits [S][K], w bf16 bits
- * [N][K] (row-major; converted to the engine's core-matrix-major layout internally), c fp32 [S][N]. */
+/* Prefill projection on the tcgen05 tensor cores: c[s][n] = sum_k a[s][k] * w[n][k]; a FP16 bits [S][K], w bf16 bits
+ * [N][K] (row-major; converted internally to the engine's core-matrix-major layout and to its fp16 twin), c fp32 [S][N]. */
 RT_API int rt_k_gemm_tc5(const uint16_t* a, const uint16_t* w, float* c, int32_t S, int32_t N, int32_t K, int32_t device);
-/* Time `iters` back-to-back launches of the decode GEMV on an [N][K] bf16 matrix that is re-streamed
- * from HBM (rotating over enough copies to exceed L2); returns mean ms per launch. */
-RT_API int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t device, double* ms_out);
+/* Time `iters` back-to-back launches of the decode projection kernel on an [N][K] bf16 matrix that is re-streamed
+ * from HBM (rotating over enough copies to exceed L2); epi 0 = plain store, 2 = the fused SwiGLU epilogue of the
+ * gate/up projection (the dominant kernel of a decode step); returns mean ms per launch. */
+RT_API int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t epi, int32_t device, double* ms_out);
 
 /* Paged GQA decode attention for callers that must not allocate.  It has no counterpart in the
  * reference.  It exists for two kinds of caller: a process that has already given (almost) all of
@@ -217,7 +228,8 @@ RT_API int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32
  *   page_table_dev int32 [T][pt_stride]        page ids of sequence t, in order
  *   query_pos_dev  int32 [T]                   position of query t = number of earlier tokens; it attends keys 0..pos
  *   out_dev        fp32 [T][n_q][hd]
- * max_len is an upper bound of query_pos+1 over the batch; chunk (multiple of 16) is the split-KV
+ * max_len is an upper bound of query_pos+1 over the batch (a position beyond it is clamped on the
+ * device: that query then attends only its first max_len keys); chunk (multiple of 16) is the split-KV
  * granularity.  The launch is asynchronous on `stream` (a cudaStream_t; NULL = default stream), and
  * `device` must be the calling thread's current device.
  * The split-KV partial results go to a 4.25 MiB scratch array built into the library (every GPU that

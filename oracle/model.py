@@ -14,14 +14,19 @@ Rounding points (they mirror the engine so that parity can be tight):
   * K (after RoPE) and V are rounded to bf16 when they enter the KV cache, and every
     attention read -- including the current token's own K/V -- sees the rounded values
     (``round_kv``);
-  * with ``round_act`` the inputs of every matmul (x * norm weight -- the RMSNorm scalar r is applied
-    to the projection's output, see ``_rms_split`` --, attention output, SwiGLU output) and Q are
-    rounded to bf16;
+  * with ``round_act`` the inputs of every projection (x * norm weight -- the RMSNorm scalar r is applied
+    to the projection's output, see ``_rms_split`` --, attention output, SwiGLU output) are rounded to
+    **fp16** (11 significant bits, saturating at +-65504) and Q is rounded to bf16.  fp16 and not bf16: with
+    bf16 matmul inputs two correct implementations that only differ in fp32 summation order drift
+    1.2e-2 of max |logit| apart on the 16-layer Llama-3.2-1B (each rounding point turns a 1e-6
+    difference into 2^-9 flips, and 64 rounding points decorrelate them), which is above the 1e-2
+    parity bar; with fp16 inputs the same experiment gives 2.5e-3 (scripts/noise_floor_probe.py);
   * everything else (residual stream, softmax, accumulation) is fp32.
 """
 from __future__ import annotations
 
 import math
+import time
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -62,6 +67,11 @@ def _rbf16(t: torch.Tensor) -> torch.Tensor:
     return t.to(torch.bfloat16).to(torch.float32)
 
 
+def _rf16(t: torch.Tensor) -> torch.Tensor:
+    """fp16 rounding of a projection input, saturating (the engine's split_f16, csrc/common.cuh)."""
+    return t.clamp(-65504.0, 65504.0).to(torch.float16).to(torch.float32)
+
+
 @dataclass
 class KVState:
     """Per-sequence KV cache: lists (one per layer) of [n_kv, len, head_dim] fp32 tensors."""
@@ -83,6 +93,9 @@ class OracleModel:
         cos, sin = rope_table(a, max_pos)
         self.cos, self.sin = torch.from_numpy(cos), torch.from_numpy(sin)
         self.max_pos = max_pos
+        # bench.py's CPU arm: seconds spent inside the decoder-layer loops (the part that scales with depth), so that a
+        # truncated-depth run of a model too big for host RAM can be extrapolated to the full layer count
+        self.layer_seconds = 0.0
 
     # -- building blocks ------------------------------------------------------------------
     def _rms(self, x, w):
@@ -93,7 +106,7 @@ class OracleModel:
         """RMSNorm(x)·w factored as (x*w, r) with r = rsqrt(mean x^2 + eps): the per-row scalar r commutes
         with the projection that follows, so ``(x*w) @ W.T * r`` is the same function as
         ``_rms(x, w) @ W.T`` (modeling_llama.py LlamaRMSNorm + the Linear after it).  The engine rounds
-        x*w to bf16 and applies r to the fp32 accumulators; with ``round_act`` the oracle rounds at the
+        x*w to fp16 and applies r to the fp32 accumulators; with ``round_act`` the oracle rounds at the
         same point."""
         var = (x * x).mean(-1, keepdim=True)
         return x * w, torch.rsqrt(var + self.a.rms_eps)
@@ -120,10 +133,12 @@ class OracleModel:
         x = sd["embed"][ids]
         G = a.n_q // a.n_kv
         scale = 1.0 / math.sqrt(a.head_dim)
-        ra = _rbf16 if round_act else (lambda t: t)
+        ra = _rf16 if round_act else (lambda t: t)
+        rq = _rbf16 if round_act else (lambda t: t)
         if not kv.k:
             kv.k = [torch.zeros(a.n_kv, 0, a.head_dim) for _ in range(a.layers)]
             kv.v = [torch.zeros(a.n_kv, 0, a.head_dim) for _ in range(a.layers)]
+        t_layers = time.perf_counter()
         for l in range(a.layers):
             p = f"l{l}."
             h, r = self._rms_split(x, sd[p + "in_norm"])
@@ -140,7 +155,7 @@ class OracleModel:
             v = v.view(T, a.n_kv, a.head_dim)
             if round_kv:
                 k, v = _rbf16(k), _rbf16(v)
-            q = ra(q)
+            q = rq(q)
             kv.k[l] = torch.cat([kv.k[l], k.transpose(0, 1)], dim=1)
             kv.v[l] = torch.cat([kv.v[l], v.transpose(0, 1)], dim=1)
             K, V = kv.k[l], kv.v[l]                      # [n_kv, L, hd]
@@ -160,6 +175,7 @@ class OracleModel:
             u = (h @ sd[p + "up"].T) * r
             act = torch.nn.functional.silu(g) * u
             x = x + ra(act) @ sd[p + "down"].T
+        self.layer_seconds += time.perf_counter() - t_layers
         kv.length = p0 + T
         if last_only:
             x = x[-1:]
@@ -170,7 +186,7 @@ class OracleModel:
     def generate(self, prompt_ids, max_new_tokens: int, kv: KVState | None = None, round_act: bool = True,
                  prefill_chunk: int = 512, return_logits: bool = False):
         """Greedy decoding, EOS ignored.  ``round_act=True`` is the engine's numerics
-        (bf16 matmul inputs everywhere).  Returns ids, or (ids, per-step logits)."""
+        (fp16 projection inputs, bf16 Q / K / V).  Returns ids, or (ids, per-step logits)."""
         kv = kv if kv is not None else KVState()
         ids = list(prompt_ids)
         logits = None
@@ -219,11 +235,13 @@ def decode_step_batch(m: OracleModel, tokens, kvs, round_act: bool = True) -> to
     Numerically the same as B calls of ``forward([tok], kv)`` up to fp32 summation order."""
     a, sd = m.a, m.sd
     B = len(tokens)
-    ra = _rbf16 if round_act else (lambda t: t)
+    ra = _rf16 if round_act else (lambda t: t)
+    rq = _rbf16 if round_act else (lambda t: t)
     pos = torch.tensor([kv.length for kv in kvs])
     x = sd["embed"][torch.as_tensor(tokens, dtype=torch.long)]
     G = a.n_q // a.n_kv
     scale = 1.0 / math.sqrt(a.head_dim)
+    t_layers = time.perf_counter()
     for l in range(a.layers):
         p = f"l{l}."
         h, r = m._rms_split(x, sd[p + "in_norm"])
@@ -231,7 +249,7 @@ def decode_step_batch(m: OracleModel, tokens, kvs, round_act: bool = True) -> to
         q, k, v = (h @ sd[p + "q"].T) * r, (h @ sd[p + "k"].T) * r, (h @ sd[p + "v"].T) * r
         if a.qkv_bias:
             q, k, v = q + sd[p + "q_bias"], k + sd[p + "k_bias"], v + sd[p + "v_bias"]
-        q = ra(m._rope(q.view(B, a.n_q, a.head_dim), pos))
+        q = rq(m._rope(q.view(B, a.n_q, a.head_dim), pos))
         k = _rbf16(m._rope(k.view(B, a.n_kv, a.head_dim), pos))
         v = _rbf16(v.view(B, a.n_kv, a.head_dim))
         outs = []
@@ -247,6 +265,7 @@ def decode_step_batch(m: OracleModel, tokens, kvs, round_act: bool = True) -> to
         h = ra(h)
         act = torch.nn.functional.silu((h @ sd[p + "gate"].T) * r) * ((h @ sd[p + "up"].T) * r)
         x = x + ra(act) @ sd[p + "down"].T
+    m.layer_seconds += time.perf_counter() - t_layers
     for kv in kvs:
         kv.length += 1
     xf, r = m._rms_split(x, sd["final_norm"])

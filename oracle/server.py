@@ -22,12 +22,19 @@ from .model import KVState, OracleModel, decode_step_batch
 
 
 class OracleServer:
-    def __init__(self, model: str, seed: int = 0, max_pos: int = 4096, max_new_tokens: int = 512, threads: int | None = None):
+    def __init__(self, model: str, seed: int = 0, max_pos: int = 4096, max_new_tokens: int = 512, threads: int | None = None,
+                 layers: int | None = None):
+        """``layers``: keep only the first n decoder layers (models too big for host RAM: bench.py times a truncated
+        depth at TRUE dimensions and extrapolates the layer loop, flagged as such)."""
         if threads:
             torch.set_num_threads(threads)
         self.model_name = model
         self.max_new_tokens = max_new_tokens
-        self.m = OracleModel(ARCHS[model], seed, max_pos=max_pos)
+        arch = ARCHS[model]
+        self.full_layers = arch.layers
+        if layers and layers < arch.layers:
+            arch = arch.with_layers(layers)
+        self.m = OracleModel(arch, seed, max_pos=max_pos)
 
     # one request, greedy (what one knight turn costs on the CPU server)
     def complete_ids(self, ids, max_new_tokens=None):
@@ -45,18 +52,23 @@ class OracleServer:
 
     # N concurrent requests with the shared prefix prefilled once and the decode projections batched:
     # the fairest CPU counterpart of the engine's BATCH mode.  Returns (ids per request, timings).
-    def complete_batch_ids(self, prompts, max_new_tokens, shared: int = 0):
+    def complete_batch_ids(self, prompts, max_new_tokens, shared: int = 0, prefill_chunk: int = 1024):
         t0 = time.perf_counter()
+        self.m.layer_seconds = 0.0
         base = KVState()
-        if shared:
-            self.m.forward(prompts[0][:shared], base, round_act=True, last_only=True)
+        for s in range(0, shared, prefill_chunk):          # chunked: the score matrix of a chunk stays in cache-sized pieces
+            self.m.forward(prompts[0][s:min(shared, s + prefill_chunk)], base, round_act=True, last_only=True)
         kvs, toks = [], []
         for p in prompts:
             kv = base.clone() if shared else KVState()
-            lg = self.m.forward(p[shared:], kv, round_act=True, last_only=True)
+            lg = None
+            for s in range(shared, len(p), prefill_chunk):
+                lg = self.m.forward(p[s:s + prefill_chunk], kv, round_act=True, last_only=True)
             kvs.append(kv)
             toks.append(int(lg[-1].argmax()))
         t1 = time.perf_counter()
+        prefill_layer_s = self.m.layer_seconds
+        self.m.layer_seconds = 0.0
         outs = [[t] for t in toks]
         for _ in range(max_new_tokens - 1):
             lg = decode_step_batch(self.m, toks, kvs)
@@ -64,7 +76,9 @@ class OracleServer:
             for o, t in zip(outs, toks):
                 o.append(t)
         t2 = time.perf_counter()
-        return outs, {"prefill_s": t1 - t0, "decode_s": t2 - t1, "decode_steps": max_new_tokens - 1}
+        return outs, {"prefill_s": t1 - t0, "decode_s": t2 - t1, "decode_steps": max_new_tokens - 1,
+                      "prefill_layer_s": prefill_layer_s, "decode_layer_s": self.m.layer_seconds,
+                      "layers": self.m.a.layers, "full_layers": self.full_layers}
 
 
 def serve(model: str, port: int = 11435, seed: int = 0, max_new_tokens: int = 64):

@@ -14,7 +14,7 @@ import math
 import torch
 import torch.distributed as dist
 
-from .model import KVState, OracleModel, _rbf16
+from .model import KVState, OracleModel, _rbf16, _rf16
 
 
 @torch.no_grad()
@@ -36,7 +36,7 @@ def forward_tp(m: OracleModel, ids, kv: KVState, rank: int, tp: int):
     for l in range(a.layers):
         p = f"l{l}."
         h, r = m._rms_split(x, sd[p + "in_norm"])
-        h = _rbf16(h)
+        h = _rf16(h)
         q = (h @ rows(sd[p + "q"], nq * hd).T) * r
         k = (h @ rows(sd[p + "k"], nkv * hd).T) * r
         v = (h @ rows(sd[p + "v"], nkv * hd).T) * r
@@ -54,19 +54,19 @@ def forward_tp(m: OracleModel, ids, kv: KVState, rank: int, tp: int):
         causal = torch.arange(L)[None, :] <= pos[:, None]
         s = s.masked_fill(~causal[None, None], float("-inf"))
         o = torch.bmm(torch.softmax(s, dim=-1).view(nkv, G * T, L), Vv).view(nkv, G, T, hd)
-        o = _rbf16(o.permute(2, 0, 1, 3).reshape(T, nq * hd))
+        o = _rf16(o.permute(2, 0, 1, 3).reshape(T, nq * hd))
         part = o @ sd[p + "o"][:, rank * nq * hd:(rank + 1) * nq * hd].T          # row-parallel partial sum
         dist.all_reduce(part)
         x = x + part
         h, r = m._rms_split(x, sd[p + "post_norm"])
-        h = _rbf16(h)
+        h = _rf16(h)
         act = torch.nn.functional.silu((h @ rows(sd[p + "gate"], F).T) * r) * ((h @ rows(sd[p + "up"], F).T) * r)
-        part = _rbf16(act) @ sd[p + "down"][:, rank * F:(rank + 1) * F].T
+        part = _rf16(act) @ sd[p + "down"][:, rank * F:(rank + 1) * F].T
         dist.all_reduce(part)
         x = x + part
     kv.length = p0 + T
     xf, r = m._rms_split(x, sd["final_norm"])
-    return (_rbf16(xf) @ rows(sd["lm_head"], V).T) * r
+    return (_rf16(xf) @ rows(sd["lm_head"], V).T) * r
 
 
 def argmax_tp(local_logits: torch.Tensor, rank: int, tp: int) -> list:

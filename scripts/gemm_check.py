@@ -5,10 +5,10 @@ from oracle import weights as W
 from theroundtaible_b200 import engine as E
 rng = np.random.default_rng(0)
 for (S, N, K) in [(128, 256, 64), (128, 256, 256), (100, 576, 448), (300, 512, 128), (1216, 3072, 2048)]:
-    a = W.f32_to_bf16_bits(rng.standard_normal((S, K)).astype(np.float32))
+    ah = rng.standard_normal((S, K)).astype(np.float16); a = ah.view(np.uint16)
     w = W.f32_to_bf16_bits((rng.standard_normal((N, K)) * 0.05).astype(np.float32))
     c = E.k_gemm_tc5(a, w)
-    ref = W.bf16_bits_to_f32(a).astype(np.float64) @ W.bf16_bits_to_f32(w).astype(np.float64).T
+    ref = ah.astype(np.float64) @ W.bf16_bits_to_f32(w).astype(np.float64).T
     err = np.abs(c - ref).max() / np.abs(ref).max()
     print(f"S={S} N={N} K={K}: rel err {err:.3e}", "OK" if err < 1e-4 else "MISMATCH", flush=True)
     if err >= 1e-4:

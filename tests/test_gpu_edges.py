@@ -85,3 +85,18 @@ def test_adapter_timeout_and_reuse_after_error():
     assert "context length exceeded" in str(ei.value)
     assert ad.execute("short prompt")                                          # the engine is still usable
     assert ad.last_generation.n_prompt_tokens == len("short prompt") + 3
+
+
+def test_eos_ids_come_from_the_configuration():
+    """rt_config.eos_ids (filled from a checkpoint's config.json by config_from_hf) decide where generation stops; the
+    literal id 2 is only the default of the byte tokenizer."""
+    prompt = list(range(20, 60))
+    with E.Engine("tiny-llama", seed=3, max_batch=1, max_ctx=128) as eng:
+        free = eng.generate_ids([prompt], max_new_tokens=12)[0].tokens
+    stop_at = free.index(free[-1])                     # first occurrence of the id that will serve as <eos>
+    cfg = E.arch_config("tiny-llama")
+    cfg.n_eos, cfg.eos_ids[0], cfg.eos_ids[1] = 2, (free[-1] + 1) % 512 if (free[-1] + 1) % 512 not in free else free[-1], free[-1]
+    with E.Engine(cfg, seed=3, max_batch=1, max_ctx=128) as eng:
+        g = eng.generate_ids([prompt], max_new_tokens=12, ignore_eos=False)[0]
+        assert g.tokens == free[:stop_at] and g.finish_reason == 1
+        assert eng.generate_ids([prompt], max_new_tokens=12, ignore_eos=True)[0].tokens == free

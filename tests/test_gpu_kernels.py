@@ -15,13 +15,19 @@ def _rand_bits(rng, shape, std=1.0):
     return W.f32_to_bf16_bits((rng.standard_normal(shape) * std).astype(np.float32))
 
 
+def _rand_f16(rng, shape, std=1.0):
+    """Projection inputs are fp16 in the engine (DESIGN.md 3 "numerics"); returns (bits, float64 values)."""
+    h = (rng.standard_normal(shape) * std).astype(np.float16)
+    return h.view(np.uint16), h.astype(np.float64)
+
+
 @pytest.mark.parametrize("N,K,T", [(16, 32, 1), (128, 256, 3), (3072, 2048, 5), (2048, 8192, 8), (1152, 896, 7),
                                    (512, 4864, 12), (256, 2048, 16), (640, 1024, 32), (16384, 2048, 3), (9728, 896, 1)])
 def test_gemv_matches_fp32_matmul(N, K, T):
     rng = np.random.default_rng(N * 7 + K + T)
-    w, x = _rand_bits(rng, (N, K), 0.05), _rand_bits(rng, (T, K))
-    y = E.k_gemv(w, x)
-    ref = W.bf16_bits_to_f32(x).astype(np.float64) @ W.bf16_bits_to_f32(w).astype(np.float64).T
+    w, (x, xf) = _rand_bits(rng, (N, K), 0.05), _rand_f16(rng, (T, K))
+    y = E.k_gemv(w, x)                               # fp16 inputs enter the MMAs as bf16 hi + lo: the products are exact
+    ref = xf @ W.bf16_bits_to_f32(w).astype(np.float64).T
     tol = 2e-5 * np.abs(ref).max() + 1e-6            # fp32 accumulation, different summation order
     assert np.abs(y - ref).max() <= tol
 
@@ -29,15 +35,15 @@ def test_gemv_matches_fp32_matmul(N, K, T):
 @pytest.mark.parametrize("S,N,K", [(128, 256, 64), (100, 576, 448), (300, 512, 128), (1, 32, 64), (1216, 3072, 2048), (257, 4096, 8192)])
 def test_tcgen05_prefill_gemm_matches_fp64_matmul(S, N, K):
     rng = np.random.default_rng(S + N + K)
-    a, w = _rand_bits(rng, (S, K)), _rand_bits(rng, (N, K), 0.05)
-    c = E.k_gemm_tc5(a, w)
-    ref = W.bf16_bits_to_f32(a).astype(np.float64) @ W.bf16_bits_to_f32(w).astype(np.float64).T
+    (a, af), w = _rand_f16(rng, (S, K)), _rand_bits(rng, (N, K), 0.05)
+    c = E.k_gemm_tc5(a, w)                           # fp16 activations x the fp16 twin of the bf16 weights
+    ref = af @ W.bf16_bits_to_f32(w).astype(np.float64).T
     assert np.abs(c - ref).max() <= 2e-5 * np.abs(ref).max() + 1e-6     # fp32 accumulation in TMEM
 
 
 def test_gemv_is_deterministic_run_to_run():
     rng = np.random.default_rng(5)
-    w, x = _rand_bits(rng, (2048, 2048), 0.05), _rand_bits(rng, (8, 2048))
+    w, (x, _) = _rand_bits(rng, (2048, 2048), 0.05), _rand_f16(rng, (8, 2048))
     a, b = E.k_gemv(w, x), E.k_gemv(w, x)
     assert (a.view(np.uint32) == b.view(np.uint32)).all()        # fixed-order reduction: bit-identical
 

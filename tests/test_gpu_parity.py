@@ -268,9 +268,17 @@ def test_adapter_execute_returns_nonempty_text_and_round_batches():
     assert isinstance(text, str) and len(text) > 0
     assert ad.get_max_source_chars() == 2000
     head = "Je neemt deel aan een TheRoundtAIble discussie.\nREGELS: " + "x" * 200 + "\nJe naam is: "
-    texts = ad.execute_round([head + n for n in ("Claude", "Gemini", "GPT")])
+    prompts = [head + n for n in ("Claude", "Gemini", "GPT")]
+    texts = ad.execute_round(prompts)
     assert len(texts) == 3 and all(len(t) > 0 for t in texts)
-    assert texts[0] == ad.execute(head + "Claude") or True            # SEQ and BATCH agree up to tie-breaks
+    batch = [g.tokens for g in ad.last_round]
+    assert ad.execute(prompts[0]) == E.detokenize(ad.last_generation.tokens)
+    seq = ad.last_generation.tokens
+    # SEQ (one knight per call) and BATCH (one call per round) both follow the oracle under the margin rule: they can
+    # only part ways at a numerical tie of the oracle's own top two logits
+    oracle = OracleModel(ARCHS["tiny-qwen"], 0, max_pos=2048)
+    for p, toks in [(prompts[0], seq)] + list(zip(prompts, batch)):
+        _greedy_compare(toks, oracle, E.tokenize_chat(p), len(toks), err_bound=REL_TOL * 2.5)
 
 
 def test_config2_architecture_full_depth_llama32_1b():
@@ -278,21 +286,16 @@ def test_config2_architecture_full_depth_llama32_1b():
     128,256-token head) against the oracle: teacher-forced logits through both kernel paths, then 3 knights sharing a
     prefix, greedy, under the margin-aware rule.
 
-    Tolerance, as measured (scripts/parity_probe_1b.py): with random N(0, 0.02) weights the logits of
-    this model are small (max |logit| ~ 4 over 128k entries) and the bf16 rounding of the activations -- the numerics
-    contract itself -- moves them by 1.5-2.1e-2 of max |logit| (oracle with vs without that rounding); two evaluation
-    orders of the SAME contract (the engine's prefill and decode kernels) differ by up to 1.3e-2.  The 1e-2 bar that the
-    tiny, 0.5B and truncated-depth models meet is therefore AT the rounding-noise floor here.  What is asserted: the RMS
-    error over the vocabulary stays below 3e-3 of max |logit|, the worst single logit below 1.5e-2, and the engine sits
-    closer to the oracle than the oracle's own rounding sits to exact activations."""
+    The bar is north_star's: every step's logits within 1e-2 of max |logit|, in BOTH kernel paths, and 64 greedy tokens
+    under the margin rule.  Round 1 missed it at full depth (1.0-1.3e-2) because bf16 projection inputs put the
+    rounding-noise floor of the contract itself at 1.2e-2 for this model (scripts/noise_floor_probe.py); projection
+    inputs are fp16 since round 2 (floor 2.5e-3), so the bar holds with margin."""
     a = ARCHS["llama-3.2-1b"]
     oracle = OracleModel(a, 0, max_pos=256)
     rng = np.random.default_rng(1234 + 2)
     ids = rng.integers(0, a.vocab, 72)
     ref = oracle.forward(ids, KVState(), round_act=True).numpy()
-    exact_act = oracle.forward(ids, KVState(), round_act=False).numpy()
     scale = np.abs(ref).max(-1)
-    floor = (np.abs(ref - exact_act).max(-1) / scale).max()
     with E.Engine("llama-3.2-1b", seed=0, max_batch=3, max_ctx=256) as eng:
         eng.seq_reset()
         got1 = eng.step_logits(ids, mode=1)
@@ -301,13 +304,34 @@ def test_config2_architecture_full_depth_llama32_1b():
         for got, want, sc in ((got1, ref, scale), (got0, ref[:40], scale[:40])):
             worst = (np.abs(got - want).max(-1) / sc).max()
             rms = (np.sqrt(((got - want) ** 2).mean(-1)) / sc).max()
-            assert rms <= 3e-3, rms
-            assert worst <= 1.5e-2 and worst < floor, (worst, floor)
+            assert worst <= REL_TOL, worst
+            assert rms <= 1e-3, rms
         prompts = [ids[:48].tolist() + rng.integers(0, a.vocab, 10 + i).tolist() for i in range(3)]
-        gens = eng.generate_ids(prompts, max_new_tokens=24)
-    bound = 1.5e-2 * float(np.abs(ref).max())
-    ties = sum(_greedy_compare(g.tokens, oracle, p, 24, err_bound=bound) for p, g in zip(prompts, gens))
+        gens = eng.generate_ids(prompts, max_new_tokens=64)
+    bound = REL_TOL * float(np.abs(ref).max())
+    ties = sum(_greedy_compare(g.tokens, oracle, p, 64, err_bound=bound) for p, g in zip(prompts, gens))
     assert ties <= 4
+
+
+@pytest.mark.parametrize("model,layers,n_ids", [("llama-3.1-8b", 8, 96), ("qwen2.5-32b", 1, 64), ("llama-3.1-70b", 1, 64)])
+def test_large_configs_true_dimensions_truncated_depth(model, layers, n_ids):
+    """SURVEY.md 8c "Large configs": the benchmarked models the CPU oracle cannot hold at full depth are checked at their
+    TRUE dimensions with the layer count truncated (stated here and in every report): Llama-3.1-8B at 8 of 32 layers,
+    Qwen2.5-32B (hidden 5,120, 40/8 heads, qkv bias, FFN 27,648, 152k vocab) and Llama-3.1-70B (hidden 8,192, 64/8 heads,
+    FFN 28,672) at one decoder layer each.  Both kernel paths against the oracle at the north_star bar."""
+    a = ARCHS[model].with_layers(layers)
+    oracle = OracleModel(a, 0, max_pos=256)
+    ids = np.random.default_rng(layers + n_ids).integers(0, a.vocab, n_ids)
+    ref = oracle.forward(ids, KVState(), round_act=True).numpy()
+    del oracle
+    scale = np.abs(ref).max(-1)
+    with E.Engine(f"{model}@L{layers}", seed=0, max_batch=1, max_ctx=256) as eng:
+        eng.seq_reset()
+        got1 = eng.step_logits(ids, mode=1)
+        eng.seq_reset()
+        got0 = eng.step_logits(ids[:40], mode=0)
+    assert (np.abs(got1 - ref).max(-1) / scale).max() <= REL_TOL
+    assert (np.abs(got0 - ref[:40]).max(-1) / scale[:40]).max() <= REL_TOL
 
 
 def test_config2_full_size_properties():

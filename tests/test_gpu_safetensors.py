@@ -88,6 +88,13 @@ def test_from_pretrained_matches_hf(tmp_path, family, tied, head_dim):
         # and free-running generation runs on the loaded weights
         g = eng.generate_ids([[1, 2, 3, 4, 5]], max_new_tokens=8)[0]
         assert len(g.tokens) == 8
+        # the text entry points tokenise with the built-in BYTE tokenizer, which is not this checkpoint's: refused
+        from theroundtaible_b200.engine import EngineError
+        with pytest.raises(EngineError, match="byte-level"):
+            eng.generate("hello")
+        # the end-of-sequence id comes from config.json (here transformers' default for the family), not a literal
+        want_eos = m.config.eos_token_id
+        assert (eng.cfg.n_eos == 0) if want_eos is None else (eng.cfg.n_eos >= 1 and eng.cfg.eos_ids[0] == want_eos)
 
 
 def test_fp32_checkpoint_sharded_directory(tmp_path):

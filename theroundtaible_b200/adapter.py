@@ -93,6 +93,7 @@ class B200LocalLlmAdapter(BaseAdapter):
         self._engine_args = dict(seed=seed, max_batch=max_batch, max_ctx=max_ctx, flags=RT_FLAG_PREFIX_CACHE)
         self._load_error: Optional[BaseException] = None
         self.last_generation = None          # engine.Generation of the last execute(): token counts, timings, cache hits
+        self.last_round = None               # the Generations of the last execute_round()
 
     # -- engine life cycle ----------------------------------------------------------------------
     def _device(self) -> int:
@@ -156,6 +157,7 @@ class B200LocalLlmAdapter(BaseAdapter):
         try:
             gens = self._get_engine().generate_batch(list(prompts), max_new_tokens=self.max_new_tokens,
                                                      ignore_eos=self.ignore_eos, deadline_ms=int(timeout), **self._sampling)
+            self.last_round = gens
             return [g.text for g in gens]
         except Exception as ex:  # noqa: BLE001
             raise classify_error(ex, self.name) from ex

@@ -16,7 +16,8 @@ LIB_DIR = os.path.join(HERE, "_lib")
 LIB = os.path.join(LIB_DIR, "librt_engine.so")
 SOURCES = ["engine.cu", "capi.cu", "noalloc.cu", "prefill.cu", "tp.cu", "tokenizer.cpp", "safetensors.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared", "-ldl"]
+              "-Xcompiler", "-fPIC,-fvisibility=hidden"]
+LINK_FLAGS = ["-shared", "-ldl"]
 
 
 def _fingerprint() -> str:
@@ -38,15 +39,28 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     extra = os.environ.get("RT_NVCC_EXTRA", "").split()      # experiments only (e.g. -DRT_ATTN_STAGES=3)
-    cmd = [nvcc, *NVCC_FLAGS, *extra, "-o", LIB, *[os.path.join(CSRC, s) for s in SOURCES]]
+    # one nvcc per translation unit, in parallel, then one link
+    from concurrent.futures import ThreadPoolExecutor
+    obj_dir = os.path.join(LIB_DIR, "obj")
+    os.makedirs(obj_dir, exist_ok=True)
+    vflags = ["-Xptxas", "-v"] if verbose else []
+
+    def compile_one(src):
+        obj = os.path.join(obj_dir, os.path.splitext(src)[0] + ".o")
+        r = subprocess.run([nvcc, *NVCC_FLAGS, *vflags, *extra, "-c", "-o", obj, os.path.join(CSRC, src)],
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed on {src}:\n" + r.stdout + r.stderr)
+        return obj, r.stderr
+
+    with ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 4)) as pool:
+        results = list(pool.map(compile_one, SOURCES))
     if verbose:
-        cmd.insert(1, "-Xptxas")
-        cmd.insert(2, "-v")
-    r = subprocess.run(cmd, capture_output=True, text=True)
+        for _, err in results:
+            print(err)
+    r = subprocess.run([nvcc, *NVCC_FLAGS, *LINK_FLAGS, "-o", LIB, *[o for o, _ in results]], capture_output=True, text=True)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
-    if verbose:
-        print(r.stderr)
+        raise RuntimeError("nvcc link failed:\n" + r.stdout + r.stderr)
     with open(stamp, "w") as f:
         f.write(fp)
     return LIB

@@ -38,7 +38,7 @@ struct Attn3Args {
     const int* slot_pos;
     int T, n_q, n_kv;
     float scale_log2;
-    bf16* out;                  // [T][n_q*hd] normalised
+    f16* out;                   // [T][n_q*hd] normalised, fp16 (the O-projection's input)
     int ldo;
     int early;                  // index setup and old KV pages before the PDL wait (see AttnArgs.early)
 };
@@ -299,8 +299,8 @@ __global__ void __launch_bounds__(A3_WARPS * 32, 1) attn_decode3_kernel(const At
         }
         const float inv = 1.0f / L;
         uint2 pk;
-        pk.x = pack_bf16(acc.x * inv, acc.y * inv);
-        pk.y = pack_bf16(acc.z * inv, acc.w * inv);
+        pk.x = pack_f16(acc.x * inv, acc.y * inv);
+        pk.y = pack_f16(acc.z * inv, acc.w * inv);
         *reinterpret_cast<uint2*>(a.out + (size_t)slot * a.ldo + (size_t)(h * G + row) * HD + d4) = pk;
     }
 }

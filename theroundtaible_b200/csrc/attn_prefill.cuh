@@ -207,10 +207,10 @@ __global__ void __launch_bounds__(128, PFA_MIN_CTAS) attn_prefill_kernel(const P
     for (int r = 0; r < 2; ++r) {
         if (!row_ok[r]) continue;
         const float inv = 1.0f / l_run[r];
-        bf16* dst = a.out + (size_t)row_tok[r] * ldq + (size_t)row_head[r] * HD;
+        f16* dst = a.out + (size_t)row_tok[r] * ldq + (size_t)row_head[r] * HD;
 #pragma unroll
         for (int d = 0; d < HD / 8; ++d)
-            *reinterpret_cast<uint32_t*>(dst + d * 8 + 2 * q) = pack_bf16(o[d][2 * r] * inv, o[d][2 * r + 1] * inv);
+            *reinterpret_cast<uint32_t*>(dst + d * 8 + 2 * q) = pack_f16(o[d][2 * r] * inv, o[d][2 * r + 1] * inv);
     }
 }
 

@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5b_kernel(const 
         p5_wait(b_of, (n_tiles - 1) & 1);
         tc5_fence_after();
         const float inv = 1.0f / l_run;
-        bf16* dst = a.out + (size_t)(tok0 + t) * ((size_t)a.n_q * HD) + (size_t)(h * a.G + g) * HD + half * (HD / 2);
+        f16* dst = a.out + (size_t)(tok0 + t) * ((size_t)a.n_q * HD) + (size_t)(h * a.G + g) * HD + half * (HD / 2);
 #pragma unroll 1
         for (int c = 0; c < NH; ++c) {
             float w[32];
@@ -239,8 +239,8 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5b_kernel(const 
 #pragma unroll
                 for (int i = 0; i < 32; i += 8) {
                     uint4 pk;
-                    pk.x = pack_bf16(w[i] * inv, w[i + 1] * inv); pk.y = pack_bf16(w[i + 2] * inv, w[i + 3] * inv);
-                    pk.z = pack_bf16(w[i + 4] * inv, w[i + 5] * inv); pk.w = pack_bf16(w[i + 6] * inv, w[i + 7] * inv);
+                    pk.x = pack_f16(w[i] * inv, w[i + 1] * inv); pk.y = pack_f16(w[i + 2] * inv, w[i + 3] * inv);
+                    pk.z = pack_f16(w[i + 4] * inv, w[i + 5] * inv); pk.w = pack_f16(w[i + 6] * inv, w[i + 7] * inv);
                     *reinterpret_cast<uint4*>(dst + c * 32 + i) = pk;
                 }
             }

@@ -13,7 +13,6 @@
 
 int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi);
 void rt_attn_host_setup();
-void rt_gemv_stream_alloc(rt_engine* e);
 void rt_attn_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunk_blocks);
 
 namespace {
@@ -82,6 +81,7 @@ int rt_arch_by_name(const char* name, rt_config* cfg) {
                 cfg->ffn = r.ffn; cfg->vocab = r.vocab; cfg->tied = r.tied; cfg->qkv_bias = r.qkv_bias;
                 cfg->rope_theta = r.rope_theta; cfg->rms_eps = r.rms_eps; cfg->rope_factor = r.rope_factor;
                 cfg->rope_low_freq = r.rope_low; cfg->rope_high_freq = r.rope_high; cfg->rope_orig_ctx = r.rope_orig;
+                cfg->n_eos = 0;     // the byte tokenizer's <eos>
                 return;
             }
         }
@@ -150,6 +150,10 @@ int rt_generate_batch(rt_engine* e, const char* const* prompts, const size_t* le
     if (!e) { g_err = "invalid argument: null engine"; return RT_ERR_INVALID; }
     return guard(e, [&] {
         RT_REQUIRE(prompts && lens && outs && n >= 1, "null argument");
+        // the byte-level tokenizer only matches the seeded weights: a checkpoint's vocabulary is its own tokenizer's
+        if (e->from_checkpoint)
+            throw RtError(RT_ERR_INVALID, "text generation is unavailable for an engine created from a checkpoint: the built-in "
+                                          "tokenizer is byte-level; use rt_generate_ids with the checkpoint's tokenizer");
         std::vector<std::vector<int>> ids(n);
         std::vector<const int32_t*> ptrs(n);
         std::vector<int32_t> ls(n);
@@ -248,7 +252,6 @@ struct Scratch {
         e.dev = device;
         e.sm_count = prop.multiProcessorCount;
         RT_CUDA(cudaStreamCreateWithFlags(&e.st, cudaStreamNonBlocking));
-        rt_gemv_stream_alloc(&e);
     }
     template <typename T>
     T* alloc(size_t n, bool zero = true) {
@@ -275,7 +278,7 @@ int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t
         RT_REQUIRE(N > 0 && N % 16 == 0 && K > 0 && K % 32 == 0 && T >= 1 && T <= MAX_SLOTS, "need N%16==0, K%32==0, 1<=T<=32");
         Scratch s(device);
         bf16* dw = s.alloc<bf16>((size_t)N * K, false);
-        bf16* dx = s.alloc<bf16>((size_t)MAX_SLOTS * K);
+        f16* dx = s.alloc<f16>((size_t)MAX_SLOTS * K);
         float* dy = s.alloc<float>((size_t)MAX_SLOTS * N);
         std::vector<uint16_t> cm((size_t)N * K);
         wgen::rowmajor_to_cm(w, cm.data(), N, K);     // the kernel streams the core-matrix-major layout (gemv.cuh)
@@ -431,8 +434,9 @@ int rt_k_gemm_tc5(const uint16_t* a_bits, const uint16_t* w_bits, float* c, int3
         RT_REQUIRE(S >= 1 && N > 0 && N % 32 == 0 && K > 0 && K % 64 == 0, "need N % 32 == 0 and K % 64 == 0");
         Scratch s(device);
         const int S_pad = cdiv(S, 128) * 128;
-        bf16* da = s.alloc<bf16>((size_t)S_pad * K);
+        f16* da = s.alloc<f16>((size_t)S_pad * K);
         bf16* dw = s.alloc<bf16>((size_t)N * K, false);
+        f16* dw16 = s.alloc<f16>((size_t)N * K, false);
         float* dc = s.alloc<float>((size_t)S * N);
         std::vector<uint16_t> cm((size_t)N * K);
         wgen::rowmajor_to_cm(w_bits, cm.data(), N, K);
@@ -440,9 +444,10 @@ int rt_k_gemm_tc5(const uint16_t* a_bits, const uint16_t* w_bits, float* c, int3
         RT_CUDA(cudaMemcpyAsync(dw, cm.data(), (size_t)N * K * 2, cudaMemcpyHostToDevice, s.e.st));
         PfTensorMap ma, mw;
         pf_make_map_a(&ma, da, S_pad, K);
-        pf_make_map_w(&mw, dw, N, K, PF_BN);
+        bf16_to_f16_kernel<<<1024, 256, 0, s.e.st>>>(dw, dw16, (size_t)N * K / 8);     // the fp16 twin, as the engine makes it
+        pf_make_map_w(&mw, dw16, N, K, PF_BN);
         Gemm5Args g{};
-        g.S = S; g.N = N; g.K = K; g.out = dc; g.ldo = N;
+        g.ab_f16 = 1; g.S = S; g.N = N; g.K = K; g.out = dc; g.ldo = N;
         pf_gemm(s.e.st, false, G5_EPI_STORE, ma, mw, g);
         RT_CUDA(cudaGetLastError());
         if (const char* it = getenv("RT_GEMM_BENCH_ITERS")) {
@@ -466,24 +471,26 @@ int rt_k_gemm_tc5(const uint16_t* a_bits, const uint16_t* w_bits, float* c, int3
     });
 }
 
-int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t device, double* ms_out) {
+int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t epi, int32_t device, double* ms_out) {
     return guard(nullptr, [&] {
         RT_REQUIRE(ms_out != nullptr, "null argument");
         RT_REQUIRE(N > 0 && N % 16 == 0 && K > 0 && K % 32 == 0 && T >= 1 && T <= MAX_SLOTS && iters >= 1, "bad shape");
+        RT_REQUIRE(epi == EPI_STORE || epi == EPI_SWIGLU, "epi must be 0 (store) or 2 (SwiGLU)");
         Scratch s(device);
         const size_t mat = (size_t)N * K;
         const int copies = (int)std::max<size_t>(2, (size_t)400e6 / (mat * 2) + 1);   // > 3x L2 in rotation
         bf16* dw = s.alloc<bf16>(mat * copies);
-        bf16* dx = s.alloc<bf16>((size_t)MAX_SLOTS * K);
+        f16* dx = s.alloc<f16>((size_t)MAX_SLOTS * K);
         float* dy = s.alloc<float>((size_t)MAX_SLOTS * N);
         GemvArgs a{};
         a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N;
+        a.out_bf = s.alloc<f16>((size_t)MAX_SLOTS * N / 2); a.ldob = N / 2;      // SwiGLU: gate/up row pairs -> N/2 outputs
         cudaEvent_t e0, e1;
         RT_CUDA(cudaEventCreate(&e0));
         RT_CUDA(cudaEventCreate(&e1));
-        for (int i = 0; i < 3; ++i) { a.W = dw + mat * (i % copies); rt_gemv_host_dispatch(&s.e, a, EPI_STORE); }
+        for (int i = 0; i < 3; ++i) { a.W = dw + mat * (i % copies); rt_gemv_host_dispatch(&s.e, a, epi); }
         RT_CUDA(cudaEventRecord(e0, s.e.st));
-        for (int i = 0; i < iters; ++i) { a.W = dw + mat * (i % copies); rt_gemv_host_dispatch(&s.e, a, EPI_STORE); }
+        for (int i = 0; i < iters; ++i) { a.W = dw + mat * (i % copies); rt_gemv_host_dispatch(&s.e, a, epi); }
         RT_CUDA(cudaEventRecord(e1, s.e.st));
         RT_CUDA(cudaStreamSynchronize(s.e.st));
         RT_CUDA(cudaGetLastError());

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdexcept>
 #include <string>
@@ -25,6 +26,7 @@ struct RtError : public std::runtime_error {
     } while (0)
 
 typedef __nv_bfloat16 bf16;
+typedef __half f16;
 
 __host__ __device__ inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
@@ -40,6 +42,26 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 __device__ __forceinline__ uint16_t f2bf_bits(float a) {
     bf16 t = __float2bfloat16_rn(a);
     return *reinterpret_cast<uint16_t*>(&t);
+}
+
+// ---- the activation contract -----------------------------------------------------------------------------------
+// Every projection input (x * norm weight, attention output, SwiGLU output) is rounded to fp16, saturating at
+// +-65504, in BOTH phases; weights, Q, K and V are bf16; accumulation, residual stream and softmax are fp32
+// (DESIGN.md 3 "numerics"; oracle/model.py `_rf16`).  With bf16 inputs two correct implementations drift 1.2e-2 of
+// max |logit| apart on the 16-layer 1B model (rounding flips decorrelate), above the 1e-2 parity bar; fp16 gives 2.5e-3.
+__device__ __forceinline__ float sat_f16(float v) { return v > 65504.f ? 65504.f : (v < -65504.f ? -65504.f : v); }
+__device__ __forceinline__ uint32_t pack_f16(float a, float b) {
+    __half2 t = __floats2half2_rn(sat_f16(a), sat_f16(b));   // .x = a (low half)
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ f16 to_f16(float a) { return __float2half_rn(sat_f16(a)); }
+// The decode kernels multiply with mma.sync, whose operands must share one 16-bit format, and the weights are bf16:
+// an fp16 value (11 significant bits) is fed as bf16 hi (8 bits, RNE) + bf16 lo (the remainder: <= 3 significant bits,
+// exact), two MMAs on the same weight fragment -- free under an HBM-bound stream.  `w` holds two fp16 values.
+__device__ __forceinline__ void split_f16x2(uint32_t w, uint32_t& hi, uint32_t& lo) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    hi = pack_bf16(f.x, f.y);
+    lo = pack_bf16(f.x - bf16lo(hi), f.y - bf16hi(hi));
 }
 
 // streaming 16-byte load that does not pollute L1 (weights are read exactly once per step)

@@ -12,9 +12,7 @@
 #include <cuda_profiler_api.h>
 #include <memory>
 
-#include "attn_decode2.cuh"
 #include "attn_decode3.cuh"
-#include "gemv_stream.cuh"
 #include "kernels.cuh"
 #include "safetensors.h"
 #include "sampler.cuh"
@@ -407,23 +405,8 @@ void gemv_pick_warps(rt_engine* e, const GemvArgs& a, int grid) {
     else gemv_launch<EPI, NT, MT, 8>(e, a, grid);
 }
 
-template <int EPI, int NT>
-void gemv_stream_launch(rt_engine* e, const GemvArgs& a, int grid) {
-    GemvStreamFix fx{e->gs_scratch, e->gs_flags};
-    launch_pdl(e, gemv_stream_kernel<NT, EPI>, dim3(grid), dim3(GS_THREADS), (size_t)GS_RING_BYTES, a, fx);
-}
-
 template <int EPI>
 int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
-    if (e->use_stream && e->gs_scratch && EPI == EPI_STORE && !a.ss_in && !a.inv_rms) {
-        // persistent stream-K kernel: one CTA per SM, equal contiguous byte ranges; candidates are per 16-row tile
-        const long long units = (long long)(a.N / 16) * (a.K / 32);
-        const int grid = (int)std::min<long long>(e->sm_count, units);
-        if (a.T <= 8) gemv_stream_launch<EPI, 1>(e, a, grid);
-        else if (a.T <= 16) gemv_stream_launch<EPI, 2>(e, a, grid);
-        else gemv_stream_launch<EPI, 4>(e, a, grid);
-        return a.N / 16;
-    }
     static const int force_mt = env_int("RT_GEMV_MT", 0);
     const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);
     // rows per CTA: the smallest 16*MT that fits the whole matrix into ONE wave of resident CTAs (2 per SM with 8 warps,
@@ -474,30 +457,6 @@ int rt_gemv_host_dispatch(rt_engine* e, const GemvArgs& a, int epi) {
     }
 }
 
-void rt_gemv_stream_setup() {
-    auto set = [](auto kern) { RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_RING_BYTES)); };
-    set(gemv_stream_kernel<1, EPI_STORE>); set(gemv_stream_kernel<2, EPI_STORE>); set(gemv_stream_kernel<4, EPI_STORE>);
-    set(gemv_stream_kernel<1, EPI_RESID>); set(gemv_stream_kernel<2, EPI_RESID>); set(gemv_stream_kernel<4, EPI_RESID>);
-    set(gemv_stream_kernel<1, EPI_SWIGLU>); set(gemv_stream_kernel<2, EPI_SWIGLU>); set(gemv_stream_kernel<4, EPI_SWIGLU>);
-    set(gemv_stream_kernel<1, EPI_LOGITS>); set(gemv_stream_kernel<2, EPI_LOGITS>); set(gemv_stream_kernel<4, EPI_LOGITS>);
-    set(gemv_stream_kernel<1, EPI_QKV>); set(gemv_stream_kernel<2, EPI_QKV>); set(gemv_stream_kernel<4, EPI_QKV>);
-}
-
-void rt_gemv_stream_alloc(rt_engine* e) {
-    // experimental: measured slower than gemv_kernel in round 1 (per-tile reduce is not overlapped with one CTA per SM),
-    // so it is opt-in (RT_GEMV_STREAM=1); profiles/r1_summary.md has the numbers
-    e->use_stream = env_int("RT_GEMV_STREAM", 0) != 0;
-    rt_gemv_stream_setup();
-    void* p = nullptr;
-    RT_CUDA(cudaMalloc(&p, (size_t)e->sm_count * 16 * 32 * sizeof(float)));
-    e->allocs.push_back(p);
-    e->gs_scratch = reinterpret_cast<float*>(p);
-    RT_CUDA(cudaMalloc(&p, (size_t)e->sm_count * sizeof(int)));
-    e->allocs.push_back(p);
-    e->gs_flags = reinterpret_cast<int*>(p);
-    RT_CUDA(cudaMemsetAsync(e->gs_flags, 0, (size_t)e->sm_count * sizeof(int), e->st));
-}
-
 void rt_attn_host_setup() {
     // opt in to > 48 KB of dynamic shared memory (per device, idempotent)
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(128)));
@@ -531,25 +490,6 @@ void rt_attn3_host_launch(rt_engine* e, const Attn3Args& a, int hd, int cs) {
     if (hd == 128) attn3_launch_hd<128>(e, a, cs);
     else if (hd == 64) attn3_launch_hd<64>(e, a, cs);
     else attn3_launch_hd<32>(e, a, cs);
-}
-
-template <int HD, int NWARP>
-static void attn2_launch_t(rt_engine* e, const AttnArgs& a, int n_chunks) {
-    static_assert(ad2_smem_bytes(HD) <= 48 * 1024, "the ring fits the default dynamic shared memory limit");
-    (void)n_chunks;
-    launch_pdl(e, attn_decode2_kernel<HD, NWARP>, dim3(a.n_kv * (a.grid_nsh + a.T * a.grid_nown)), dim3(NWARP * 32), ad2_smem_bytes(HD), a);
-}
-template <int HD>
-static void attn2_launch_hd(rt_engine* e, const AttnArgs& a, int n_chunks) {
-    if (a.n_shared_tiles <= 1) attn2_launch_t<HD, 1>(e, a, n_chunks);
-    else if (a.n_shared_tiles == 2) attn2_launch_t<HD, 2>(e, a, n_chunks);
-    else attn2_launch_t<HD, 4>(e, a, n_chunks);
-}
-// version 2 of the decode attention (attn_decode2.cuh): CTA-shared page ring, one CTA per (kv head, chunk)
-void rt_attn2_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunks) {
-    if (hd == 128) attn2_launch_hd<128>(e, a, n_chunks);
-    else if (hd == 64) attn2_launch_hd<64>(e, a, n_chunks);
-    else attn2_launch_hd<32>(e, a, n_chunks);
 }
 
 void rt_attn_host_launch(rt_engine* e, const AttnArgs& a, int hd, int n_chunk_blocks) {
@@ -591,7 +531,6 @@ void engine_init(rt_engine* e) {
     RT_CUDA(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (auto& ev : e->ev) RT_CUDA(cudaEventCreate(&ev));
     rt_attn_host_setup();
-    rt_gemv_stream_alloc(e);
     if (c.tp_size > 1) e->tp = tp_init(c.tp_rank, c.tp_size, c.nccl_id);
 
     e->L = c.layers; e->H = c.hidden; e->hd = c.head_dim; e->nq = c.n_q; e->nkv = c.n_kv; e->F = c.ffn; e->vocab = c.vocab;
@@ -600,8 +539,18 @@ void engine_init(rt_engine* e) {
     e->qkv_rows = (e->nq_l + 2 * e->nkv_l) * e->hd;
     RT_REQUIRE(e->qkv_rows % 16 == 0 && (2 * e->F_l) % 16 == 0 && e->H % 16 == 0, "projection row counts must be multiples of 16");
 
-    if (c.weights_path && c.weights_path[0]) load_weights(e);
+    e->from_checkpoint = c.weights_path && c.weights_path[0];
+    RT_REQUIRE(c.n_eos >= 0 && c.n_eos <= 3, "n_eos must be 0..3");
+    if (c.n_eos > 0) {
+        e->n_eos = c.n_eos;
+        for (int i = 0; i < 3; ++i) e->eos_ids[i] = i < c.n_eos ? c.eos_ids[i] : -1;
+    } else if (e->from_checkpoint) {
+        e->n_eos = 0;                  // a checkpoint without ids in its configuration never stops early
+    }
+    if (e->from_checkpoint) load_weights(e);
     else build_weights(e);
+    e->cfg.weights_path = nullptr;     // caller-owned strings: not kept beyond creation
+    e->cfg.nccl_id = nullptr;
     build_rope_tables(e);
 
     // KV pool
@@ -645,13 +594,14 @@ void engine_init(rt_engine* e) {
     // activations: zero-filled so that the padded slots of a GEMV hold finite values
     auto zalloc_f = [&](size_t n) { float* p = dalloc<float>(e, n); RT_CUDA(cudaMemsetAsync(p, 0, n * sizeof(float), e->st)); return p; };
     auto zalloc_b = [&](size_t n) { bf16* p = dalloc<bf16>(e, n); RT_CUDA(cudaMemsetAsync(p, 0, n * sizeof(bf16), e->st)); return p; };
+    auto zalloc_h = [&](size_t n) { f16* p = dalloc<f16>(e, n); RT_CUDA(cudaMemsetAsync(p, 0, n * sizeof(f16), e->st)); return p; };
     e->x = zalloc_f((size_t)MAX_SLOTS * e->H);
     e->delta = zalloc_f((size_t)MAX_SLOTS * e->H);
     e->qkv = zalloc_f((size_t)MAX_SLOTS * e->qkv_rows);
-    e->xn = zalloc_b((size_t)MAX_SLOTS * e->H);
+    e->xn = zalloc_h((size_t)MAX_SLOTS * e->H);
     e->qb = zalloc_b((size_t)MAX_SLOTS * e->nq_l * e->hd);
-    e->attn_bf = zalloc_b((size_t)MAX_SLOTS * e->nq_l * e->hd);
-    e->act_bf = zalloc_b((size_t)MAX_SLOTS * e->F_l);
+    e->attn_bf = zalloc_h((size_t)MAX_SLOTS * e->nq_l * e->hd);
+    e->act_bf = zalloc_h((size_t)MAX_SLOTS * e->F_l);
     e->part_o = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * e->hd);
     e->part_ml = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * 2);
     e->ss_part = zalloc_f((size_t)(e->H / 16) * 32);
@@ -669,6 +619,8 @@ void engine_init(rt_engine* e) {
     if (c.tp_size > 1) {
         e->loc_best = zalloc_f(64);
         e->all_best = zalloc_f((size_t)64 * c.tp_size);
+        e->logits_full = zalloc_f((size_t)MAX_SLOTS * e->vocab);
+        e->tp_stop = zalloc_f(1);
         e->tpf_on = env_int("RT_TP_FUSED", 1) != 0 && c.tp_size <= TPF_MAX && e->H <= 4 * TPF_THREADS * TPF_CMAX && e->H % 4 == 0;
         if (e->tpf_on) {
             // separate allocations: CUDA IPC shares whole allocations
@@ -680,19 +632,6 @@ void engine_init(rt_engine* e) {
             RT_CUDA(cudaStreamSynchronize(e->st));
             for (int j = 0; j < 2; ++j) tp_ipc_exchange(e->tp, e->tpf_delta[j], e->tpf_peer_delta[j], e->st);
             tp_ipc_exchange(e->tp, e->tpf_flags, e->tpf_peer_flags, e->st);
-            // push variant (partials stored into the peers by the projection epilogue): measured SLOWER than the pull kernel
-            // (config 4: TP=2 875 vs 886 tok/s, TP=4 1,154 vs 1,217: every producer CTA pays a system-scope fence), kept opt-in
-            e->tpp_on = env_int("RT_TP_PUSH", 0) != 0;
-            if (e->tpp_on) {
-                for (int j = 0; j < 2; ++j) e->tpp_recv[j] = zalloc_f((size_t)c.tp_size * MAX_SLOTS * e->H);
-                e->tpp_cnt = dalloc<unsigned long long>(e, 2);
-                e->tpp_expect = dalloc<unsigned long long>(e, (size_t)2 * MAX_SLOTS * TPF_CMAX);
-                RT_CUDA(cudaMemsetAsync(e->tpp_cnt, 0, 2 * sizeof(unsigned long long), e->st));
-                RT_CUDA(cudaMemsetAsync(e->tpp_expect, 0, (size_t)2 * MAX_SLOTS * TPF_CMAX * sizeof(unsigned long long), e->st));
-                RT_CUDA(cudaStreamSynchronize(e->st));
-                for (int j = 0; j < 2; ++j) tp_ipc_exchange(e->tp, e->tpp_recv[j], e->tpp_peer_recv[j], e->st);
-                tp_ipc_exchange(e->tp, e->tpp_cnt, e->tpp_peer_cnt, e->st);
-            }
             // nobody may raise a flag before every rank has cleared its own: one more collective as a barrier
             tp_allreduce_sum_f32(e->tp, e->loc_best, 64, e->st);
             RT_CUDA(cudaStreamSynchronize(e->st));
@@ -704,10 +643,10 @@ void engine_init(rt_engine* e) {
     const int bt = std::max(1, 64 / e->G);
     e->pf_work_cap = (e->pf_cap / bt + 2 * e->n_seq + 2) * e->nkv_l;
     e->pf_x = zalloc_f((size_t)e->pf_cap * e->H);
-    e->pf_xn = zalloc_b((size_t)e->pf_cap * e->H);
+    e->pf_xn = zalloc_h((size_t)e->pf_cap * e->H);
     e->pf_q = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
-    e->pf_attn = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
-    e->pf_act = zalloc_b((size_t)e->pf_cap * e->F_l);
+    e->pf_attn = zalloc_h((size_t)e->pf_cap * e->nq_l * e->hd);
+    e->pf_act = zalloc_h((size_t)e->pf_cap * e->F_l);
     if (c.tp_size > 1) e->pf_delta = zalloc_f((size_t)e->pf_cap * e->H);
     e->pf_inv_rms = zalloc_f(e->pf_cap);
     e->pf_tok = dalloc<int>(e, e->pf_cap);
@@ -722,11 +661,23 @@ void engine_init(rt_engine* e) {
         pf_make_map_a(&e->map_act, e->pf_act, e->pf_cap, e->F_l);
         e->map_w.resize((size_t)4 * e->L);
         for (int l = 0; l < e->L; ++l) {
-            pf_make_map_w(&e->map_w[4 * l + 0], e->layers[l].wqkv, e->qkv_rows, e->H, PF_BN);
-            pf_make_map_w(&e->map_w[4 * l + 1], e->layers[l].wo, e->H, e->nq_l * e->hd, PF_BN);
-            pf_make_map_w(&e->map_w[4 * l + 2], e->layers[l].wgu, 2 * e->F_l, e->H, PF_BN);
-            pf_make_map_w(&e->map_w[4 * l + 3], e->layers[l].wdown, e->H, e->F_l, PF_BN);
+            // fp16 twins of the layer matrices (kernels.cuh bf16_to_f16_kernel): what the prefill GEMMs read
+            LayerW& w = e->layers[l];
+            auto twin = [&](const bf16* src, size_t n) {
+                f16* t = dalloc<f16>(e, n);
+                bf16_to_f16_kernel<<<e->sm_count * 4, 256, 0, e->st>>>(src, t, n / 8);
+                return t;
+            };
+            w.wqkv16 = twin(w.wqkv, (size_t)e->qkv_rows * e->H);
+            w.wo16 = twin(w.wo, (size_t)e->H * e->nq_l * e->hd);
+            w.wgu16 = twin(w.wgu, (size_t)2 * e->F_l * e->H);
+            w.wdown16 = twin(w.wdown, (size_t)e->H * e->F_l);
+            pf_make_map_w(&e->map_w[4 * l + 0], w.wqkv16, e->qkv_rows, e->H, PF_BN);
+            pf_make_map_w(&e->map_w[4 * l + 1], w.wo16, e->H, e->nq_l * e->hd, PF_BN);
+            pf_make_map_w(&e->map_w[4 * l + 2], w.wgu16, 2 * e->F_l, e->H, PF_BN);
+            pf_make_map_w(&e->map_w[4 * l + 3], w.wdown16, e->H, e->F_l, PF_BN);
         }
+        RT_CUDA(cudaGetLastError());
         // tcgen05 prefill attention (attn_prefill_tc5.cuh): head_dim 128, a q-head group that fits 128 rows
         // head_dim 64 also runs (RT_PFA_TC5=2) but gains nothing measurable: the kernel is softmax-paced and a 64-dim head
         // only halves its MMA work (30k-token 1B prompt: 378 vs 391 ms)
@@ -750,10 +701,6 @@ void engine_free(rt_engine* e) {
     if (e->tp && e->tpf_on) {
         for (int j = 0; j < 2; ++j) tp_ipc_close(e->tp, e->tpf_peer_delta[j]);
         tp_ipc_close(e->tp, e->tpf_peer_flags);
-        if (e->tpp_on) {
-            for (int j = 0; j < 2; ++j) tp_ipc_close(e->tp, e->tpp_peer_recv[j]);
-            tp_ipc_close(e->tp, e->tpp_peer_cnt);
-        }
     }
     tp_destroy(e->tp);
     e->tp = nullptr;
@@ -900,20 +847,7 @@ void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* p
 // Fused path: ONE kernel pulls every rank's partial over NVLink peer memory (tp_fused.cuh); otherwise NCCL + rmsnorm.
 static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, const bf16* norm_w) {
     const int H = e->H;
-    if (e->tpp_on) {
-        const int tp = e->cfg.tp_size;
-        for (int p = 0; p < tp; ++p) {
-            g.push_dst[p] = reinterpret_cast<float*>(e->tpp_peer_recv[site][p]);
-            g.push_cnt[p] = reinterpret_cast<unsigned long long*>(e->tpp_peer_cnt[p]) + site;
-        }
-        g.push_tp = tp; g.push_rank = e->cfg.tp_rank;
-        const int grid = gemv_dispatch<EPI_PUSH>(e, g);
-        TpPushArgs a{};
-        a.recv = e->tpp_recv[site]; a.cnt = e->tpp_cnt + site; a.expect = e->tpp_expect + (size_t)site * MAX_SLOTS * TPF_CMAX;
-        a.arrivals = (unsigned long long)tp * grid; a.tp = tp; a.H = H; a.T = T;
-        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.ss_part = e->ss_part;
-        launch_pdl(e, tp_push_reduce_norm_kernel, dim3(cdiv(H / 4, TPF_THREADS), MAX_SLOTS), dim3(TPF_THREADS), 0, a);
-    } else if (e->tpf_on) {
+    if (e->tpf_on) {
         g.out = e->tpf_delta[site]; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
         TpFusedArgs a{};
@@ -949,10 +883,17 @@ static void lm_head_and_sample(rt_engine* e, int T, bool sample, bool advance, b
     // top-k / top-p: the projection only stores the logits; sampler.cuh filters and draws (one CTA per slot)
     const bool filtered = sample && inv_temp > 0.f && ((top_k > 0 && top_k < e->vocab) || (top_p > 0.f && top_p < 1.f));
     if (filtered) {
-        RT_REQUIRE(!e->tp, "top_k / top_p sampling is not available with tensor parallel (vocab-parallel logits)");
         lm_head_and_sample(e, T, false, false, true, 0.f, seed, direct_scale);
         TopkpArgs k{};
         k.logits = e->logits; k.ld = e->vocab_l; k.V = e->vocab_l; k.T = T;
+        if (e->tp) {
+            // vocab-parallel shards -> full rows on every rank (one grouped all-gather); every rank then filters and draws
+            // from identical inputs with the same noise stream, so all ranks pick the same token
+            tp_allgather_rows(e->tp, e->logits, (size_t)e->vocab_l * sizeof(float), e->logits_full, (size_t)e->vocab * sizeof(float),
+                              (size_t)e->vocab_l * sizeof(float), T, e->st);
+            e->launches++;
+            k.logits = e->logits_full; k.ld = e->vocab; k.V = e->vocab;
+        }
         k.inv_temp = inv_temp; k.top_k = top_k; k.top_p = top_p; k.seed = seed; k.step_ptr = e->d_step;
         k.next_tok = e->d_next_tok; k.done_counter = e->done_counter;
         if (advance) { k.tok = e->d_tok; k.pos = e->d_pos; k.out_tokens = e->d_out_tokens; k.max_out = e->max_out; k.step_w = e->d_step; }
@@ -1036,10 +977,6 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         a.pf[0] = {w.wo, pf_wo};
         a.pf[1] = {w.wgu, pf_wgu};
         if (!(skip & 4)) {
-            // version 2 (CTA-shared page ring) is correct but measured slower in round 1 (profiles/r1_summary.md): opt-in
-            static const int attn_v2 = env_int("RT_ATTN_V2", 0);
-            a.grid_nsh = o.n_shared_tiles > 0 ? o.n_sh : 0;
-            a.grid_nown = o.n_own;
             if (o.attn3_cs > 0 && T <= 8) {
                 Attn3Args a3{};
                 a3.Q = a.Q; a3.ldq = a.ldq; a3.Kp = kp; a3.Vp = vp; a3.page_table = a.page_table; a3.pt_stride = a.pt_stride;
@@ -1047,8 +984,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
                 a3.scale_log2 = a.scale_log2; a3.out = e->attn_bf; a3.ldo = e->nq_l * hd; a3.early = a.early;
                 rt_attn3_host_launch(e, a3, hd, o.attn3_cs);
             } else {
-            if (attn_v2 && o.n_shared_tiles <= 4) rt_attn2_host_launch(e, a, hd, o.n_chunks);
-            else rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
+            rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
             MergeArgs m{};
             m.part_o = e->part_o; m.part_ml = e->part_ml; m.max_chunks = MAX_CHUNKS; m.slot_pos = e->d_pos;
             m.shared_len_ptr = e->d_shared_len; m.cascade = o.n_shared_tiles > 0; m.chunk_keys = o.chunk_pages * KV_PAGE;
@@ -1125,10 +1061,23 @@ static void plan_chunks(int max_len, int shared_len, StepOpts& o, int hd = 64) {
     }
 }
 
-static void check_deadline(double t0, uint64_t deadline_ms) {
+// Under tensor parallel the decision is COLLECTIVE: every rank contributes "my clock says stop" and all of them stop
+// if any does, at the same point of the call -- otherwise one rank would throw while its peers launch kernels that wait
+// for its partial sums (tp_fused.cuh).  Hence deadline_ms must be the same on every rank.
+static void check_deadline(rt_engine* e, double t0, uint64_t deadline_ms) {
     if (deadline_ms == 0) return;
     const double el = now_ms() - t0;
-    if (el > (double)deadline_ms)
+    bool stop = el > (double)deadline_ms;
+    if (e->tp) {
+        const float mine = stop ? 1.f : 0.f;
+        float any = 0.f;
+        RT_CUDA(cudaMemcpyAsync(e->tp_stop, &mine, sizeof(float), cudaMemcpyHostToDevice, e->st));
+        tp_allreduce_sum_f32(e->tp, e->tp_stop, 1, e->st);
+        RT_CUDA(cudaMemcpyAsync(&any, e->tp_stop, sizeof(float), cudaMemcpyDeviceToHost, e->st));
+        RT_CUDA(cudaStreamSynchronize(e->st));
+        stop = any > 0.f;
+    }
+    if (stop)
         throw RtError(RT_ERR_TIMEOUT, "generation timed out after " + std::to_string((long long)el) + " ms (deadline " +
                                           std::to_string((unsigned long long)deadline_ms) + " ms)");
 }
@@ -1155,7 +1104,7 @@ static void prefill_via_slabs(rt_engine* e, const std::vector<int>& tok, const s
                 if (want_first[s0 + i] >= 0)
                     RT_CUDA(cudaMemcpyAsync(e->d_out_tokens + (size_t)want_first[s0 + i] * e->max_out, e->d_next_tok + i,
                                             sizeof(int), cudaMemcpyDeviceToDevice, e->st));
-        check_deadline(t0, deadline_ms);
+        check_deadline(e, t0, deadline_ms);
     }
 }
 
@@ -1208,7 +1157,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             bf16* kp = e->kpool + (size_t)l * e->layer_pool_elems;
             bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
             Gemm5Args g{};
-            g.S = S; g.N = e->qkv_rows; g.K = H; g.row_scale = e->pf_inv_rms; g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t;
+            g.ab_f16 = 1; g.S = S; g.N = e->qkv_rows; g.K = H; g.row_scale = e->pf_inv_rms; g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t;
             g.tok_seq = e->pf_seq; g.tok_pos = e->pf_pos; g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq;
             g.Q = e->pf_q; g.Kp = kp; g.Vp = vp; g.n_q = e->nq_l; g.n_kv = e->nkv_l; g.hd = hd;
             pf_gemm(e->st, pdl, G5_EPI_QKV, e->map_xn, e->map_w[4 * l + 0], g);
@@ -1226,7 +1175,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             e->launches++;
 
             Gemm5Args go{};
-            go.S = S; go.N = H; go.K = e->nq_l * hd; go.ldo = H;
+            go.ab_f16 = 1; go.S = S; go.N = H; go.K = e->nq_l * hd; go.ldo = H;
             go.out = e->tp ? e->pf_delta : e->pf_x;
             pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
             if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
@@ -1234,10 +1183,10 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             e->launches += 2;
 
             Gemm5Args gu{};
-            gu.S = S; gu.N = 2 * e->F_l; gu.K = H; gu.row_scale = e->pf_inv_rms; gu.out_bf = e->pf_act; gu.ldob = e->F_l;
+            gu.ab_f16 = 1; gu.S = S; gu.N = 2 * e->F_l; gu.K = H; gu.row_scale = e->pf_inv_rms; gu.out_bf = e->pf_act; gu.ldob = e->F_l;
             pf_gemm(e->st, pdl, G5_EPI_SWIGLU, e->map_xn, e->map_w[4 * l + 2], gu);
             Gemm5Args gd{};
-            gd.S = S; gd.N = H; gd.K = e->F_l; gd.ldo = H;
+            gd.ab_f16 = 1; gd.S = S; gd.N = H; gd.K = e->F_l; gd.ldo = H;
             gd.out = e->tp ? e->pf_delta : e->pf_x;
             pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
             if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
@@ -1252,7 +1201,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             const int T = (int)rows.size();
             for (int j = 0; j < T; ++j)
             {
-                RT_CUDA(cudaMemcpyAsync(e->xn + (size_t)j * H, e->pf_xn + (size_t)rows[j] * H, (size_t)H * sizeof(bf16),
+                RT_CUDA(cudaMemcpyAsync(e->xn + (size_t)j * H, e->pf_xn + (size_t)rows[j] * H, (size_t)H * sizeof(f16),
                                         cudaMemcpyDeviceToDevice, e->st));
                 RT_CUDA(cudaMemcpyAsync(e->inv_rms + j, e->pf_inv_rms + rows[j], sizeof(float), cudaMemcpyDeviceToDevice, e->st));
             }
@@ -1278,7 +1227,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
                                             cudaMemcpyDeviceToDevice, e->st));
             }
         }
-        check_deadline(t0, deadline_ms);
+        check_deadline(e, t0, deadline_ms);
     }
 }
 
@@ -1439,6 +1388,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     plan_chunks(max_len, shared, dec, e->hd);
 
     const int n_steps = s.max_new_tokens - 1;
+    auto is_eos = [&](int t) { for (int j = 0; j < e->n_eos; ++j) if (t == e->eos_ids[j]) return true; return false; };
     const bool use_graph = !(e->cfg.flags & RT_FLAG_NO_GRAPH);
     if (use_graph && n_steps > 0) ensure_graph(e, dec);
     std::vector<int> host_out((size_t)n * s.max_new_tokens);
@@ -1471,14 +1421,14 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
         steps_done += burst;
         if (deadline_ms || !s.ignore_eos) {
             RT_CUDA(cudaStreamSynchronize(e->st));
-            check_deadline(t0, deadline_ms);
+            check_deadline(e, t0, deadline_ms);
             if (!s.ignore_eos) {
                 bool all_done = true;
                 for (int i = 0; i < n; ++i) {
                     RT_CUDA(cudaMemcpy(host_out.data() + (size_t)i * s.max_new_tokens, e->d_out_tokens + (size_t)i * e->max_out,
                                        (size_t)(steps_done + 1) * sizeof(int), cudaMemcpyDeviceToHost));
                     bool found = false;
-                    for (int k = 0; k <= steps_done && !found; ++k) found = host_out[(size_t)i * s.max_new_tokens + k] == 2;
+                    for (int k = 0; k <= steps_done && !found; ++k) found = is_eos(host_out[(size_t)i * s.max_new_tokens + k]);
                     all_done = all_done && found;
                 }
                 if (all_done) break;
@@ -1504,7 +1454,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
         n_out[i] = produced;
         if (!s.ignore_eos)
             for (int k = 0; k < produced; ++k)
-                if (host_out[(size_t)i * s.max_new_tokens + k] == 2) { n_out[i] = k; finish[i] = 1; break; }
+                if (is_eos(host_out[(size_t)i * s.max_new_tokens + k])) { n_out[i] = k; finish[i] = 1; break; }
     }
     for (int i = 0; i < n; ++i) {
         rt_result& r = outs[i];

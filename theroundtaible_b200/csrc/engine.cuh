@@ -17,6 +17,9 @@ struct LayerW {
     bf16* wo = nullptr;     // [H][nq_l*hd]
     bf16* wgu = nullptr;    // [2*F_l][H]  per 16-row tile: 8 gate rows then the 8 matching up rows
     bf16* wdown = nullptr;  // [H][F_l]
+    // fp16 twins of the four matrices (same CM layout), read by the tcgen05 prefill GEMMs: kind::f16 wants both operands
+    // in ONE 16-bit format and the activations are fp16 (common.cuh).  Every bf16 weight with |w| >= 2^-14 is exact in fp16.
+    f16 *wqkv16 = nullptr, *wo16 = nullptr, *wgu16 = nullptr, *wdown16 = nullptr;
     bf16* norm1 = nullptr;  // [H]
     bf16* norm2 = nullptr;  // [H]
 };
@@ -47,6 +50,8 @@ struct rt_engine {
     cudaStream_t st = nullptr;
     std::string err;
     long long launches = 0;
+    bool from_checkpoint = false;   // weights came from rt_config.weights_path (its vocabulary is not the byte tokenizer's)
+    int n_eos = 1, eos_ids[3] = {2, -1, -1};
 
     // global dims and this rank's shard
     int L = 0, H = 0, hd = 0, nq = 0, nkv = 0, F = 0, vocab = 0;
@@ -84,7 +89,8 @@ struct rt_engine {
 
     // activations (MAX_SLOTS rows each)
     float *x = nullptr, *qkv = nullptr, *delta = nullptr, *logits = nullptr;
-    bf16 *xn = nullptr, *qb = nullptr, *attn_bf = nullptr, *act_bf = nullptr;
+    f16 *xn = nullptr, *attn_bf = nullptr, *act_bf = nullptr;   // projection inputs: fp16 (common.cuh)
+    bf16* qb = nullptr;
     float *part_o = nullptr, *part_ml = nullptr;
     long long pf_attn_bytes = 0;   // weights pulled into L2 while a layer's attention runs (RT_PF_ATTN_MB)
     long long pf_tail_bytes = 0;   // head of the NEXT projection's weights each projection asks for at its tail (RT_PF_TAIL_MB)
@@ -93,9 +99,6 @@ struct rt_engine {
     float* pf_inv_rms = nullptr;   // [pf_cap]
     int* done_counter = nullptr;   // arrival counter of the sampler tails (lm_head, top-k/top-p)
     bool use_pdl = true;
-    bool use_stream = false;       // persistent TMA-fed stream-K projection kernel (gemv_stream.cuh)
-    float* gs_scratch = nullptr;   // [SMs][16][32] stream-K partial tiles
-    int* gs_flags = nullptr;       // [SMs]
     float* cta_max = nullptr;
     int* cta_idx = nullptr;
     int lm_ctas = 0;
@@ -104,7 +107,8 @@ struct rt_engine {
     int pf_cap = 0, pf_work_cap = 0;
     bool pf_ok = false;
     float* pf_x = nullptr;
-    bf16 *pf_xn = nullptr, *pf_q = nullptr, *pf_attn = nullptr, *pf_act = nullptr;
+    f16 *pf_xn = nullptr, *pf_attn = nullptr, *pf_act = nullptr;
+    bf16* pf_q = nullptr;
     int *pf_tok = nullptr, *pf_seq = nullptr, *pf_pos = nullptr;
     int4* pf_work = nullptr;
     int* pf_host = nullptr;        // pinned staging: tok, seq, pos (pf_cap each) + work items
@@ -117,6 +121,8 @@ struct rt_engine {
     TpComm* tp = nullptr;
     float* loc_best = nullptr;     // [64 words]: 32 local winning scores, 32 local winning ids
     float* all_best = nullptr;     // [tp][64 words]
+    float* logits_full = nullptr;  // [32][vocab]: all ranks' logits shards, gathered for top-k / top-p sampling
+    float* tp_stop = nullptr;      // [1] the ranks' collective "deadline passed" flag
     float* pf_delta = nullptr;     // [pf_cap][H] partial sums of the row-parallel prefill GEMMs
     // fused peer-memory all-reduce (tp_fused.cuh): two partial buffers (O-proj / down-proj call sites), flags, epochs
     bool tpf_on = false;
@@ -124,14 +130,6 @@ struct rt_engine {
     int *tpf_flags = nullptr, *tpf_epoch = nullptr;
     void* tpf_peer_delta[2][8] = {};
     void* tpf_peer_flags[8] = {};
-    // push variant of the exchange (tp_fused.cuh, gemv.cuh EPI_PUSH): per call site a receive buffer [tp][32][H] and an
-    // arrival counter on every rank, both mapped into every process
-    bool tpp_on = false;
-    float* tpp_recv[2] = {nullptr, nullptr};
-    unsigned long long* tpp_cnt = nullptr;             // [2]
-    unsigned long long* tpp_expect = nullptr;          // [2][32][TPF_CMAX], local only
-    void* tpp_peer_recv[2][8] = {};
-    void* tpp_peer_cnt[8] = {};
 
     // cached decode graph
     cudaGraphExec_t graph_exec = nullptr;       // one decode step

@@ -3,7 +3,7 @@
 // No reference counterpart (/root/reference/src/adapters/local-llm.ts:159 delegates generation to an external
 // server); SURVEY.md 8(a-K) row "prefill GEMM".
 //
-//   C[S][N] = A[S][K] * W[N][K]^T      A: bf16 activations, row-major, S tokens;  W: bf16 weights, CM layout
+//   C[S][N] = A[S][K] * W[N][K]^T      A: fp16 activations, row-major, S tokens;  W: fp16 twin of the bf16 weights, CM layout
 //
 // A persistent CTA (one per SM) walks 128 x BN tiles (tokens x weight rows), token blocks fastest, with two accumulators in TMEM
 // so that a tile's epilogue runs under the next tile's MMAs.  Per tile:
@@ -156,7 +156,10 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
     } else if (warp == 1) {
         if (lane == 0) {
             // instruction descriptor: D=f32 [4,6)=1, A=bf16 [7,10)=1, B=bf16 [10,13)=1, K-major both, N>>3 [17,23), M>>4 [24,29)
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(G5_BM >> 4) << 24);
+            // A/B format 0 = f16, 1 = bf16.  kind::f16 wants ONE format for both operands (an f16 A with a bf16 B raised an
+            // illegal-instruction fault on B200), so the engine multiplies fp16 activations by the fp16 twin of the weights
+            const uint32_t fmt = a.ab_f16 ? 0u : 1u;
+            const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(G5_BM >> 4) << 24);
             int it = 0, lt = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
                 const int acc = lt & 1;
@@ -228,8 +231,8 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
                         act[r] = gt / (1.0f + expf(-gt)) * up;
                     }
                     uint4 p;
-                    p.x = pack_bf16(act[0], act[1]); p.y = pack_bf16(act[2], act[3]);
-                    p.z = pack_bf16(act[4], act[5]); p.w = pack_bf16(act[6], act[7]);
+                    p.x = pack_f16(act[0], act[1]); p.y = pack_f16(act[2], act[3]);
+                    p.z = pack_f16(act[4], act[5]); p.w = pack_f16(act[6], act[7]);
                     *reinterpret_cast<uint4*>(a.out_bf + (size_t)m * a.ldob + (n0 >> 1) + t * 8) = p;
                 }
             } else {  // G5_EPI_QKV

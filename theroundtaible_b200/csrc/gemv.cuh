@@ -18,14 +18,17 @@
 // added in fixed warp order through shared memory (bit-reproducible, no atomics).  With PDL the first weight
 // loads are issued BEFORE griddepcontrol.wait, so the HBM stream keeps running across kernel boundaries.
 //
+// Activations arrive as fp16 and are split into bf16 hi + lo in registers (common.cuh split_f16x2): two MMAs per weight
+// fragment, so the product is exact in the fp16 input and the kernel stays HBM-bound.
+//
 // Fusions: EPI_QKV    -> + bias, RoPE, q -> bf16 Q buffer, k/v -> bf16 into their KV page;
-//          EPI_RESID  -> x += acc, xw = bf16(x * w_next) and per-tile partial sums of x^2: the next projection applies
+//          EPI_RESID  -> x += acc, xw = fp16(x * w_next) and per-tile partial sums of x^2: the next projection applies
 //                        the RMSNorm scale to its accumulators (no RMSNorm launch, no tail);
-//          EPI_SWIGLU -> bf16(silu(gate) * up);   EPI_LOGITS -> logits and per-CTA arg-max candidates.
+//          EPI_SWIGLU -> fp16(silu(gate) * up);   EPI_LOGITS -> logits and per-CTA arg-max candidates.
 #pragma once
 #include "common.cuh"
 
-enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4, EPI_PUSH = 5 };
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4 };
 
 constexpr int KV_PAGE = 16;
 
@@ -33,14 +36,14 @@ struct GemvArgs {
     const bf16* W;            // CM layout
     int N, K, T;
     // B operand
-    const bf16* X;            // !NORM: [>=NT*8][ldx] bf16 (rows >= T readable, finite)
+    const f16* X;             // [>=NT*8][ldx] fp16 (the activation contract, common.cuh); fed to the MMAs as bf16 hi + lo
     int ldx;
     // RMSNorm is split around the projections ("scale after the matmul"): the PRODUCER of the residual stream (RESID
     // epilogue, embed kernel) writes xw = bf16(x * norm_w) per element plus the per-16-row-tile partial sums of x^2; the
     // CONSUMER projection multiplies its accumulators by r = rsqrt(mean x^2 + eps) in the epilogue.  No kernel ever
     // waits for a whole row, so there is no RMSNorm launch and no last-CTA tail on the critical path.
     const bf16* norm_w;       // RESID: weight of the NEXT norm [N]; nullable => no xw / partial sums
-    bf16* xn_out;             // RESID: xw out [T][N]
+    f16* xn_out;              // RESID: xw out [T][N]
     float* ss_out;            // RESID: [N/16][32] partial sums of x^2 of the updated rows
     const float* ss_in;       // consumer: partial sums [n_parts_in][32] of the rows behind X (nullable)
     int n_parts_in;
@@ -51,7 +54,7 @@ struct GemvArgs {
     float* out;               // STORE: out[t*ldo+n] = acc (+bias) ; RESID: out[t*ldo+n] += acc
     int ldo;
     const float* bias;        // STORE / QKV (physical row order), nullable
-    bf16* out_bf;             // SWIGLU: [t*ldob + col]
+    f16* out_bf;              // SWIGLU: [t*ldob + col]
     int ldob;
     // LOGITS
     float* logits;
@@ -59,12 +62,6 @@ struct GemvArgs {
     float* cta_max;
     int* cta_idx;
     int row_offset;
-    // EPI_PUSH (tensor parallel, row-parallel projections): the fp32 partial sums go straight into EVERY rank's receive
-    // buffer [tp][32 slots][N] (slot `push_rank` of it) with P2P stores over NVLink, and every CTA then adds 1 to every
-    // rank's arrival counter (tp_fused.cuh: the consumer waits for tp x gridDim.x arrivals and reads LOCAL memory)
-    float* push_dst[8];
-    unsigned long long* push_cnt[8];
-    int push_tp, push_rank;
     int late_launch;          // QKV only: griddepcontrol.launch_dependents after the wait instead of at the start
     L2Prefetch pf;            // a later kernel's weights: each CTA asks for its slice once its own stream is issued
     float inv_temp;
@@ -251,14 +248,20 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 #pragma unroll
         for (int u = 0; u < U; ++u)
 #pragma unroll
-            for (int mt = 0; mt < MT; ++mt)
+            for (int nt = 0; nt < NT; ++nt) {
+                uint4 xh, xl;                      // the fp16 inputs as bf16 hi + lo
+                split_f16x2(xv[u][nt].x, xh.x, xl.x);
+                split_f16x2(xv[u][nt].y, xh.y, xl.y);
+                split_f16x2(xv[u][nt].z, xh.z, xl.z);
+                split_f16x2(xv[u][nt].w, xh.w, xl.w);
 #pragma unroll
-                for (int nt = 0; nt < NT; ++nt) {
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
-                                   xv[u][nt].x, xv[u][nt].y);
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
-                                   xv[u][nt].z, xv[u][nt].w);
+                for (int mt = 0; mt < MT; ++mt) {
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y, xh.x, xh.y);
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w, xh.z, xh.w);
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y, xl.x, xl.y);
+                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w, xl.z, xl.w);
                 }
+            }
         // next batch of weights
         if (kbb + U < kb1) {
 #pragma unroll
@@ -321,18 +324,6 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 a.out[(size_t)s * a.ldo + n] = v;
             }
         }
-    } else if (EPI == EPI_PUSH) {
-        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
-            const int r = e % (MT * 16), s = e / (MT * 16);
-            const int n = row0 + r;
-            if (s < a.T && n < a.N) {
-                const float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
-                const size_t off = ((size_t)a.push_rank * 32 + s) * a.N + n;
-#pragma unroll
-                for (int p = 0; p < 8; ++p)
-                    if (p < a.push_tp) a.push_dst[p][off] = v;
-            }
-        }
     } else if (EPI == EPI_RESID) {
         for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
             const int r = e % (MT * 16), s = e / (MT * 16);
@@ -343,7 +334,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 const float v = (first ? pre_f0 : *o) + res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
                 *o = v;
                 if (a.norm_w) {
-                    a.xn_out[(size_t)s * a.N + n] = __float2bfloat16_rn(v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])));
+                    a.xn_out[(size_t)s * a.N + n] = to_f16(v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])));
                     res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] = v;
                 }
             }
@@ -373,7 +364,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 const float gt = res[mt * NT + (s >> 3)][rr][s & 7] * s_rn[s];
                 const float up = res[mt * NT + (s >> 3)][rr + 8][s & 7] * s_rn[s];
                 const float act = gt / (1.0f + expf(-gt)) * up;
-                a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = __float2bfloat16_rn(act);
+                a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = to_f16(act);
             }
         }
     } else if (EPI == EPI_QKV) {
@@ -448,13 +439,6 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     __syncthreads();                                 // red / res are reused by the next group
     }
 
-    if (EPI == EPI_PUSH) {
-        // all of this CTA's partials are on their way: make them visible system-wide, then tell every rank
-        __threadfence_system();
-        __syncthreads();
-        if ((int)threadIdx.x < a.push_tp)
-            asm volatile("red.release.sys.global.add.u64 [%0], %1;" ::"l"(a.push_cnt[threadIdx.x]), "l"(1ull) : "memory");
-    }
     if (EPI == EPI_LOGITS) {
         if (threadIdx.x < NT * 8) {
             a.cta_max[blockIdx.x * 32 + threadIdx.x] = cand_best;

@@ -12,12 +12,12 @@
 
 // =================================================================================================
 // Embedding gather from the CM-layout table (gemv.cuh):  x[t][:] = float(E[tok[t]][:]), and the first layer's
-// RMSNorm in its split form (gemv.cuh): xw = bf16(x * w), per-16-element partial sums of x^2 (decode consumers) and
+// RMSNorm in its split form (gemv.cuh): xw = fp16(x * w), per-16-element partial sums of x^2 (decode consumers) and
 // r = rsqrt(mean x^2 + eps) (prefill / tensor-parallel consumers).  One CTA per slot, one thread per 16 elements.
 // =================================================================================================
 static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __restrict__ E, const int* __restrict__ tok,
                                                                 float* __restrict__ x, const bf16* __restrict__ norm_w,
-                                                                bf16* __restrict__ xw, float* __restrict__ ss_part,
+                                                                f16* __restrict__ xw, float* __restrict__ ss_part,
                                                                 float* __restrict__ inv_rms, int H, int vocab, float eps) {
     griddep_launch();
     griddep_wait();
@@ -42,10 +42,10 @@ static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __re
             o[0] = a;
             o[1] = b;
             uint4 p;
-            p.x = pack_bf16(a.x * bf16lo(wv.x), a.y * bf16hi(wv.x));
-            p.y = pack_bf16(a.z * bf16lo(wv.y), a.w * bf16hi(wv.y));
-            p.z = pack_bf16(b.x * bf16lo(wv.z), b.y * bf16hi(wv.z));
-            p.w = pack_bf16(b.z * bf16lo(wv.w), b.w * bf16hi(wv.w));
+            p.x = pack_f16(a.x * bf16lo(wv.x), a.y * bf16hi(wv.x));
+            p.y = pack_f16(a.z * bf16lo(wv.y), a.w * bf16hi(wv.y));
+            p.z = pack_f16(b.x * bf16lo(wv.z), b.y * bf16hi(wv.z));
+            p.w = pack_f16(b.z * bf16lo(wv.w), b.w * bf16hi(wv.w));
             *reinterpret_cast<uint4*>(xw + (size_t)t * H + k) = p;
             ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
         }
@@ -64,10 +64,22 @@ static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __re
     }
 }
 
+// fp16 twin of a bf16 weight matrix (same element order: the CM layout is kept), for the tcgen05 prefill GEMMs whose two
+// operands must share one 16-bit format (gemm_tc5.cuh).  bf16 has 8 significant bits, fp16 11: exact for |w| >= 2^-14.
+static __global__ void bf16_to_f16_kernel(const bf16* __restrict__ in, f16* __restrict__ out, size_t n8) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = reinterpret_cast<const uint4*>(in)[i];
+        uint4 o;
+        o.x = pack_f16(bf16lo(v.x), bf16hi(v.x)); o.y = pack_f16(bf16lo(v.y), bf16hi(v.y));
+        o.z = pack_f16(bf16lo(v.z), bf16hi(v.z)); o.w = pack_f16(bf16lo(v.w), bf16hi(v.w));
+        reinterpret_cast<uint4*>(out)[i] = o;
+    }
+}
+
 // Split RMSNorm for the paths that have a whole row in one place (prefill, tensor parallel): x (+= delta) stays fp32,
-// xw = bf16(x * w), inv_rms[t] = rsqrt(mean x^2 + eps).  One CTA per token.
+// xw = fp16(x * w), inv_rms[t] = rsqrt(mean x^2 + eps).  One CTA per token.
 static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ x, const float* __restrict__ delta,
-                                                            const bf16* __restrict__ w, bf16* __restrict__ xw,
+                                                            const bf16* __restrict__ w, f16* __restrict__ xw,
                                                             float* __restrict__ inv_rms, int H, float eps) {
     const int t = blockIdx.x;
     float* xr = x + (size_t)t * H;
@@ -82,8 +94,8 @@ static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ 
         }
         const uint2 wv = *reinterpret_cast<const uint2*>(w + c);
         uint2 o;
-        o.x = pack_bf16(v.x * bf16lo(wv.x), v.y * bf16hi(wv.x));
-        o.y = pack_bf16(v.z * bf16lo(wv.y), v.w * bf16hi(wv.y));
+        o.x = pack_f16(v.x * bf16lo(wv.x), v.y * bf16hi(wv.x));
+        o.y = pack_f16(v.z * bf16lo(wv.y), v.w * bf16hi(wv.y));
         *reinterpret_cast<uint2*>(xw + (size_t)t * H + c) = o;
         ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
@@ -217,8 +229,8 @@ struct AttnArgs {
     int early;                  // 1 = index setup and old KV pages before the PDL wait (needs a producer that releases
                                 // this kernel only after its own wait: the engine's QKV projection does)
     float scale_log2;           // log2(e)/sqrt(hd)
-    // version 2 (attn_decode2.cuh): exact 1-D grid = n_kv * (grid_nsh + T * grid_nown) CTAs, no empty CTAs
-    int grid_nsh, grid_nown;
+    int max_len;                // > 0: positions are clamped to max_len - 1 (callers whose positions the host cannot check:
+                                // a bad position then gives a truncated result, never a partial outside the scratch)
 };
 
 #ifndef RT_ATTN_STAGES
@@ -283,7 +295,8 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, HD == 128 ? 2 : 4) attn_decod
     if ((int)blockIdx.z < a.T) {
         const int slot = blockIdx.z;
         seq = a.slot_seq[slot];
-        const int len = a.slot_pos[slot] + 1;
+        int len = a.slot_pos[slot] + 1;
+        if (a.max_len > 0) len = min(len, a.max_len);
         key0 = sh + c * C;
         key1 = min(key0 + C, len);
         pidx = nsh_chunks + c;
@@ -308,7 +321,7 @@ __global__ void __launch_bounds__(ATTN_WARPS * 32, HD == 128 ? 2 : 4) attn_decod
             row_head[i] = h * G + (row_ok[i] ? R % G : 0);
         }
     }
-    if (key0 >= key1) return;  // warp-uniform
+    if (key0 >= key1 || pidx >= a.max_chunks) return;  // warp-uniform
 
     const uint32_t sbase = smem_u32(smem_raw) + warp * (ATTN_STAGES * STAGE_BYTES);
     const int* pt = a.page_table + (size_t)seq * a.pt_stride;
@@ -477,16 +490,18 @@ struct MergeArgs {
     const int* slot_pos;
     const int* shared_len_ptr;
     int cascade;       // n_shared_tiles > 0
+    int max_len;       // > 0: clamp of slot_pos + 1 (see AttnArgs)
     int chunk_keys;    // C
     int n_q, hd;
-    bf16* out_bf;      // nullable  [T][ldo]
+    f16* out_bf;       // nullable  [T][ldo]: fp16, the input of the O-projection
     float* out_f32;    // nullable  [T][ldo]
     int ldo;
 };
 
 static __global__ void attn_merge_kernel(const MergeArgs a) {
     const int t = blockIdx.y, head = blockIdx.x, d = threadIdx.x;
-    const int len = a.slot_pos[t] + 1;
+    int len = a.slot_pos[t] + 1;
+    if (a.max_len > 0) len = min(len, a.max_len);
     const int sh = (a.cascade && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
     const int C = a.chunk_keys;
     const int n = (sh + C - 1) / C + (len - sh + C - 1) / C;
@@ -500,7 +515,7 @@ static __global__ void attn_merge_kernel(const MergeArgs a) {
         acc += a.part_o[(base + i) * a.hd + d] * w;
     }
     const float r = acc / L;
-    if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * a.hd + d] = __float2bfloat16_rn(r);
+    if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * a.hd + d] = to_f16(r);
     if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * a.hd + d] = r;
 }
 
@@ -572,7 +587,7 @@ static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs
     if (threadIdx.x < HD) {
         const float r = (sacc[0][threadIdx.x] + sacc[1][threadIdx.x]) + (sacc[2][threadIdx.x] + sacc[3][threadIdx.x]);
         const float o = r / sL[0];
-        if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * HD + threadIdx.x] = __float2bfloat16_rn(o);
+        if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * HD + threadIdx.x] = to_f16(o);
         if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * HD + threadIdx.x] = o;
     }
     RT_TR(64);

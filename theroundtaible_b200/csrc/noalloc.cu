@@ -10,6 +10,7 @@
 // Cost: every GPU that loads this library holds RT_NOALLOC_SCRATCH_BYTES (4.25 MiB) until the process
 // exits, used or not.
 #include <cmath>
+#include <mutex>
 #include <string>
 
 #include "engine.cuh"
@@ -32,7 +33,7 @@ static __device__ __align__(256) int g_noalloc_identity[MAX_SLOTS] = {0,  1,  2,
                                                                       16, 17, 18, 19, 20, 21, 22, 23, 24, 25, 26, 27, 28, 29, 30, 31};
 
 struct DevSetup {
-    bool done = false;
+    std::once_flag once;
     float* scratch = nullptr;
     int* identity = nullptr;
 };
@@ -42,14 +43,14 @@ DevSetup g_setup[NOALLOC_MAX_DEVICES];
 // kernels of THIS translation unit in to their dynamic shared memory size.  Nothing here allocates.
 const DevSetup& setup_device(int device) {
     DevSetup& s = g_setup[device];
-    if (s.done) return s;
+    std::call_once(s.once, [&] {       // two host threads may make their first call on a device at the same time
     RT_CUDA(cudaGetSymbolAddress((void**)&s.scratch, g_noalloc_scratch));
     RT_CUDA(cudaGetSymbolAddress((void**)&s.identity, g_noalloc_identity));
     const size_t per_hd = (size_t)ATTN_WARPS * ATTN_STAGES * 2 * KV_PAGE * 2;
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per_hd * 128)));
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per_hd * 64)));
     RT_CUDA(cudaFuncSetAttribute(attn_decode_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per_hd * 32)));
-    s.done = true;
+    });
     return s;
 }
 
@@ -96,6 +97,9 @@ RT_API int rt_k_attention_noalloc(const void* q_dev, const void* kpool_dev, cons
         a.part_ml = s.scratch + NOALLOC_O_FLOATS;
         a.max_chunks = n_chunks;
         a.scale_log2 = (float)(1.4426950408889634 / std::sqrt((double)hd));
+        // the positions live on the device: the kernels clamp them to max_len, so that a position beyond what the caller
+        // declared truncates that query's context instead of writing partials past the shared scratch array
+        a.max_len = max_len;
         const dim3 grid(cdiv(n_chunks, ATTN_WARPS), n_kv, T);
         const size_t smem = (size_t)ATTN_WARPS * ATTN_STAGES * 2 * KV_PAGE * hd * 2;
         if (hd == 128) attn_decode_kernel<128><<<grid, ATTN_WARPS * 32, smem, st>>>(a);
@@ -103,7 +107,7 @@ RT_API int rt_k_attention_noalloc(const void* q_dev, const void* kpool_dev, cons
         else attn_decode_kernel<32><<<grid, ATTN_WARPS * 32, smem, st>>>(a);
         MergeArgs m{};
         m.part_o = a.part_o; m.part_ml = a.part_ml; m.max_chunks = n_chunks; m.slot_pos = query_pos_dev;
-        m.shared_len_ptr = nullptr; m.cascade = 0; m.chunk_keys = chunk; m.n_q = n_q; m.hd = hd;
+        m.shared_len_ptr = nullptr; m.cascade = 0; m.max_len = max_len; m.chunk_keys = chunk; m.n_q = n_q; m.hd = hd;
         m.out_bf = nullptr; m.out_f32 = out_dev; m.ldo = n_q * hd;
         attn_merge_kernel<<<dim3(n_q, T), hd, 0, st>>>(m);
         RT_CUDA(cudaGetLastError());

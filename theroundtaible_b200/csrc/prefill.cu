@@ -4,7 +4,6 @@
 #include <cstring>
 
 #include "attn_prefill.cuh"
-#include "attn_prefill_tc5.cuh"
 #include "attn_prefill_tc5b.cuh"
 #include "gemm_tc5.cuh"
 
@@ -147,16 +146,13 @@ void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows, int hd) 
 
 void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
                       const int* page_table, int pt_stride, const int* tok_pos, const int4* work, int n_q, int n_kv, int G, int BT,
-                      int n_pages_pool, int layer, float scale_log2, bf16* out, int hd) {
+                      int n_pages_pool, int layer, float scale_log2, f16* out, int hd) {
     if (n_items <= 0) return;
     Pf5Args a{};
     a.page_table = page_table; a.pt_stride = pt_stride; a.tok_pos = tok_pos; a.work = work; a.n_q = n_q; a.n_kv = n_kv; a.G = G; a.BT = BT;
     a.n_pages_pool = n_pages_pool; a.layer = layer; a.scale_log2 = scale_log2; a.out = out;
-    // the pipelined 64-key-tile variant (attn_prefill_tc5b.cuh) unless RT_PFA_TC5B=0 (config-3 prefill 174 vs 193 ms)
-    static const bool variant_b = !(getenv("RT_PFA_TC5B") && atoi(getenv("RT_PFA_TC5B")) == 0);
-    const size_t smem = variant_b ? p6_smem_bytes(hd) : p5_smem_bytes(hd);
-    auto kern = variant_b ? (hd == 128 ? attn_prefill_tc5b_kernel<128> : attn_prefill_tc5b_kernel<64>)
-                          : (hd == 128 ? attn_prefill_tc5_kernel<128> : attn_prefill_tc5_kernel<64>);
+    const size_t smem = p6_smem_bytes(hd);
+    auto kern = hd == 128 ? attn_prefill_tc5b_kernel<128> : attn_prefill_tc5b_kernel<64>;
     RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(n_items);

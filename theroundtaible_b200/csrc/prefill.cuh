@@ -14,12 +14,13 @@ enum { G5_EPI_QKV = 0, G5_EPI_RESID = 1, G5_EPI_SWIGLU = 2, G5_EPI_STORE = 3 };
 
 struct Gemm5Args {
     int S, N, K;
+    int ab_f16;               // 1: BOTH operands hold fp16 values (engine: fp16 activations x the fp16 twin of the weights); 0: both bf16
     const float* row_scale;   // nullable: acc *= row_scale[token] first (split RMSNorm: r = rsqrt(mean x^2 + eps))
     // RESID: out[m*ldo + n] += acc ; STORE: out[m*ldo + n] = acc
     float* out;
     int ldo;
     // SWIGLU
-    bf16* out_bf;
+    f16* out_bf;              // fp16
     int ldob;
     // QKV
     const float* bias;
@@ -45,7 +46,7 @@ struct PfAttnArgs {
     const int4* work;       // {first token (flat), n tokens, sequence, kv head}
     int n_q, n_kv;
     float scale_log2;
-    bf16* out;              // [S][n_q*hd]
+    f16* out;               // [S][n_q*hd] fp16 (the O-projection's input)
 };
 
 void pf_attention(cudaStream_t st, bool pdl, int hd, int n_items, const PfAttnArgs& a);
@@ -56,7 +57,7 @@ void pf_make_map_q3(PfTensorMap* out, const void* base, int tokens, int n_q, int
 void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows, int hd);
 void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
                       const int* page_table, int pt_stride, const int* tok_pos, const int4* work, int n_q, int n_kv, int G, int BT,
-                      int n_pages_pool, int layer, float scale_log2, bf16* out, int hd);
+                      int n_pages_pool, int layer, float scale_log2, f16* out, int hd);
 void pf_make_map_a(PfTensorMap* out, const void* base, int rows, int K);
 void pf_make_map_w(PfTensorMap* out, const void* base, int N, int K, int BN);
 void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const PfTensorMap& mw, const Gemm5Args& a);

@@ -19,6 +19,8 @@ struct Api {
     ncclResult_t_ (*CommDestroy)(ncclComm_t_) = nullptr;
     ncclResult_t_ (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t_, cudaStream_t) = nullptr;
     ncclResult_t_ (*AllGather)(const void*, void*, size_t, int, ncclComm_t_, cudaStream_t) = nullptr;
+    ncclResult_t_ (*GroupStart)() = nullptr;
+    ncclResult_t_ (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(ncclResult_t_) = nullptr;
 };
 
@@ -40,6 +42,8 @@ Api& api() {
     a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(sym("ncclCommDestroy"));
     a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(sym("ncclAllReduce"));
     a.AllGather = reinterpret_cast<decltype(a.AllGather)>(sym("ncclAllGather"));
+    a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(sym("ncclGroupStart"));
+    a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(sym("ncclGroupEnd"));
     a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
     loaded = true;
     return a;
@@ -89,6 +93,15 @@ void tp_allreduce_sum_f32(TpComm* c, float* buf, size_t count, cudaStream_t st) 
 
 void tp_allgather_bytes(TpComm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st) {
     check(api().AllGather(send, recv, bytes_per_rank, NCCL_INT8, c->comm, st), "ncclAllGather");
+}
+
+void tp_allgather_rows(TpComm* c, const void* send, size_t send_stride, void* recv, size_t recv_stride, size_t bytes_per_rank, int rows,
+                       cudaStream_t st) {
+    check(api().GroupStart(), "ncclGroupStart");
+    for (int r = 0; r < rows; ++r)
+        check(api().AllGather(static_cast<const char*>(send) + r * send_stride, static_cast<char*>(recv) + r * recv_stride, bytes_per_rank,
+                              NCCL_INT8, c->comm, st), "ncclAllGather");
+    check(api().GroupEnd(), "ncclGroupEnd");
 }
 
 int tp_rank(const TpComm* c) { return c->rank; }

@@ -10,7 +10,7 @@
 //     wait local flags[t][c][p] >= e    for all p     (ld.acquire.sys)
 //     x[t][cols] += sum_p peers[p].partial[t][cols]   (ONE float4 per thread and peer, all peers' P2P loads in flight at
 //                                                      once, summed in rank order => identical on every rank)
-//     xw[t][cols] = bf16(x * w);  ss_part[c][t] = sum of x^2 over the block     (split RMSNorm: the consuming projection
+//     xw[t][cols] = fp16(x * w);  ss_part[c][t] = sum of x^2 over the block     (split RMSNorm: the consuming projection
 //                                                      adds the blocks and scales its accumulators, gemv.cuh)
 //   Several CTAs per slot and one load per thread and peer keep the exchange at ~one NVLink round trip; the first
 //   version (one CTA per slot, a serial loop over peers and four column groups) cost tp x 4 of them.
@@ -32,7 +32,7 @@ struct TpFusedArgs {
     int rank, tp, H;
     float* x;                        // local residual stream [T][H]
     const bf16* norm_w;
-    bf16* xn;                        // local [T][H]: xw = bf16(x * w) (split RMSNorm, gemv.cuh)
+    f16* xn;                         // local [T][H]: xw = fp16(x * w) (split RMSNorm, gemv.cuh)
     float* ss_part;                  // local [gridDim.x][32]: per-column-block sums of x^2 for the consuming projection
 };
 
@@ -59,7 +59,15 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
         if ((int)threadIdx.x < a.tp) {
             __threadfence_system();
             tpf_st_release_sys(a.flags[threadIdx.x] + cell * TPF_MAX + a.rank, e);
-            while (tpf_ld_acquire_sys(a.flags[a.rank] + cell * TPF_MAX + threadIdx.x) < e) {}
+            // bounded: a peer that never arrives (a rank that died or left the step) ends this kernel with a trap -- an
+            // error on this rank's stream -- instead of a GPU that spins for ever (2^28 polls ~ a minute)
+            long long spins = 0;
+            while (tpf_ld_acquire_sys(a.flags[a.rank] + cell * TPF_MAX + threadIdx.x) < e) {
+                if (++spins > (1ll << 28)) {
+                    printf("tp_fused_allreduce_norm: rank %d still waits for rank %d at epoch %d\n", a.rank, (int)threadIdx.x, e);
+                    __trap();
+                }
+            }
         }
     }
     __syncthreads();
@@ -80,80 +88,8 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
         *(reinterpret_cast<float4*>(a.x + (size_t)t * a.H) + c4) = acc;
         ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
         uint2 o;
-        o.x = pack_bf16(acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x));
-        o.y = pack_bf16(acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y));
-        *reinterpret_cast<uint2*>(a.xn + (size_t)t * a.H + c4 * 4) = o;
-    }
-    ss = warp_sum(ss);
-    if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = ss;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float tot = 0.f;
-        for (int w = 0; w < TPF_THREADS / 32; ++w) tot += sred[w];
-        a.ss_part[c * 32 + t] = tot;
-    }
-}
-
-// ---- push variant ---------------------------------------------------------------------------------------------------------
-// The row-parallel projection (gemv.cuh EPI_PUSH) has already stored every rank's partial into THIS rank's receive buffer
-// and bumped this rank's arrival counter once per producer CTA and rank.  This kernel waits until the counter reaches the
-// running total it expects (kept on the device, so CUDA-graph replays need no host counter), then reduces LOCAL memory:
-// no P2P read round trip and no flag handshake on the critical path.  A receive buffer (one per call site) is rewritten a
-// full layer later, when every rank has passed the other site's wait -- i.e. finished reading it.
-struct TpPushArgs {
-    const float* recv;               // local [tp][32][H]
-    const unsigned long long* cnt;   // local arrival counter of this call site
-    unsigned long long* expect;      // local [32][TPF_CMAX] running totals (private to each CTA)
-    unsigned long long arrivals;     // tp x producer grid size of THIS call
-    int tp, H, T;                    // the grid always covers all 32 slots: cells of unused slots only advance `expect`,
-                                     // so that every cell's running total stays in step whatever T the calls use
-    float* x;
-    const bf16* norm_w;
-    bf16* xn;
-    float* ss_part;
-};
-
-__global__ void __launch_bounds__(TPF_THREADS) tp_push_reduce_norm_kernel(const TpPushArgs a) {
-    __shared__ float sred[TPF_THREADS / 32];
-    griddep_launch();
-    const int c = blockIdx.x, t = blockIdx.y;
-    const int cell = t * TPF_CMAX + c;
-    const int n4 = a.H >> 2;
-    const int c4 = c * TPF_THREADS + threadIdx.x;
-    // nothing below depends on the previous kernel of THIS rank except through the counter, but x and the weights do
-    uint2 wv = make_uint2(0u, 0u);
-    if (c4 < n4) wv = *reinterpret_cast<const uint2*>(a.norm_w + c4 * 4);
-    griddep_wait();
-    if (t >= a.T) {
-        if (threadIdx.x == 0) a.expect[cell] += a.arrivals;
-        return;
-    }
-    if (threadIdx.x == 0) {
-        const unsigned long long want = a.expect[cell] + a.arrivals;
-        a.expect[cell] = want;
-        unsigned long long have;
-        long long spins = 0;
-        do {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(have) : "l"(a.cnt) : "memory");
-            if (++spins > (1ll << 28)) { printf("tp_push_reduce: arrivals %llu of %llu\n", have, want); __trap(); }
-        } while (have < want);
-    }
-    __syncthreads();
-    float ss = 0.f;
-    if (c4 < n4) {
-        float4 d[TPF_MAX];
-#pragma unroll
-        for (int p = 0; p < TPF_MAX; ++p)
-            if (p < a.tp) d[p] = __ldcv(reinterpret_cast<const float4*>(a.recv + ((size_t)p * 32 + t) * a.H) + c4);
-        float4 acc = *(reinterpret_cast<const float4*>(a.x + (size_t)t * a.H) + c4);
-#pragma unroll
-        for (int p = 0; p < TPF_MAX; ++p)
-            if (p < a.tp) { acc.x += d[p].x; acc.y += d[p].y; acc.z += d[p].z; acc.w += d[p].w; }
-        *(reinterpret_cast<float4*>(a.x + (size_t)t * a.H) + c4) = acc;
-        ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
-        uint2 o;
-        o.x = pack_bf16(acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x));
-        o.y = pack_bf16(acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y));
+        o.x = pack_f16(acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x));
+        o.y = pack_f16(acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y));
         *reinterpret_cast<uint2*>(a.xn + (size_t)t * a.H + c4 * 4) = o;
     }
     ss = warp_sum(ss);

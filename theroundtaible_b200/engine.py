@@ -30,7 +30,8 @@ class RtConfig(C.Structure):
         ("rope_factor", C.c_float), ("rope_low_freq", C.c_float), ("rope_high_freq", C.c_float),
         ("rope_orig_ctx", C.c_int32), ("seed", C.c_uint64), ("weights_path", C.c_char_p), ("device", C.c_int32),
         ("tp_rank", C.c_int32), ("tp_size", C.c_int32), ("nccl_id", C.c_void_p), ("max_batch", C.c_int32),
-        ("max_ctx", C.c_int32), ("kv_pool_bytes", C.c_int64), ("flags", C.c_int32), ("reserved", C.c_int32),
+        ("max_ctx", C.c_int32), ("kv_pool_bytes", C.c_int64), ("flags", C.c_int32), ("n_eos", C.c_int32),
+        ("eos_ids", C.c_int32 * 3), ("reserved", C.c_int32),
     ]
 
 
@@ -105,7 +106,7 @@ def load_library():
     lib.rt_k_rmsnorm.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), i32, i32,
                                  C.c_float, i32]
     lib.rt_k_attention.argtypes = [C.POINTER(C.c_uint16)] * 3 + [C.POINTER(i32), C.POINTER(C.c_float)] + [i32] * 8
-    lib.rt_k_gemv_bench.argtypes = [i32, i32, i32, i32, i32, C.POINTER(C.c_double)]
+    lib.rt_k_gemv_bench.argtypes = [i32, i32, i32, i32, i32, i32, C.POINTER(C.c_double)]
     lib.rt_k_gemm_tc5.argtypes = [C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.POINTER(C.c_float), i32, i32, i32, i32]
     lib.rt_k_sample_topkp.argtypes = [C.POINTER(C.c_float), i32, i32, C.c_float, i32, C.c_float, C.c_uint64, i32,
                                       C.POINTER(i32), C.POINTER(i32), C.POINTER(C.c_float), i32]
@@ -167,6 +168,11 @@ def config_from_hf(hf) -> RtConfig:
         cfg.rope_orig_ctx = rope["original_max_position_embeddings"]
     elif rtype != "default":
         raise EngineError(-1, f"rope type '{rtype}' is not supported (default and llama3 are)")
+    eos = hf.get("eos_token_id")
+    eos = [] if eos is None else ([eos] if isinstance(eos, int) else list(eos))
+    cfg.n_eos = min(len(eos), 3)
+    for i in range(cfg.n_eos):
+        cfg.eos_ids[i] = int(eos[i])
     return cfg
 
 
@@ -377,9 +383,10 @@ def k_gemm_tc5(a_bits: np.ndarray, w_bits: np.ndarray, device: int = 0) -> np.nd
     return c
 
 
-def k_gemv_bench(N: int, K: int, T: int, iters: int = 50, device: int = 0) -> float:
+def k_gemv_bench(N: int, K: int, T: int, iters: int = 50, device: int = 0, epi: int = 0) -> float:
+    """Mean ms per launch of the decode projection kernel on a matrix re-streamed from HBM; epi 2 = SwiGLU epilogue."""
     ms = C.c_double()
-    _check(load_library().rt_k_gemv_bench(N, K, T, iters, device, C.byref(ms)))
+    _check(load_library().rt_k_gemv_bench(N, K, T, iters, epi, device, C.byref(ms)))
     return ms.value
 
 
