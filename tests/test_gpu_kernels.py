@@ -22,7 +22,7 @@ def _rand_f16(rng, shape, std=1.0):
 
 
 @pytest.mark.parametrize("N,K,T", [(16, 32, 1), (128, 256, 3), (3072, 2048, 5), (2048, 8192, 8), (1152, 896, 7),
-                                   (512, 4864, 12), (256, 2048, 16), (640, 1024, 32), (16384, 2048, 3), (9728, 896, 1)])
+                                   (512, 4864, 12), (256, 2048, 16), (640, 1024, 32), (1024, 512, 4), (16384, 2048, 3), (9728, 896, 1)])
 def test_gemv_matches_fp32_matmul(N, K, T):
     rng = np.random.default_rng(N * 7 + K + T)
     w, (x, xf) = _rand_bits(rng, (N, K), 0.05), _rand_f16(rng, (T, K))

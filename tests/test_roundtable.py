@@ -120,3 +120,53 @@ def test_shuffle_is_the_reference_fisher_yates():
     # i = 2: j = floor(0.9 * 3) = 2 (no swap); i = 1: j = floor(0.1 * 2) = 0 (swap 0 and 1)
     assert R.shuffle_in_place(["a", "b", "c"], Fixed([0.9, 0.1])) == ["b", "a", "c"]
     assert R.shuffle_in_place(["a", "b", "c"], Fixed([0.0, 0.99])) == ["c", "b", "a"]
+
+
+def test_execute_with_fallback_follows_the_reference():
+    """orchestrator.ts:45-73: primary first; on failure the knight's fallback adapter is created once, must be available,
+    is kept under __fallback_<knight>, and answers this and later turns; without one the PRIMARY error propagates."""
+    class Fake:
+        def __init__(self, reply=None, fail=None, available=True):
+            self.reply, self.fail, self.available, self.calls = reply, fail, available, 0
+
+        def execute(self, prompt, timeout_ms=None):
+            self.calls += 1
+            if self.fail:
+                raise RuntimeError(self.fail)
+            return self.reply
+
+        def is_available(self):
+            return self.available
+
+    primary = Fake(fail="usage limit reached (429)")
+    spare = Fake(reply="van de reserve")
+    made = []
+
+    def create(adapter_id, timeout_ms):
+        made.append(adapter_id)
+        return spare
+    k = R.KnightConfig("Merlin", "local-llm-a", ["x"], 0, fallback="local-llm-b")
+    adapters = {"local-llm-a": primary}
+    assert R.execute_with_fallback(primary, k, "p", 1000, adapters, create) == "van de reserve"
+    assert made == ["local-llm-b"] and adapters["__fallback_Merlin"] is spare
+    assert R.execute_with_fallback(primary, k, "p", 1000, adapters, create) == "van de reserve"
+    assert made == ["local-llm-b"] and spare.calls == 2                          # created once, reused
+    # no fallback configured / fallback unavailable / no factory: the primary error is what the caller sees
+    plain = R.KnightConfig("Kay", "local-llm-a", ["x"], 1)
+    with pytest.raises(RuntimeError, match="usage limit"):
+        R.execute_with_fallback(primary, plain, "p", 1000, {}, create)
+    k2 = R.KnightConfig("Bors", "local-llm-a", ["x"], 2, fallback="local-llm-c")
+    with pytest.raises(RuntimeError, match="usage limit"):
+        R.execute_with_fallback(primary, k2, "p", 1000, {}, lambda i, t: Fake(reply="x", available=False))
+    with pytest.raises(RuntimeError, match="usage limit"):
+        R.execute_with_fallback(primary, k2, "p", 1000, {}, None)
+    # a failing fallback raises ITS error
+    with pytest.raises(RuntimeError, match="ook stuk"):
+        R.execute_with_fallback(primary, k2, "p", 1000, {}, lambda i, t: Fake(fail="ook stuk"))
+    # and the turn loop uses it: the knight with a broken primary still speaks every round
+    ok = Fake(reply="prima")
+    knights = [R.KnightConfig("Merlin", "a", ["x"], 0, fallback="b"), R.KnightConfig("Kay", "c", ["x"], 1)]
+    res = R.run_discussion({"a": Fake(fail="kapot"), "c": ok}, knights, "onderwerp", max_rounds=2,
+                           create_adapter=lambda i, t: Fake(reply="reserve spreekt"))
+    assert [t.error for t in res.turns] == [None] * 4
+    assert [e.response for e in res.all_rounds if e.knight == "Merlin"] == ["reserve spreekt"] * 2

@@ -57,7 +57,7 @@ __device__ __forceinline__ uint32_t pack_f16(float a, float b) {
 __device__ __forceinline__ f16 to_f16(float a) { return __float2half_rn(sat_f16(a)); }
 // The decode kernels multiply with mma.sync, whose operands must share one 16-bit format, and the weights are bf16:
 // an fp16 value (11 significant bits) is fed as bf16 hi (8 bits, RNE) + bf16 lo (the remainder: <= 3 significant bits,
-// exact), two MMAs on the same weight fragment -- free under an HBM-bound stream.  `w` holds two fp16 values.
+// exact), so the product with a bf16 weight is exact in the fp16 input.  `w` holds two fp16 values.
 __device__ __forceinline__ void split_f16x2(uint32_t w, uint32_t& hi, uint32_t& lo) {
     const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
     hi = pack_bf16(f.x, f.y);

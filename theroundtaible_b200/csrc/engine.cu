@@ -382,7 +382,9 @@ void launch_pdl(rt_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 
 template <int EPI, int NT, int MT, int NW>
 void gemv_launch(rt_engine* e, const GemvArgs& a, int grid) {
-    launch_pdl(e, gemv_kernel<NT, MT, EPI, NW>, dim3(grid), dim3(NW * 32), 0, a);
+    // <= 4 slots: the hi and lo parts of the activations share one MMA (gemv.cuh HM)
+    if (NT == 1 && a.T <= 4) launch_pdl(e, gemv_kernel<1, MT, EPI, NW, 1>, dim3(grid), dim3(NW * 32), 0, a);
+    else launch_pdl(e, gemv_kernel<NT, MT, EPI, NW, 0>, dim3(grid), dim3(NW * 32), 0, a);
 }
 
 int env_int(const char* name, int dflt) {
@@ -1199,12 +1201,11 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
         // next tokens (or all logits) through the decode lm_head kernel, <= 32 rows at a time
         auto lm_head_rows = [&](const std::vector<int>& rows, bool sample, bool store) {
             const int T = (int)rows.size();
-            for (int j = 0; j < T; ++j)
-            {
-                RT_CUDA(cudaMemcpyAsync(e->xn + (size_t)j * H, e->pf_xn + (size_t)rows[j] * H, (size_t)H * sizeof(f16),
-                                        cudaMemcpyDeviceToDevice, e->st));
-                RT_CUDA(cudaMemcpyAsync(e->inv_rms + j, e->pf_inv_rms + rows[j], sizeof(float), cudaMemcpyDeviceToDevice, e->st));
-            }
+            GatherRowsArgs ga{};
+            ga.src = e->pf_xn; ga.src_r = e->pf_inv_rms; ga.dst = e->xn; ga.dst_r = e->inv_rms; ga.H = H;
+            for (int j = 0; j < T; ++j) ga.rows[j] = rows[j];
+            gather_rows_kernel<<<T, 256, 0, e->st>>>(ga);
+            e->launches++;
             lm_head_and_sample(e, T, sample, false, store, base.inv_temp, base.seed, true, base.top_k, base.top_p);
         };
         if (logits_out) {

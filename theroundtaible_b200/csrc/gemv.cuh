@@ -18,8 +18,12 @@
 // added in fixed warp order through shared memory (bit-reproducible, no atomics).  With PDL the first weight
 // loads are issued BEFORE griddepcontrol.wait, so the HBM stream keeps running across kernel boundaries.
 //
-// Activations arrive as fp16 and are split into bf16 hi + lo in registers (common.cuh split_f16x2): two MMAs per weight
-// fragment, so the product is exact in the fp16 input and the kernel stays HBM-bound.
+// Activations are fp16 (common.cuh): a lane splits the 8 values it loads into bf16 hi + lo in registers (split_f16x2) and
+// feeds both to the MMAs, so the product is exact in the fp16 input.  Measured alternatives (profiles/r2_summary.md): hi / lo
+// written by the producer as two planes cost a second activation load per k-block -- the activation rows are read by EVERY
+// CTA from the same few L2 lines and that path, not the ALU, is the scarce one (+18 % per kernel against +6 % here).
+// With T <= 4 slots (template HM) hi and lo share ONE MMA: columns 0..3 carry hi of slots 0..3, columns 4..7 their lo,
+// and the epilogue adds the two columns of a slot.
 //
 // Fusions: EPI_QKV    -> + bias, RoPE, q -> bf16 Q buffer, k/v -> bf16 into their KV page;
 //          EPI_RESID  -> x += acc, xw = fp16(x * w_next) and per-tile partial sums of x^2: the next projection applies
@@ -36,14 +40,14 @@ struct GemvArgs {
     const bf16* W;            // CM layout
     int N, K, T;
     // B operand
-    const f16* X;             // [>=NT*8][ldx] fp16 (the activation contract, common.cuh); fed to the MMAs as bf16 hi + lo
+    const f16* X;             // activations [rows][ldx] fp16 (the activation contract, common.cuh)
     int ldx;
     // RMSNorm is split around the projections ("scale after the matmul"): the PRODUCER of the residual stream (RESID
     // epilogue, embed kernel) writes xw = bf16(x * norm_w) per element plus the per-16-row-tile partial sums of x^2; the
     // CONSUMER projection multiplies its accumulators by r = rsqrt(mean x^2 + eps) in the epilogue.  No kernel ever
     // waits for a whole row, so there is no RMSNorm launch and no last-CTA tail on the critical path.
     const bf16* norm_w;       // RESID: weight of the NEXT norm [N]; nullable => no xw / partial sums
-    f16* xn_out;              // RESID: xw out [T][N]
+    f16* xn_out;              // RESID: xw out [T][N] fp16
     float* ss_out;            // RESID: [N/16][32] partial sums of x^2 of the updated rows
     const float* ss_in;       // consumer: partial sums [n_parts_in][32] of the rows behind X (nullable)
     int n_parts_in;
@@ -54,7 +58,7 @@ struct GemvArgs {
     float* out;               // STORE: out[t*ldo+n] = acc (+bias) ; RESID: out[t*ldo+n] += acc
     int ldo;
     const float* bias;        // STORE / QKV (physical row order), nullable
-    f16* out_bf;              // SWIGLU: [t*ldob + col]
+    f16* out_bf;              // SWIGLU: [t*ldob + col] fp16
     int ldob;
     // LOGITS
     float* logits;
@@ -103,14 +107,19 @@ __device__ __forceinline__ float gumbel_noise(unsigned long long seed, int step,
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;"); }
 
-template <int NT, int MT, int EPI, int NW>
+template <int NT, int MT, int EPI, int NW, int HM = 0>
 __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
+    static_assert(HM == 0 || NT == 1, "the shared-MMA mode serves <= 4 slots");
     static_assert(NT * MT <= 4, "shared-memory reduction sized for NT*MT <= 4");
+    // NT = groups of 8 B-operand columns (slots).  HM: one group whose columns 0..3 are the hi part of slots 0..3 and
+    // columns 4..7 their lo part.
+    constexpr int SL = HM ? 4 : NT * 8;               // slots this instantiation serves
+    // k-blocks of weights a warp keeps in flight (registers): W takes 8*U*MT registers, X 4*U*NT
     constexpr int U = (MT * NT >= 4) ? 2 : (MT * NT == 2 ? 4 : 8);
     constexpr int NTHR = NW * 32;
     __shared__ float4 red[NW][MT * NT][32];
     __shared__ float res[MT * NT][16][8];
-    __shared__ float s_rn[NT * 8];
+    __shared__ float s_rn[SL];
     __shared__ int s_last;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
@@ -164,7 +173,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 
     // RMSNorm scale of every slot (used in the epilogue only: these loads overlap the weight stream)
     if (a.ss_in || a.inv_rms) {
-        for (int s = warp; s < NT * 8; s += NW) {
+        for (int s = warp; s < SL; s += NW) {
             float v = 0.f;
             if (s < a.T) {
                 if (a.inv_rms) {
@@ -176,9 +185,14 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             v = warp_sum(v);
             if (lane == 0) s_rn[s] = s >= a.T ? 0.f : (a.inv_rms ? v : 1.0f / sqrtf(v / (float)a.K + a.eps));
         }
-    } else if (threadIdx.x < NT * 8) {
+    } else if (threadIdx.x < SL) {
         s_rn[threadIdx.x] = 1.0f;
     }
+    // value of (row tile mt, row r, slot s) after the reduction: hi column + lo column
+    auto val = [&](int mt, int r, int s) -> float {
+        if (HM) return res[mt][r][s] + res[mt][r][s + 4];
+        return res[mt * NT + (s >> 3)][r][s & 7];
+    };
 
     // LOGITS: arg-max candidate of this CTA over all its row groups (threads < NT*8)
     float cand_best = -INFINITY;
@@ -199,7 +213,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     if (EPI == EPI_RESID) {
         const int e = threadIdx.x;
         const int r = e % (MT * 16), sl = e / (MT * 16), n = row0 + r;
-        if (e < MT * 16 * NT * 8 && sl < a.T && n < a.N) {
+        if (e < MT * 16 * SL && sl < a.T && n < a.N) {
             pre_f0 = a.out[(size_t)sl * a.ldo + n];
             if (a.norm_w) pre_f1 = __bfloat162float(a.norm_w[n]);
         }
@@ -207,7 +221,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         const int e = threadIdx.x;
         const int r = e % (MT * 8), sl = e / (MT * 8);
         const int mt = r >> 3, rr = r & 7, n = row0 + mt * 16;
-        if (e < MT * 8 * NT * 8 && sl < a.T && n < a.N) {
+        if (e < MT * 8 * SL && sl < a.T && n < a.N) {
             const int half = a.hd >> 1;
             if (a.bias) { pre_f2 = a.bias[n + rr]; pre_f3 = a.bias[n + rr + 8]; }
             const int head = n / a.hd;
@@ -235,7 +249,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             const int ko = (kb << 5) + q * 8;
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
-                const int slot = nt * 8 + g;
+                const int slot = HM ? (g & 3) : nt * 8 + g;
                 // rows of unused slots are never fetched: every CTA reads the SAME activation rows, which makes the few
                 // L2 slices holding them the hot spot of a short kernel (measured: scripts/probes/gridbar.cu mode 2)
                 if (kb < kb1 && slot < a.T) {
@@ -254,12 +268,15 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 split_f16x2(xv[u][nt].y, xh.y, xl.y);
                 split_f16x2(xv[u][nt].z, xh.z, xl.z);
                 split_f16x2(xv[u][nt].w, xh.w, xl.w);
+                if (HM && g >= 4) xh = xl;         // columns 4..7 carry the lo part of slots 0..3
 #pragma unroll
                 for (int mt = 0; mt < MT; ++mt) {
                     mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y, xh.x, xh.y);
                     mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w, xh.z, xh.w);
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y, xl.x, xl.y);
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w, xl.z, xl.w);
+                    if (!HM) {
+                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y, xl.x, xl.y);
+                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w, xl.z, xl.w);
+                    }
                 }
             }
         // next batch of weights
@@ -315,39 +332,41 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     RT_TR(EPI * 10 + 3);
 
     if (EPI == EPI_STORE) {
-        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
+        for (int e = threadIdx.x; e < MT * 16 * SL; e += NTHR) {
             const int r = e % (MT * 16), s = e / (MT * 16);
             const int n = row0 + r;
             if (s < a.T && n < a.N) {
-                float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] * s_rn[s];
+                float v = val(r >> 4, r & 15, s) * s_rn[s];
                 if (a.bias) v += a.bias[n];
                 a.out[(size_t)s * a.ldo + n] = v;
             }
         }
     } else if (EPI == EPI_RESID) {
-        for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
+        for (int e = threadIdx.x; e < MT * 16 * SL; e += NTHR) {
             const int r = e % (MT * 16), s = e / (MT * 16);
             const int n = row0 + r;
             if (s < a.T && n < a.N) {
                 float* o = a.out + (size_t)s * a.ldo + n;
                 const bool first = e == (int)threadIdx.x;
-                const float v = (first ? pre_f0 : *o) + res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7];
+                const float v = (first ? pre_f0 : *o) + val(r >> 4, r & 15, s);
                 *o = v;
                 if (a.norm_w) {
                     a.xn_out[(size_t)s * a.N + n] = to_f16(v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])));
-                    res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] = v;
+                    // the updated residual goes back (HM: into the hi column, lo column zero) for the sums of squares below
+                    if (HM) { res[r >> 4][r & 15][s] = v; res[r >> 4][r & 15][s + 4] = 0.f; }
+                    else res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] = v;
                 }
             }
         }
         if (a.norm_w) {
             __syncthreads();
-            for (int e = threadIdx.x; e < MT * NT * 8; e += NTHR) {
-                const int mt = e / (NT * 8), s = e % (NT * 8);
+            for (int e = threadIdx.x; e < MT * SL; e += NTHR) {
+                const int mt = e / SL, s = e % SL;
                 if (s < a.T && (tile0 + mt) * 16 < a.N) {
                     float ss = 0.f;
 #pragma unroll
                     for (int r = 0; r < 16; ++r) {
-                        const float v = res[mt * NT + (s >> 3)][r][s & 7];
+                        const float v = val(mt, r, s);
                         ss += v * v;
                     }
                     a.ss_out[(size_t)(tile0 + mt) * 32 + s] = ss;
@@ -356,13 +375,13 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         }
     } else if (EPI == EPI_SWIGLU) {
         // rows 0..7 of every 16-row tile are gate_{8j+r}, rows 8..15 are up_{8j+r}
-        for (int e = threadIdx.x; e < MT * 8 * NT * 8; e += NTHR) {
+        for (int e = threadIdx.x; e < MT * 8 * SL; e += NTHR) {
             const int r = e % (MT * 8), s = e / (MT * 8);
             const int mt = r >> 3, rr = r & 7;
             const int n = row0 + mt * 16;
             if (s < a.T && n < a.N) {
-                const float gt = res[mt * NT + (s >> 3)][rr][s & 7] * s_rn[s];
-                const float up = res[mt * NT + (s >> 3)][rr + 8][s & 7] * s_rn[s];
+                const float gt = val(mt, rr, s) * s_rn[s];
+                const float up = val(mt, rr + 8, s) * s_rn[s];
                 const float act = gt / (1.0f + expf(-gt)) * up;
                 a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = to_f16(act);
             }
@@ -371,13 +390,13 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         // tile j of a head holds dims [8j, 8j+8) in rows 0..7 and dims [hd/2+8j, hd/2+8j+8) in rows 8..15:
         // a rotate_half pair (d, d+hd/2) sits in rows (r, r+8) of one tile.
         const int half = a.hd >> 1;
-        for (int e = threadIdx.x; e < MT * 8 * NT * 8; e += NTHR) {
+        for (int e = threadIdx.x; e < MT * 8 * SL; e += NTHR) {
             const int r = e % (MT * 8), s = e / (MT * 8);
             const int mt = r >> 3, rr = r & 7;
             const int n = row0 + mt * 16;
             if (s < a.T && n < a.N) {
-                float x1 = res[mt * NT + (s >> 3)][rr][s & 7] * s_rn[s];
-                float x2 = res[mt * NT + (s >> 3)][rr + 8][s & 7] * s_rn[s];
+                float x1 = val(mt, rr, s) * s_rn[s];
+                float x2 = val(mt, rr + 8, s) * s_rn[s];
                 if (e == (int)threadIdx.x) {          // inputs fetched before the weight stream (see above)
                     x1 += pre_f2;
                     x2 += pre_f3;
@@ -413,20 +432,20 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         }
     } else {  // EPI_LOGITS
         if (a.logits) {
-            for (int e = threadIdx.x; e < MT * 16 * NT * 8; e += NTHR) {
+            for (int e = threadIdx.x; e < MT * 16 * SL; e += NTHR) {
                 const int r = e % (MT * 16), s = e / (MT * 16);
                 const int n = row0 + r;
-                if (s < a.T && n < a.N) a.logits[(size_t)s * a.ld_logits + n] = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] * s_rn[s];
+                if (s < a.T && n < a.N) a.logits[(size_t)s * a.ld_logits + n] = val(r >> 4, r & 15, s) * s_rn[s];
             }
         }
-        if (threadIdx.x < NT * 8) {
+        if (threadIdx.x < SL) {
             const int s = threadIdx.x;
             if (s < a.T) {
                 const int step = (a.inv_temp > 0.f && a.step_ptr) ? *a.step_ptr : 0;
                 for (int r = 0; r < MT * 16; ++r) {
                     const int n = row0 + r;
                     if (n >= a.N) break;
-                    float v = res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] * s_rn[s];
+                    float v = val(r >> 4, r & 15, s) * s_rn[s];
                     if (a.inv_temp > 0.f) v = v * a.inv_temp + gumbel_noise(a.seed, step, s, a.row_offset + n);
                     if (v > cand_best) { cand_best = v; cand_idx = a.row_offset + n; }      // rows ascend: lowest index wins ties
                 }
@@ -440,7 +459,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     }
 
     if (EPI == EPI_LOGITS) {
-        if (threadIdx.x < NT * 8) {
+        if (threadIdx.x < SL) {
             a.cta_max[blockIdx.x * 32 + threadIdx.x] = cand_best;
             a.cta_idx[blockIdx.x * 32 + threadIdx.x] = cand_idx;
         }

@@ -10,6 +10,30 @@
 #include "common.cuh"
 #include "gemv.cuh"
 
+// a projection input leaves its producer as fp16 (common.cuh)
+__device__ __forceinline__ void store_act4(f16* base, size_t idx, const float (&y)[4]) {
+    uint2 o;
+    o.x = pack_f16(y[0], y[1]); o.y = pack_f16(y[2], y[3]);
+    *reinterpret_cast<uint2*>(base + idx) = o;
+}
+// Rows of a prefill activation buffer -> slots of the decode buffer, with their RMSNorm scale: how the last prompt tokens
+// reach the decode lm_head kernel.  One CTA per row.
+struct GatherRowsArgs {
+    const f16* src;        // [S][H]
+    const float* src_r;    // [S]
+    f16* dst;              // [32][H]
+    float* dst_r;          // [32]
+    int H;
+    int rows[32];
+};
+static __global__ void __launch_bounds__(256) gather_rows_kernel(const GatherRowsArgs a) {
+    const int t = blockIdx.x, r = a.rows[t];
+    for (int c = threadIdx.x * 4; c < a.H; c += blockDim.x * 4) {
+        *reinterpret_cast<uint2*>(a.dst + (size_t)t * a.H + c) = *reinterpret_cast<const uint2*>(a.src + (size_t)r * a.H + c);
+    }
+    if (threadIdx.x == 0) a.dst_r[t] = a.src_r[r];
+}
+
 // =================================================================================================
 // Embedding gather from the CM-layout table (gemv.cuh):  x[t][:] = float(E[tok[t]][:]), and the first layer's
 // RMSNorm in its split form (gemv.cuh): xw = fp16(x * w), per-16-element partial sums of x^2 (decode consumers) and
@@ -41,12 +65,10 @@ static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __re
             float4* o = reinterpret_cast<float4*>(x + (size_t)t * H + k);
             o[0] = a;
             o[1] = b;
-            uint4 p;
-            p.x = pack_f16(a.x * bf16lo(wv.x), a.y * bf16hi(wv.x));
-            p.y = pack_f16(a.z * bf16lo(wv.y), a.w * bf16hi(wv.y));
-            p.z = pack_f16(b.x * bf16lo(wv.z), b.y * bf16hi(wv.z));
-            p.w = pack_f16(b.z * bf16lo(wv.w), b.w * bf16hi(wv.w));
-            *reinterpret_cast<uint4*>(xw + (size_t)t * H + k) = p;
+            const float y0[4] = {a.x * bf16lo(wv.x), a.y * bf16hi(wv.x), a.z * bf16lo(wv.y), a.w * bf16hi(wv.y)};
+            const float y1[4] = {b.x * bf16lo(wv.z), b.y * bf16hi(wv.z), b.z * bf16lo(wv.w), b.w * bf16hi(wv.w)};
+            store_act4(xw, (size_t)t * H + k, y0);
+            store_act4(xw, (size_t)t * H + k + 4, y1);
             ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
         }
         if (ss_part) ss_part[part * 32 + (t & 31)] = ss;
@@ -93,10 +115,8 @@ static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ 
             *reinterpret_cast<float4*>(xr + c) = v;
         }
         const uint2 wv = *reinterpret_cast<const uint2*>(w + c);
-        uint2 o;
-        o.x = pack_f16(v.x * bf16lo(wv.x), v.y * bf16hi(wv.x));
-        o.y = pack_f16(v.z * bf16lo(wv.y), v.w * bf16hi(wv.y));
-        *reinterpret_cast<uint2*>(xw + (size_t)t * H + c) = o;
+        const float y[4] = {v.x * bf16lo(wv.x), v.y * bf16hi(wv.x), v.z * bf16lo(wv.y), v.w * bf16hi(wv.y)};
+        store_act4(xw, (size_t)t * H + c, y);
         ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
     __shared__ float red[8];

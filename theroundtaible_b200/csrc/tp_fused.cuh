@@ -19,7 +19,7 @@
 // later; by then every peer has passed the next all-reduce's wait, i.e. finished reading it -- no trailing barrier.
 // Each rank runs this kernel on its own GPU (never two ranks on one device).
 #pragma once
-#include "gemv.cuh"
+#include "kernels.cuh"
 
 constexpr int TPF_MAX = 8;
 constexpr int TPF_CMAX = 16;         // column blocks per slot (H <= 4 * TPF_THREADS * TPF_CMAX)
@@ -32,7 +32,7 @@ struct TpFusedArgs {
     int rank, tp, H;
     float* x;                        // local residual stream [T][H]
     const bf16* norm_w;
-    f16* xn;                         // local [T][H]: xw = fp16(x * w) (split RMSNorm, gemv.cuh)
+    f16* xn;                         // local [32][H]: xw = fp16(x * w) (split RMSNorm, gemv.cuh)
     float* ss_part;                  // local [gridDim.x][32]: per-column-block sums of x^2 for the consuming projection
 };
 
@@ -87,10 +87,8 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
             if (p < a.tp) { acc.x += d[p].x; acc.y += d[p].y; acc.z += d[p].z; acc.w += d[p].w; }
         *(reinterpret_cast<float4*>(a.x + (size_t)t * a.H) + c4) = acc;
         ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
-        uint2 o;
-        o.x = pack_f16(acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x));
-        o.y = pack_f16(acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y));
-        *reinterpret_cast<uint2*>(a.xn + (size_t)t * a.H + c4 * 4) = o;
+        const float y[4] = {acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x), acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y)};
+        store_act4(a.xn, (size_t)t * a.H + c4 * 4, y);
     }
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = ss;

@@ -9,6 +9,7 @@ Follows (behaviour, not code):
   * /root/reference/src/utils/prompt.ts:82-105   nine ``String.replace(string, string)`` calls in a fixed order --
                                                  FIRST occurrence only, ``$`` patterns of the replacement interpreted
   * /root/reference/src/orchestrator.ts:33-39    Fisher-Yates shuffle for the speaking order of later rounds
+  * /root/reference/src/orchestrator.ts:45-73    executeWithFallback: primary adapter, then the knight's ``fallback``
   * /root/reference/src/orchestrator.ts:347-456  round loop, prompt join (empty parts dropped), entry appended
   * /root/reference/src/orchestrator.ts:521-535  a failing knight is reported and skipped; the round goes on
   * /root/reference/src/consensus.ts:218-224     consensus = every latest block scores >= threshold
@@ -231,17 +232,43 @@ class DiscussionResult:
     rounds_run: int
 
 
+def execute_with_fallback(primary, knight: KnightConfig, prompt: str, timeout_ms: int, adapters: dict,
+                          create_adapter: Optional[Callable] = None, on_fallback: Optional[Callable] = None) -> str:
+    """orchestrator.ts:45-73: run the prompt on the primary adapter; if that raises and the knight names a ``fallback``
+    adapter id, build it once (``create_adapter(id, timeout_ms)``; kept under ``__fallback_<knight>`` in the SAME adapter
+    map, so later turns reuse it), require ``is_available()``, and run the prompt there.  Without a usable fallback the
+    PRIMARY error is what propagates; a failure of the fallback itself propagates as its own error."""
+    try:
+        return primary.execute(prompt, timeout_ms)
+    except Exception as primary_error:  # noqa: BLE001
+        if not knight.fallback:
+            raise
+        key = f"__fallback_{knight.name}"
+        fallback = adapters.get(key)
+        if fallback is None and create_adapter is not None:
+            created = create_adapter(knight.fallback, timeout_ms)
+            if created is not None and created.is_available():
+                adapters[key] = created
+                fallback = created
+        if fallback is None:
+            raise primary_error
+        if on_fallback:
+            on_fallback(knight, primary_error)
+        return fallback.execute(prompt, timeout_ms)
+
+
 def run_discussion(adapters: dict, knights, topic: str, *, max_rounds: int = 5, consensus_threshold: float = 9,
                    timeout_per_turn_seconds: int = 120, chronicle: str = "", context: Optional[dict] = None,
                    template: Optional[str] = None, personalities: Optional[dict] = None,
                    rng: Optional[random.Random] = None,
                    parse_consensus: Callable = parse_consensus_minimal,
-                   on_turn: Optional[Callable] = None) -> DiscussionResult:
+                   on_turn: Optional[Callable] = None, create_adapter: Optional[Callable] = None) -> DiscussionResult:
     """orchestrator.ts:347-456 + 521-560: ``max_rounds`` rounds; round 1 in priority order, later rounds shuffled;
     every knight's prompt is built from ALL entries so far (including this round's earlier speakers); a knight whose
     adapter is missing is skipped, one whose ``execute`` raises is reported (classified) and skipped; after each round
     the latest blocks are checked for consensus.  ``adapters`` maps ``knight.adapter`` ids to adapter objects (knights
-    sharing an id share an instance, adapters.ts:84)."""
+    sharing an id share an instance, adapters.ts:84).  ``create_adapter(adapter_id, timeout_ms)`` builds a knight's runtime
+    fallback adapter on first need (``execute_with_fallback``)."""
     rng = rng or random.Random(0)
     ordered = sorted(knights, key=lambda k: k.priority)                          # orchestrator.ts:325-327 (stable)
     all_rounds, turns, latest = [], [], {}
@@ -258,7 +285,8 @@ def run_discussion(adapters: dict, knights, topic: str, *, max_rounds: int = 5, 
             prompt = build_full_prompt(system_prompt, topic, context)
             t0 = time.perf_counter()
             try:
-                response = adapter.execute(prompt, timeout_per_turn_seconds * 1000)
+                response = execute_with_fallback(adapter, knight, prompt, timeout_per_turn_seconds * 1000, adapters,
+                                                 create_adapter)
             except Exception as ex:  # noqa: BLE001 - orchestrator.ts:521-535 reports and carries on
                 err = ex if isinstance(ex, AdapterError) else classify_error(ex, knight.name)
                 turns.append(TurnStats(knight.name, round_no, len(prompt), (time.perf_counter() - t0) * 1e3,
