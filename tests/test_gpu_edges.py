@@ -100,3 +100,29 @@ def test_eos_ids_come_from_the_configuration():
         g = eng.generate_ids([prompt], max_new_tokens=12, ignore_eos=False)[0]
         assert g.tokens == free[:stop_at] and g.finish_reason == 1
         assert eng.generate_ids([prompt], max_new_tokens=12, ignore_eos=True)[0].tokens == free
+
+
+@pytest.mark.parametrize("name,knights,shared,own", [("tiny-llama-hd128", 3, 4300, 30), ("tiny-qwen-hd128", 2, 4200, 17),
+                                                      ("tiny-qwen-hd128", 1, 0, 4500), ("llama-3.2-1b@L2", 5, 4150, 40)])
+def test_tcgen05_decode_attention_long_contexts(name, knights, shared, own, monkeypatch):
+    """Contexts beyond the cluster kernel's 4,096 tokens take the tcgen05 decode attention (attn_decode_tc5.cuh): query rows
+    = (slot, q-head) pairs in TMEM, one CTA per key range, shared-prefix ranges serving every knight at once (G = 4 and
+    G = 5 groups, head_dim 128 and 64, with and without a shared prefix).  Must match the oracle under the margin rule and
+    the mma.sync split-KV kernel it replaces (RT_DEC5=0) up to near-ties."""
+    base = name.split("@")[0]
+    a = ARCHS[base].with_layers(2) if "@L2" in name else ARCHS[base]
+    rng = np.random.default_rng(shared + own)
+    common = rng.integers(0, a.vocab, shared).tolist()
+    prompts = [common + rng.integers(0, a.vocab, own + 3 * i).tolist() for i in range(knights)]
+    ctx = shared + own + 64
+    with E.Engine(name, seed=5, max_batch=knights, max_ctx=ctx) as eng:
+        new = eng.generate_ids(prompts, max_new_tokens=10)
+    monkeypatch.setenv("RT_DEC5", "0")
+    with E.Engine(name, seed=5, max_batch=knights, max_ctx=ctx) as eng:
+        old = eng.generate_ids(prompts, max_new_tokens=10)
+    oracle = OracleModel(a, 5, max_pos=ctx)
+    bound = REL_TOL * 2.5
+    for p, g, o in zip(prompts, new, old):
+        _greedy_compare(g.tokens, oracle, p, 10, err_bound=bound)
+        _greedy_compare(o.tokens, oracle, p, 10, err_bound=bound)
+    assert sum(g.tokens == o.tokens for g, o in zip(new, old)) >= (knights + 1) // 2

@@ -31,17 +31,23 @@ def _fingerprint() -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """``trace``: the profiling variant librt_engine_trace.so (-DRT_TRACE: every kernel records globaltimer stamps, see
+    scripts/trace_timeline.py); load it with RT_LIB=<path>.  The product library is never built with it."""
     os.makedirs(LIB_DIR, exist_ok=True)
-    stamp = os.path.join(LIB_DIR, "librt_engine.stamp")
+    tag = "_trace" if trace else ("_" + os.environ["RT_BUILD_TAG"] if os.environ.get("RT_BUILD_TAG") else "")   # experiments: RT_BUILD_TAG + RT_NVCC_EXTRA
+    LIB = os.path.join(LIB_DIR, f"librt_engine{tag}.so")
+    stamp = os.path.join(LIB_DIR, f"librt_engine{tag}.stamp")
     fp = _fingerprint()
     if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read().strip() == fp:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     extra = os.environ.get("RT_NVCC_EXTRA", "").split()      # experiments only (e.g. -DRT_ATTN_STAGES=3)
+    if trace:
+        extra.append("-DRT_TRACE")
     # one nvcc per translation unit, in parallel, then one link
     from concurrent.futures import ThreadPoolExecutor
-    obj_dir = os.path.join(LIB_DIR, "obj")
+    obj_dir = os.path.join(LIB_DIR, "obj" + tag)
     os.makedirs(obj_dir, exist_ok=True)
     vflags = ["-Xptxas", "-v"] if verbose else []
 
@@ -67,4 +73,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, trace="--trace" in sys.argv))

@@ -19,7 +19,7 @@ constexpr int P6_STAGES = 3;
 constexpr int P6_TILE_BYTES = 64 * 128;              // 64 rows (keys) x 64 bf16
 constexpr int P6_PBUF = 2 * P5_HALF_BYTES;           // P hi (128 rows x 64 keys = 16 KB) + P lo
 constexpr size_t p6_smem_bytes(int hd) {
-    return (size_t)(hd / 64) * P5_HALF_BYTES + (size_t)P6_STAGES * 2 * (hd / 64) * P6_TILE_BYTES + 2 * P6_PBUF + 1024 + 256 + 1024;
+    return (size_t)(hd / 64) * P5_HALF_BYTES + (size_t)P6_STAGES * 2 * (hd / 64) * P6_TILE_BYTES + 2 * P6_PBUF + 1024 + 256 + 1024 + 512;   // + page-id cache
 }
 
 // one MUFU instruction (exp2f without fast-math expands to range handling around it; inputs here are <= 8, and anything
@@ -84,23 +84,36 @@ __global__ void __launch_bounds__(P5_THREADS, 1) attn_prefill_tc5b_kernel(const 
     constexpr int PPT = P6_KEYS / KV_PAGE;             // pages per tile
 
     if (warp == 0) {
-        if (lane == 0) {
+        {
             const int* pt = a.page_table + (size_t)seq * a.pt_stride;
-            mbar_expect_tx(b_q, (uint32_t)NH * 64u * (uint32_t)a.G * (uint32_t)a.BT * 2u);
-            for (int c = 0; c < NH; ++c) p5_tma_3d(s_q + c * P5_HALF_BYTES, &map_q, b_q, c * 64, h * a.G, tok0);
+            // the page ids of the next 32 tiles are fetched by the whole warp at once into shared memory: read one by one by
+            // the issuing lane, every id is a dependent global load in front of its TMA (four per tile)
+            int* spt = reinterpret_cast<int*>(gen + (xchg - sbase) + 1024);
+            if (lane == 0) {
+                mbar_expect_tx(b_q, (uint32_t)NH * 64u * (uint32_t)a.G * (uint32_t)a.BT * 2u);
+                for (int c = 0; c < NH; ++c) p5_tma_3d(s_q + c * P5_HALF_BYTES, &map_q, b_q, c * 64, h * a.G, tok0);
+            }
             for (int j = 0; j < n_tiles; ++j) {
+                if ((j & 31) == 0) {
+                    __syncwarp();
+                    for (int i = lane; i < 32 * PPT; i += 32) spt[i] = (j * PPT + i < n_pages) ? pt[j * PPT + i] : 0;
+                    __syncwarp();
+                }
+                // one box per lane: 16 K/V boxes of a tile issued by 16 lanes at once.  Issued one after the other by a single
+                // lane they took ~1.2 us per tile (in-kernel trace) and paced the whole pipeline
                 const int s = j % P6_STAGES;
-                p5_wait(b_kve + 8 * s, ((j / P6_STAGES) & 1) ^ 1);
+                if (lane == 0) {
+                    p5_wait(b_kve + 8 * s, ((j / P6_STAGES) & 1) ^ 1);
+                    mbar_expect_tx(b_kvf + 8 * s, (uint32_t)min(PPT, n_pages - j * PPT) * (uint32_t)(NH * 4096));
+                }
+                __syncwarp();
                 const int npg = min(PPT, n_pages - j * PPT);
-                mbar_expect_tx(b_kvf + 8 * s, (uint32_t)npg * (uint32_t)(NH * 4096));
                 const uint32_t st = s_kv + s * STAGE;
-                for (int p = 0; p < npg; ++p) {
-                    const int page = pt[j * PPT + p];
+                if (lane < npg * 2 * NH) {
+                    const int p = lane / (2 * NH), c = (lane % (2 * NH)) >> 1, is_v = lane & 1;
+                    const int page = spt[(j & 31) * PPT + p];
                     const int row = ((a.layer * a.n_pages_pool + page) * a.n_kv + h) * KV_PAGE;
-                    for (int c = 0; c < NH; ++c) {
-                        tma_load_2d(st + c * P6_TILE_BYTES + p * (KV_PAGE * 128), &map_k, b_kvf + 8 * s, c * 64, row);
-                        tma_load_2d(st + (NH + c) * P6_TILE_BYTES + p * (KV_PAGE * 128), &map_v, b_kvf + 8 * s, c * 64, row);
-                    }
+                    tma_load_2d(st + (is_v * NH + c) * P6_TILE_BYTES + p * (KV_PAGE * 128), is_v ? &map_v : &map_k, b_kvf + 8 * s, c * 64, row);
                 }
             }
         }

@@ -88,8 +88,19 @@ __device__ __forceinline__ void rt_trace(int tag) {
     }
 }
 #define RT_TR(tag) rt_trace(tag)
+// a record from whichever single thread calls it (warp-specialised kernels: the role's leader lane)
+__device__ __forceinline__ void rt_trace_one(int tag) {
+    if (g_rt_trace) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        const unsigned i = atomicAdd(&g_rt_trace_n, 1u);
+        if (i < RT_TRACE_CAP) g_rt_trace[i] = {t, tag, (int)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z))};
+    }
+}
+#define RT_TR1(tag) rt_trace_one(tag)
 #else
 #define RT_TR(tag)
+#define RT_TR1(tag)
 #endif
 
 // ---- weight stream pipelining through L2 -----------------------------------------------------------------------

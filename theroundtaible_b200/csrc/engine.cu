@@ -13,11 +13,18 @@
 #include <memory>
 
 #include "attn_decode3.cuh"
+#include "attn_decode_tc5.cuh"
 #include "kernels.cuh"
 #include "safetensors.h"
 #include "sampler.cuh"
 #include "tp_fused.cuh"
 #include "weights.cuh"
+
+#ifdef RT_TRACE
+// the trace symbols are per translation unit: prefill.cu (tcgen05 kernels) keeps its own buffer
+void pf_trace_begin();
+void pf_trace_end(FILE* f);
+#endif
 
 namespace {
 
@@ -338,6 +345,7 @@ void load_weights(rt_engine* e) {
 #ifdef RT_TRACE
 // timeline dump (RT_TRACE_FILE): records of {globaltimer ns, tag, cta} written by thread 0 of every CTA
 static void trace_begin() {
+    pf_trace_begin();
     RtTraceRec* buf = nullptr;
     cudaMalloc(&buf, (size_t)RT_TRACE_CAP * sizeof(RtTraceRec));
     unsigned zero = 0;
@@ -353,7 +361,7 @@ static void trace_end(const char* path) {
     n = std::min(n, RT_TRACE_CAP);
     std::vector<RtTraceRec> h(n);
     cudaMemcpy(h.data(), buf, (size_t)n * sizeof(RtTraceRec), cudaMemcpyDeviceToHost);
-    if (FILE* f = fopen(path, "wb")) { fwrite(h.data(), sizeof(RtTraceRec), n, f); fclose(f); }
+    if (FILE* f = fopen(path, "wb")) { fwrite(h.data(), sizeof(RtTraceRec), n, f); pf_trace_end(f); fclose(f); }
     RtTraceRec* null = nullptr;
     cudaMemcpyToSymbol(g_rt_trace, &null, sizeof null);
     cudaFree(buf);
@@ -685,11 +693,20 @@ void engine_init(rt_engine* e) {
         // only halves its MMA work (30k-token 1B prompt: 378 vs 391 ms)
         const int tc5 = env_int("RT_PFA_TC5", 1);
         e->pfa_tc5 = tc5 != 0 && (e->hd == 128 || (e->hd == 64 && tc5 == 2)) && e->G <= 16;   // RT_PFA_TC5=0: the mma.sync kernel
-        if (e->pfa_tc5) {
-            pf_make_map_q3(&e->map_q3, e->pf_q, e->pf_cap, e->nq_l, e->G, 128 / e->G, e->hd);
+        // tcgen05 decode attention for long contexts (attn_decode_tc5.cuh): head_dim 64 / 128, rows = (slot, head) pairs
+        e->dec5_ok = env_int("RT_DEC5", 1) != 0 && (e->hd == 128 || e->hd == 64) && e->G <= 16;
+        if (e->pfa_tc5 || e->dec5_ok) {
             const long long rows = (long long)e->L * e->n_pages * e->nkv_l * KV_PAGE;
             pf_make_map_kv(&e->map_kpool, e->kpool, rows, e->hd);
             pf_make_map_kv(&e->map_vpool, e->vpool, rows, e->hd);
+        }
+        if (e->pfa_tc5) pf_make_map_q3(&e->map_q3, e->pf_q, e->pf_cap, e->nq_l, e->G, 128 / e->G, e->hd);
+        if (e->dec5_ok) {
+            e->dec5_bt = std::min(128 / e->G, MAX_SLOTS);
+            pf_make_map_q3(&e->map_qdec, e->qb, MAX_SLOTS, e->nq_l, e->G, e->dec5_bt, e->hd);
+            e->dec5_cap = 2 * e->sm_count;
+            e->dec5_items_dev = dalloc<Dec5Item>(e, e->dec5_cap);
+            RT_CUDA(cudaMallocHost(&e->dec5_items_host, (size_t)e->dec5_cap * sizeof(Dec5Item)));
         }
     }
     RT_CUDA(cudaStreamSynchronize(e->st));
@@ -710,6 +727,7 @@ void engine_free(rt_engine* e) {
     if (e->h_page_table) cudaFreeHost(e->h_page_table);
     if (e->h_stage) cudaFreeHost(e->h_stage);
     if (e->pf_host) cudaFreeHost(e->pf_host);
+    if (e->dec5_items_host) cudaFreeHost(e->dec5_items_host);
     for (auto& ev : e->ev)
         if (ev) cudaEventDestroy(ev);
     if (e->st) cudaStreamDestroy(e->st);
@@ -986,10 +1004,24 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
                 a3.scale_log2 = a.scale_log2; a3.out = e->attn_bf; a3.ldo = e->nq_l * hd; a3.early = a.early;
                 rt_attn3_host_launch(e, a3, hd, o.attn3_cs);
             } else {
-            rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
             MergeArgs m{};
+            m.n_sh_parts = -1;
+            m.chunk_keys = o.chunk_pages * KV_PAGE;
+            m.cascade = o.n_shared_tiles > 0;
+            if (o.dec5_items > 0) {
+                Dec5Args d{};
+                d.page_table = e->d_page_table; d.pt_stride = e->max_pages_per_seq; d.slot_seq = e->d_seq; d.slot_pos = e->d_pos;
+                d.shared_len_ptr = e->d_shared_len; d.items = reinterpret_cast<const Dec5Item*>(e->dec5_items_dev);
+                d.T = T; d.n_q = e->nq_l; d.n_kv = e->nkv_l; d.G = e->G; d.BT = e->dec5_bt; d.n_pages_pool = e->n_pages; d.layer = l;
+                d.scale_log2 = a.scale_log2; d.part_o = e->part_o; d.part_ml = e->part_ml; d.max_chunks = MAX_CHUNKS;
+                pf_attention_dec5(e->st, e->use_pdl, o.dec5_items, e->map_qdec, e->map_kpool, e->map_vpool, d, hd);
+                e->launches++;
+                m.n_sh_parts = o.dec5_nsh; m.chunk_keys = o.dec5_own_span; m.cascade = 1;
+            } else {
+                rt_attn_host_launch(e, a, hd, o.n_chunk_blocks);
+            }
             m.part_o = e->part_o; m.part_ml = e->part_ml; m.max_chunks = MAX_CHUNKS; m.slot_pos = e->d_pos;
-            m.shared_len_ptr = e->d_shared_len; m.cascade = o.n_shared_tiles > 0; m.chunk_keys = o.chunk_pages * KV_PAGE;
+            m.shared_len_ptr = e->d_shared_len;
             m.n_q = e->nq_l; m.hd = hd; m.out_bf = e->attn_bf; m.out_f32 = nullptr; m.ldo = e->nq_l * hd;
             const dim3 mg(e->nq_l, T);
             if (hd == 128) launch_pdl(e, attn_merge2_kernel<128>, mg, dim3(128), 0, m);
@@ -1066,6 +1098,34 @@ static void plan_chunks(int max_len, int shared_len, StepOpts& o, int hd = 64) {
 // Under tensor parallel the decision is COLLECTIVE: every rank contributes "my clock says stop" and all of them stop
 // if any does, at the same point of the call -- otherwise one rank would throw while its peers launch kernels that wait
 // for its partial sums (tp_fused.cuh).  Hence deadline_ms must be the same on every rank.
+// Work items of the tcgen05 decode attention (attn_decode_tc5.cuh) for a call whose sequences share `shared` keys and reach
+// at most max_len: one CTA per item, all items within ONE wave, the key ranges sized so that every item walks about the
+// same number of 64-key tiles.  Uploaded once per call; the kernels read the positions themselves.
+static void plan_dec5(rt_engine* e, int max_len, int shared, StepOpts& o) {
+    o.dec5_items = 0;
+    if (!e->dec5_ok || o.attn3_cs > 0 || o.T > e->dec5_bt || o.T > 8) return;
+    const int T = o.T, nkv = e->nkv_l;
+    const int sh_tiles = cdiv(shared, P6_KEYS), own_tiles = cdiv(std::max(max_len - shared, 1), P6_KEYS);
+    int L = 1;                                             // tiles per item: the smallest that fits one wave
+    auto count = [&](int l) { return nkv * cdiv(sh_tiles, l) + T * nkv * cdiv(own_tiles, l); };
+    while (count(L) > e->sm_count && L < 4096) ++L;
+    const int n_sh = sh_tiles ? cdiv(sh_tiles, L) : 0, n_own = cdiv(own_tiles, L);
+    if (count(L) > e->dec5_cap || n_sh + n_own + 1 > MAX_CHUNKS) return;
+    Dec5Item* it = reinterpret_cast<Dec5Item*>(e->dec5_items_host);
+    int n = 0;
+    // own items first: they are the ones that may end early, the shared ranges are always full
+    for (int t = 0; t < T; ++t)
+        for (int h = 0; h < nkv; ++h)
+            for (int c = 0; c < n_own; ++c) it[n++] = Dec5Item{t, h, c * L * P6_KEYS, L * P6_KEYS, n_sh + c, {0, 0, 0}};
+    for (int h = 0; h < nkv; ++h)
+        for (int c = 0; c < n_sh; ++c) it[n++] = Dec5Item{-1, h, c * L * P6_KEYS, L * P6_KEYS, c, {0, 0, 0}};
+    RT_CUDA(cudaStreamSynchronize(e->st));                 // the staging buffer of the previous call has been consumed
+    RT_CUDA(cudaMemcpyAsync(e->dec5_items_dev, it, (size_t)n * sizeof(Dec5Item), cudaMemcpyHostToDevice, e->st));
+    o.dec5_items = n;
+    o.dec5_nsh = n_sh;
+    o.dec5_own_span = L * P6_KEYS;
+}
+
 static void check_deadline(rt_engine* e, double t0, uint64_t deadline_ms) {
     if (deadline_ms == 0) return;
     const double el = now_ms() - t0;
@@ -1259,7 +1319,7 @@ static cudaGraphExec_t capture_steps(rt_engine* e, const StepOpts& o, int steps,
 
 static void ensure_graph(rt_engine* e, const StepOpts& o) {
     const StepOpts& g = e->graph_opts;
-    if (e->graph_exec && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks && g.n_sh == o.n_sh && g.n_own == o.n_own &&
+    if (e->graph_exec && g.dec5_items == o.dec5_items && g.dec5_nsh == o.dec5_nsh && g.dec5_own_span == o.dec5_own_span && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks && g.n_sh == o.n_sh && g.n_own == o.n_own &&
         g.n_shared_tiles == o.n_shared_tiles && g.attn3_cs == o.attn3_cs && g.inv_temp == o.inv_temp && g.seed == o.seed && g.top_k == o.top_k && g.top_p == o.top_p)
         return;
     if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }
@@ -1387,6 +1447,7 @@ void engine_generate_ids(rt_engine* e, const int32_t* const* prompts, const int3
     dec.advance = true;
     dec.n_shared_tiles = shared > 0 ? cdiv(n * e->G, 16) : 0;
     plan_chunks(max_len, shared, dec, e->hd);
+    plan_dec5(e, max_len, shared, dec);
 
     const int n_steps = s.max_new_tokens - 1;
     auto is_eos = [&](int t) { for (int j = 0; j < e->n_eos; ++j) if (t == e->eos_ids[j]) return true; return false; };

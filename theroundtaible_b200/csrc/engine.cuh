@@ -41,6 +41,8 @@ struct StepOpts {
     bool qkv_late = false;     // QKV projections release their dependent after their own wait (multi-step graphs)
     bool in_graph = false;     // the step is being captured into the decode graph (consecutive steps fully serialised)
     int top_k = 0;             // sampler.cuh; only with inv_temp > 0
+    // tcgen05 decode attention for long contexts (attn_decode_tc5.cuh): work items of the call, 0 = not used
+    int dec5_items = 0, dec5_nsh = 0, dec5_own_span = 0;
     float top_p = 0.f;
 };
 
@@ -114,6 +116,12 @@ struct rt_engine {
     int* pf_host = nullptr;        // pinned staging: tok, seq, pos (pf_cap each) + work items
     PfTensorMap map_xn{}, map_attn{}, map_act{};
     PfTensorMap map_q3{}, map_kpool{}, map_vpool{};   // tcgen05 prefill attention (head_dim 128, opt-in)
+    PfTensorMap map_qdec{};           // the decode queries qb as (dims, heads, slots) for attn_decode_tc5.cuh
+    bool dec5_ok = false;
+    int dec5_bt = 0;
+    void* dec5_items_dev = nullptr;   // Dec5Item[dec5_cap]
+    void* dec5_items_host = nullptr;  // pinned
+    int dec5_cap = 0;
     bool pfa_tc5 = false;
     std::vector<PfTensorMap> map_w;   // per layer: qkv, o, gate/up, down
 

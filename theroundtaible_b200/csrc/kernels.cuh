@@ -510,6 +510,8 @@ struct MergeArgs {
     const int* slot_pos;
     const int* shared_len_ptr;
     int cascade;       // n_shared_tiles > 0
+    int n_sh_parts;    // >= 0: the shared prefix contributes exactly this many partials (attn_decode_tc5.cuh: its key ranges are
+                       // not multiples of chunk_keys); -1: ceil(shared / chunk_keys) as written by attn_decode_kernel
     int max_len;       // > 0: clamp of slot_pos + 1 (see AttnArgs)
     int chunk_keys;    // C
     int n_q, hd;
@@ -555,7 +557,7 @@ static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs
     const int len = a.slot_pos[t] + 1;
     const int sh = (a.cascade && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
     const int C = a.chunk_keys;
-    const int n = (sh + C - 1) / C + (len - sh + C - 1) / C;
+    const int n = (a.n_sh_parts >= 0 ? a.n_sh_parts : (sh + C - 1) / C) + (len - sh + C - 1) / C;
     const size_t base = ((size_t)t * a.n_q + head) * a.max_chunks;
     constexpr int MAXB = (136 + 31) / 32;   // MAX_CHUNKS / 32
     float2 ml[MAXB];

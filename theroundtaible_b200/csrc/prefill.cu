@@ -4,6 +4,7 @@
 #include <cstring>
 
 #include "attn_prefill.cuh"
+#include "attn_decode_tc5.cuh"
 #include "attn_prefill_tc5b.cuh"
 #include "gemm_tc5.cuh"
 
@@ -167,3 +168,49 @@ void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap&
     RT_CUDA(cudaLaunchKernelEx(&cfg, kern, reinterpret_cast<const CUtensorMap&>(mq), reinterpret_cast<const CUtensorMap&>(mk),
                                reinterpret_cast<const CUtensorMap&>(mv), a));
 }
+
+void pf_attention_dec5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
+                       const Dec5Args& a, int hd) {
+    if (n_items <= 0) return;
+    const size_t smem = p6_smem_bytes(hd) + (D5_PARTS - 2) * 512;   // the exchange area holds D5_PARTS values per row
+    auto kern = hd == 128 ? attn_decode_tc5_kernel<128> : attn_decode_tc5_kernel<64>;
+    RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(n_items);
+    cfg.blockDim = dim3(D5_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    RT_CUDA(cudaLaunchKernelEx(&cfg, kern, reinterpret_cast<const CUtensorMap&>(mq), reinterpret_cast<const CUtensorMap&>(mk),
+                               reinterpret_cast<const CUtensorMap&>(mv), a));
+}
+
+#ifdef RT_TRACE
+#include <cstdio>
+#include <vector>
+void pf_trace_begin() {
+    RtTraceRec* buf = nullptr;
+    cudaMalloc(&buf, (size_t)RT_TRACE_CAP * sizeof(RtTraceRec));
+    unsigned zero = 0;
+    cudaMemcpyToSymbol(g_rt_trace_n, &zero, sizeof zero);
+    cudaMemcpyToSymbol(g_rt_trace, &buf, sizeof buf);
+}
+void pf_trace_end(FILE* f) {
+    RtTraceRec* buf = nullptr;
+    unsigned n = 0;
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(&buf, g_rt_trace, sizeof buf);
+    cudaMemcpyFromSymbol(&n, g_rt_trace_n, sizeof n);
+    n = n < RT_TRACE_CAP ? n : RT_TRACE_CAP;
+    std::vector<RtTraceRec> h(n);
+    cudaMemcpy(h.data(), buf, (size_t)n * sizeof(RtTraceRec), cudaMemcpyDeviceToHost);
+    fwrite(h.data(), sizeof(RtTraceRec), n, f);
+    RtTraceRec* null = nullptr;
+    cudaMemcpyToSymbol(g_rt_trace, &null, sizeof null);
+    cudaFree(buf);
+}
+#endif

@@ -58,6 +58,10 @@ void pf_make_map_kv(PfTensorMap* out, const void* base, long long rows, int hd);
 void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
                       const int* page_table, int pt_stride, const int* tok_pos, const int4* work, int n_q, int n_kv, int G, int BT,
                       int n_pages_pool, int layer, float scale_log2, f16* out, int hd);
+// tcgen05 decode attention for long contexts (attn_decode_tc5.cuh): query rows = (slot, q-head) pairs, work items = key ranges
+struct Dec5Args;
+void pf_attention_dec5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
+                       const Dec5Args& a, int hd);
 void pf_make_map_a(PfTensorMap* out, const void* base, int rows, int K);
 void pf_make_map_w(PfTensorMap* out, const void* base, int N, int K, int BN);
 void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const PfTensorMap& mw, const Gemm5Args& a);

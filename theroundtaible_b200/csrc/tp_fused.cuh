@@ -45,8 +45,10 @@ __device__ __forceinline__ int tpf_ld_acquire_sys(const int* p) {
 
 __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(const TpFusedArgs a) {
     __shared__ float sred[TPF_THREADS / 32];
+    RT_TR(70);
     griddep_launch();
     griddep_wait();                         // this rank's partial comes from the previous kernel
+    RT_TR(71);
     const int c = blockIdx.x, t = blockIdx.y;
     const int cell = t * TPF_CMAX + c;
     if (threadIdx.x < 32) {
@@ -71,6 +73,7 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
         }
     }
     __syncthreads();
+    RT_TR(72);                              // every peer's flag seen
 
     const int n4 = a.H >> 2;
     const int c4 = c * TPF_THREADS + threadIdx.x;
@@ -98,4 +101,5 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
         for (int w = 0; w < TPF_THREADS / 32; ++w) tot += sred[w];
         a.ss_part[c * 32 + t] = tot;
     }
+    RT_TR(74);
 }

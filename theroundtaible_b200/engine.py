@@ -76,10 +76,11 @@ def load_library():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(_LIB_PATH):
-        raise EngineError(-2, f"native library not found at {_LIB_PATH}: run `python -m theroundtaible_b200.build` "
+    path = os.environ.get("RT_LIB") or _LIB_PATH        # RT_LIB: a profiling build of the same sources (build.py --trace)
+    if not os.path.exists(path):
+        raise EngineError(-2, f"native library not found at {path}: run `python -m theroundtaible_b200.build` "
                               "(this backend has no CPU fallback)")
-    lib = C.CDLL(_LIB_PATH)
+    lib = C.CDLL(path)
     vp, i32, i64, u64, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_size_t
     lib.rt_arch_by_name.argtypes = [C.c_char_p, C.POINTER(RtConfig)]
     lib.rt_engine_create.argtypes = [C.POINTER(RtConfig), C.POINTER(vp)]
