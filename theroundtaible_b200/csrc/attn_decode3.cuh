@@ -38,7 +38,7 @@ struct Attn3Args {
     const int* slot_pos;
     int T, n_q, n_kv;
     float scale_log2;
-    f16* out;                   // [T][n_q*hd] normalised, fp16 (the O-projection's input)
+    bf16* out;                  // normalised output = the O-projection's input: XF layout over ldo columns (common.cuh)
     int ldo;
     int early;                  // index setup and old KV pages before the PDL wait (see AttnArgs.early)
 };
@@ -298,9 +298,7 @@ __global__ void __launch_bounds__(A3_WARPS * 32, 1) attn_decode3_kernel(const At
             L += l2[(size_t)c * PF + 16 * HD + row * 2 + 1] * sc;
         }
         const float inv = 1.0f / L;
-        uint2 pk;
-        pk.x = pack_f16(acc.x * inv, acc.y * inv);
-        pk.y = pack_f16(acc.z * inv, acc.w * inv);
-        *reinterpret_cast<uint2*>(a.out + (size_t)slot * a.ldo + (size_t)(h * G + row) * HD + d4) = pk;
+        const float y[4] = {acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv};
+        xf_store4(a.out, a.ldo, slot, (h * G + row) * HD + d4, y);
     }
 }

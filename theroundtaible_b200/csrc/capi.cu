@@ -278,12 +278,21 @@ int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t
         RT_REQUIRE(N > 0 && N % 16 == 0 && K > 0 && K % 32 == 0 && T >= 1 && T <= MAX_SLOTS, "need N%16==0, K%32==0, 1<=T<=32");
         Scratch s(device);
         bf16* dw = s.alloc<bf16>((size_t)N * K, false);
-        f16* dx = s.alloc<f16>((size_t)MAX_SLOTS * K);
+        bf16* dx = s.alloc<bf16>(xf_elems(K));
         float* dy = s.alloc<float>((size_t)MAX_SLOTS * N);
         std::vector<uint16_t> cm((size_t)N * K);
         wgen::rowmajor_to_cm(w, cm.data(), N, K);     // the kernel streams the core-matrix-major layout (gemv.cuh)
+        // the fp16 inputs as the engine's producers store them: bf16 hi + lo in the XF layout (common.cuh)
+        std::vector<bf16> xf(xf_elems(K), __float2bfloat16_rn(0.f));
+        for (int t = 0; t < T; ++t)
+            for (int k = 0; k < K; ++k) {
+                const float h = __half2float(__ushort_as_half(x[(size_t)t * K + k]));
+                const bf16 hi = __float2bfloat16_rn(h);
+                xf[xf_index(t, k, K)] = hi;
+                xf[xf_index(t, k, K) + 256] = __float2bfloat16_rn(h - __bfloat162float(hi));
+            }
         RT_CUDA(cudaMemcpyAsync(dw, cm.data(), (size_t)N * K * 2, cudaMemcpyHostToDevice, s.e.st));
-        RT_CUDA(cudaMemcpyAsync(dx, x, (size_t)T * K * 2, cudaMemcpyHostToDevice, s.e.st));
+        RT_CUDA(cudaMemcpyAsync(dx, xf.data(), xf.size() * 2, cudaMemcpyHostToDevice, s.e.st));
         GemvArgs a{};
         a.W = dw; a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N;
         rt_gemv_host_dispatch(&s.e, a, EPI_STORE);
@@ -480,11 +489,11 @@ int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t epi,
         const size_t mat = (size_t)N * K;
         const int copies = (int)std::max<size_t>(2, (size_t)400e6 / (mat * 2) + 1);   // > 3x L2 in rotation
         bf16* dw = s.alloc<bf16>(mat * copies);
-        f16* dx = s.alloc<f16>((size_t)MAX_SLOTS * K);
+        bf16* dx = s.alloc<bf16>(xf_elems(K));
         float* dy = s.alloc<float>((size_t)MAX_SLOTS * N);
         GemvArgs a{};
         a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N;
-        a.out_bf = s.alloc<f16>((size_t)MAX_SLOTS * N / 2); a.ldob = N / 2;      // SwiGLU: gate/up row pairs -> N/2 outputs
+        a.out_bf = s.alloc<bf16>(xf_elems(N / 2)); a.ldob = N / 2;               // SwiGLU: gate/up row pairs -> N/2 outputs (XF layout)
         cudaEvent_t e0, e1;
         RT_CUDA(cudaEventCreate(&e0));
         RT_CUDA(cudaEventCreate(&e1));

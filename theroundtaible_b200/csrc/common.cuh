@@ -57,11 +57,33 @@ __device__ __forceinline__ uint32_t pack_f16(float a, float b) {
 __device__ __forceinline__ f16 to_f16(float a) { return __float2half_rn(sat_f16(a)); }
 // The decode kernels multiply with mma.sync, whose operands must share one 16-bit format, and the weights are bf16:
 // an fp16 value (11 significant bits) is fed as bf16 hi (8 bits, RNE) + bf16 lo (the remainder: <= 3 significant bits,
-// exact), so the product with a bf16 weight is exact in the fp16 input.  `w` holds two fp16 values.
-__device__ __forceinline__ void split_f16x2(uint32_t w, uint32_t& hi, uint32_t& lo) {
-    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
-    hi = pack_bf16(f.x, f.y);
-    lo = pack_bf16(f.x - bf16lo(hi), f.y - bf16hi(hi));
+// exact), so the product with a bf16 weight is exact in the fp16 input.  The PRODUCER of an activation splits it once and
+// stores both parts in the decode kernels' "XF" layout, which is the order the projection kernel's lanes fetch their
+// MMA B fragments in (gemv.cuh): [slot group of 8][k-block of 32][hi | lo][slot in group][32 k] bf16, so the 8 slots x 32 k
+// of one part are 512 contiguous bytes -- 4 full cache lines per warp load instead of 8 half lines of a row-major matrix.
+__host__ __device__ inline size_t xf_index(int slot, int k, int K) {   // the hi part; the lo part is 256 elements further
+    return (size_t)(slot >> 3) * ((size_t)K * 16) + (size_t)(k >> 5) * 512 + (size_t)((slot & 7) * 32 + (k & 31));
+}
+__host__ __device__ inline size_t xf_elems(int K) { return (size_t)K * 64; }      // 32 slots x 2 parts
+__device__ __forceinline__ void split_f16x2(float a, float b, uint32_t& hi, uint32_t& lo) {
+    const float ha = __half2float(__float2half_rn(sat_f16(a))), hb = __half2float(__float2half_rn(sat_f16(b)));
+    hi = pack_bf16(ha, hb);
+    lo = pack_bf16(ha - bf16lo(hi), hb - bf16hi(hi));
+}
+__device__ __forceinline__ void xf_store1(bf16* base, int K, int slot, int k, float v) {
+    const float h = __half2float(__float2half_rn(sat_f16(v)));
+    const bf16 hi = __float2bfloat16_rn(h);
+    const size_t i = xf_index(slot, k, K);
+    base[i] = hi;
+    base[i + 256] = __float2bfloat16_rn(h - __bfloat162float(hi));
+}
+__device__ __forceinline__ void xf_store4(bf16* base, int K, int slot, int k, const float (&y)[4]) {   // k % 4 == 0
+    uint2 h, l;
+    split_f16x2(y[0], y[1], h.x, l.x);
+    split_f16x2(y[2], y[3], h.y, l.y);
+    const size_t i = xf_index(slot, k, K);
+    *reinterpret_cast<uint2*>(base + i) = h;
+    *reinterpret_cast<uint2*>(base + i + 256) = l;
 }
 
 // streaming 16-byte load that does not pollute L1 (weights are read exactly once per step)

@@ -608,10 +608,10 @@ void engine_init(rt_engine* e) {
     e->x = zalloc_f((size_t)MAX_SLOTS * e->H);
     e->delta = zalloc_f((size_t)MAX_SLOTS * e->H);
     e->qkv = zalloc_f((size_t)MAX_SLOTS * e->qkv_rows);
-    e->xn = zalloc_h((size_t)MAX_SLOTS * e->H);
+    e->xn = zalloc_b(xf_elems(e->H));
     e->qb = zalloc_b((size_t)MAX_SLOTS * e->nq_l * e->hd);
-    e->attn_bf = zalloc_h((size_t)MAX_SLOTS * e->nq_l * e->hd);
-    e->act_bf = zalloc_h((size_t)MAX_SLOTS * e->F_l);
+    e->attn_bf = zalloc_b(xf_elems(e->nq_l * e->hd));
+    e->act_bf = zalloc_b(xf_elems(e->F_l));
     e->part_o = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * e->hd);
     e->part_ml = zalloc_f((size_t)MAX_SLOTS * e->nq_l * MAX_CHUNKS * 2);
     e->ss_part = zalloc_f((size_t)(e->H / 16) * 32);
@@ -882,7 +882,7 @@ static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, c
         g.out = e->delta; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
         tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
-        rms_xw_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, e->inv_rms, H, e->cfg.rms_eps);
+        rms_xw_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, 1, e->inv_rms, H, e->cfg.rms_eps);
         e->launches += 2;
     }
 }
@@ -961,7 +961,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
     static const int skip = env_int("RT_SKIP_MASK", 0);
 
     launch_pdl(e, embed_norm_kernel, dim3(T), dim3(256), 0, (const bf16*)e->embed, (const int*)e->d_tok, e->x,
-               (const bf16*)e->layers[0].norm1, e->xn, e->ss_part, e->inv_rms, H, e->vocab, e->cfg.rms_eps);
+               (const bf16*)e->layers[0].norm1, (void*)e->xn, 1, e->ss_part, e->inv_rms, H, e->vocab, e->cfg.rms_eps);
 
     for (int l = 0; l < e->L; ++l) {
         const LayerW& w = e->layers[l];
@@ -1104,6 +1104,12 @@ static void plan_chunks(int max_len, int shared_len, StepOpts& o, int hd = 64) {
 static void plan_dec5(rt_engine* e, int max_len, int shared, StepOpts& o) {
     o.dec5_items = 0;
     if (!e->dec5_ok || o.attn3_cs > 0 || o.T > e->dec5_bt || o.T > 8) return;
+    // measured (profiles/r2_summary.md): with >= 8 kv heads on the GPU and <= 32 query rows per kv head on a shared prefix
+    // the mma.sync split-KV kernel has enough warps in flight and is 0-3 % faster (config 3: 3.52 vs 3.63 ms per step); with
+    // fewer kv heads per GPU (tensor-parallel shards: 70B/TP8 -7 %, 32B/TP4 -5 %), more rows, or no shared prefix (SEQ mode,
+    // -3 %) the tensor-memory kernel wins.  RT_DEC5=2 forces it.
+    static const int dec5_mode = env_int("RT_DEC5", 1);
+    if (dec5_mode != 2 && shared > 0 && o.T * e->G <= 32 && e->nkv_l >= 8) return;
     const int T = o.T, nkv = e->nkv_l;
     const int sh_tiles = cdiv(shared, P6_KEYS), own_tiles = cdiv(std::max(max_len - shared, 1), P6_KEYS);
     int L = 1;                                             // tiles per item: the smallest that fits one wave
@@ -1213,7 +1219,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
         RT_CUDA(cudaMemcpyAsync(e->pf_work, hw, (size_t)n_items * sizeof(int4), cudaMemcpyHostToDevice, e->st));
 
         launch_pdl(e, embed_norm_kernel, dim3(S), dim3(256), 0, (const bf16*)e->embed, (const int*)e->pf_tok, e->pf_x,
-                   (const bf16*)e->layers[0].norm1, e->pf_xn, (float*)nullptr, e->pf_inv_rms, H, e->vocab, e->cfg.rms_eps);
+                   (const bf16*)e->layers[0].norm1, (void*)e->pf_xn, 0, (float*)nullptr, e->pf_inv_rms, H, e->vocab, e->cfg.rms_eps);
         for (int l = 0; l < e->L; ++l) {
             const LayerW& w = e->layers[l];
             bf16* kp = e->kpool + (size_t)l * e->layer_pool_elems;
@@ -1241,7 +1247,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             go.out = e->tp ? e->pf_delta : e->pf_x;
             pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
             if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
-            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, w.norm2, e->pf_xn, e->pf_inv_rms, H, e->cfg.rms_eps);
+            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, w.norm2, e->pf_xn, 0, e->pf_inv_rms, H, e->cfg.rms_eps);
             e->launches += 2;
 
             Gemm5Args gu{};
@@ -1253,7 +1259,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
             if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
             const bf16* nw = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;
-            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, nw, e->pf_xn, e->pf_inv_rms, H, e->cfg.rms_eps);
+            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, nw, e->pf_xn, 0, e->pf_inv_rms, H, e->cfg.rms_eps);
             e->launches += 3;
         }
         RT_CUDA(cudaGetLastError());

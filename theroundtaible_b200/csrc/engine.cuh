@@ -91,7 +91,8 @@ struct rt_engine {
 
     // activations (MAX_SLOTS rows each)
     float *x = nullptr, *qkv = nullptr, *delta = nullptr, *logits = nullptr;
-    f16 *xn = nullptr, *attn_bf = nullptr, *act_bf = nullptr;   // projection inputs: fp16 (common.cuh)
+    // projection inputs of the decode kernels: fp16 values as bf16 hi + lo in the XF layout (common.cuh)
+    bf16 *xn = nullptr, *attn_bf = nullptr, *act_bf = nullptr;
     bf16* qb = nullptr;
     float *part_o = nullptr, *part_ml = nullptr;
     long long pf_attn_bytes = 0;   // weights pulled into L2 while a layer's attention runs (RT_PF_ATTN_MB)

@@ -18,15 +18,16 @@
 // added in fixed warp order through shared memory (bit-reproducible, no atomics).  With PDL the first weight
 // loads are issued BEFORE griddepcontrol.wait, so the HBM stream keeps running across kernel boundaries.
 //
-// Activations are fp16 (common.cuh): a lane splits the 8 values it loads into bf16 hi + lo in registers (split_f16x2) and
-// feeds both to the MMAs, so the product is exact in the fp16 input.  Measured alternatives (profiles/r2_summary.md): hi / lo
-// written by the producer as two planes cost a second activation load per k-block -- the activation rows are read by EVERY
-// CTA from the same few L2 lines and that path, not the ALU, is the scarce one (+18 % per kernel against +6 % here).
+// Activations are fp16 VALUES (common.cuh) that their producer has split into bf16 hi + lo and stored in the XF layout
+// (common.cuh xf_index): the lanes of a warp fetch the B fragments of a k-block as 512 contiguous bytes per part, and both
+// parts go through the MMAs, so the product is exact in the fp16 input.  Measured alternatives (profiles/r2_summary.md): the
+// split done in registers by the consumer costs ~36 ALU instructions per k-block and lane (+6-8 % per step); hi / lo as two
+// ROW-MAJOR planes double the half-line requests to the few L2 lines every CTA reads (+18 % per kernel).
 // With T <= 4 slots (template HM) hi and lo share ONE MMA: columns 0..3 carry hi of slots 0..3, columns 4..7 their lo,
 // and the epilogue adds the two columns of a slot.
 //
 // Fusions: EPI_QKV    -> + bias, RoPE, q -> bf16 Q buffer, k/v -> bf16 into their KV page;
-//          EPI_RESID  -> x += acc, xw = fp16(x * w_next) and per-tile partial sums of x^2: the next projection applies
+//          EPI_RESID  -> x += acc, xw = fp16(x * w_next) (XF layout) and per-tile partial sums of x^2: the next projection applies
 //                        the RMSNorm scale to its accumulators (no RMSNorm launch, no tail);
 //          EPI_SWIGLU -> fp16(silu(gate) * up);   EPI_LOGITS -> logits and per-CTA arg-max candidates.
 #pragma once
@@ -40,14 +41,14 @@ struct GemvArgs {
     const bf16* W;            // CM layout
     int N, K, T;
     // B operand
-    const f16* X;             // activations [rows][ldx] fp16 (the activation contract, common.cuh)
-    int ldx;
+    const bf16* X;            // activations of the K input columns in the XF layout (common.cuh): bf16 hi + lo of fp16 values
+    int ldx;                  // (unused: the XF layout is fixed by K)
     // RMSNorm is split around the projections ("scale after the matmul"): the PRODUCER of the residual stream (RESID
     // epilogue, embed kernel) writes xw = bf16(x * norm_w) per element plus the per-16-row-tile partial sums of x^2; the
     // CONSUMER projection multiplies its accumulators by r = rsqrt(mean x^2 + eps) in the epilogue.  No kernel ever
     // waits for a whole row, so there is no RMSNorm launch and no last-CTA tail on the critical path.
     const bf16* norm_w;       // RESID: weight of the NEXT norm [N]; nullable => no xw / partial sums
-    f16* xn_out;              // RESID: xw out [T][N] fp16
+    bf16* xn_out;             // RESID: xw out, XF layout over N columns
     float* ss_out;            // RESID: [N/16][32] partial sums of x^2 of the updated rows
     const float* ss_in;       // consumer: partial sums [n_parts_in][32] of the rows behind X (nullable)
     int n_parts_in;
@@ -58,7 +59,7 @@ struct GemvArgs {
     float* out;               // STORE: out[t*ldo+n] = acc (+bias) ; RESID: out[t*ldo+n] += acc
     int ldo;
     const float* bias;        // STORE / QKV (physical row order), nullable
-    f16* out_bf;              // SWIGLU: [t*ldob + col] fp16
+    bf16* out_bf;             // SWIGLU: XF layout over ldob columns
     int ldob;
     // LOGITS
     float* logits;
@@ -115,7 +116,8 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     // columns 4..7 their lo part.
     constexpr int SL = HM ? 4 : NT * 8;               // slots this instantiation serves
     // k-blocks of weights a warp keeps in flight (registers): W takes 8*U*MT registers, X 4*U*NT
-    constexpr int U = (MT * NT >= 4) ? 2 : (MT * NT == 2 ? 4 : 8);
+    constexpr int XP = HM ? 1 : 2;                    // activation loads per (k-block, slot group): HM lanes pick their part
+    constexpr int U = HM ? 8 / MT : (NT == 1 ? (MT == 1 ? 6 : (MT == 2 ? 4 : 2)) : (NT == 2 && MT == 1 ? 4 : 2));
     constexpr int NTHR = NW * 32;
     __shared__ float4 red[NW][MT * NT][32];
     __shared__ float res[MT * NT][16][8];
@@ -242,43 +244,37 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 
     for (int kbb = kb0; kbb < kb1; kbb += U) {
         // B operand for this batch
-        uint4 xv[U][NT];
+        uint4 xv[U][NT][XP];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const int kb = kbb + u;
-            const int ko = (kb << 5) + q * 8;
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
                 const int slot = HM ? (g & 3) : nt * 8 + g;
-                // rows of unused slots are never fetched: every CTA reads the SAME activation rows, which makes the few
+                // XF layout: [slot group][k-block][hi | lo][8 slots][32 k]; HM lanes 4..7 fetch the lo part of slots 0..3.
+                // Rows of unused slots are never fetched: every CTA reads the SAME activation lines, which makes the few
                 // L2 slices holding them the hot spot of a short kernel (measured: scripts/probes/gridbar.cu mode 2)
-                if (kb < kb1 && slot < a.T) {
-                    xv[u][nt] = *reinterpret_cast<const uint4*>(a.X + (size_t)slot * a.ldx + ko);
-                } else {
-                    xv[u][nt] = make_uint4(0, 0, 0, 0);
+                const bf16* xp = a.X + (size_t)nt * ((size_t)a.K * 16) + (size_t)kb * 512 + (HM ? (g >> 2) * 256 + (g & 3) * 32 : g * 32) + q * 8;
+#pragma unroll
+                for (int p = 0; p < XP; ++p) {
+                    if (kb < kb1 && slot < a.T) xv[u][nt][p] = *reinterpret_cast<const uint4*>(xp + p * 256);
+                    else xv[u][nt][p] = make_uint4(0, 0, 0, 0);
                 }
             }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u)
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-                uint4 xh, xl;                      // the fp16 inputs as bf16 hi + lo
-                split_f16x2(xv[u][nt].x, xh.x, xl.x);
-                split_f16x2(xv[u][nt].y, xh.y, xl.y);
-                split_f16x2(xv[u][nt].z, xh.z, xl.z);
-                split_f16x2(xv[u][nt].w, xh.w, xl.w);
-                if (HM && g >= 4) xh = xl;         // columns 4..7 carry the lo part of slots 0..3
+            for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-                for (int mt = 0; mt < MT; ++mt) {
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y, xh.x, xh.y);
-                    mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w, xh.z, xh.w);
-                    if (!HM) {
-                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y, xl.x, xl.y);
-                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w, xl.z, xl.w);
+                for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                    for (int p = 0; p < XP; ++p) {       // hi part, then lo part, into the same accumulator
+                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
+                                       xv[u][nt][p].x, xv[u][nt][p].y);
+                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
+                                       xv[u][nt][p].z, xv[u][nt][p].w);
                     }
-                }
-            }
         // next batch of weights
         if (kbb + U < kb1) {
 #pragma unroll
@@ -351,7 +347,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 const float v = (first ? pre_f0 : *o) + val(r >> 4, r & 15, s);
                 *o = v;
                 if (a.norm_w) {
-                    a.xn_out[(size_t)s * a.N + n] = to_f16(v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])));
+                    xf_store1(a.xn_out, a.N, s, n, v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])));
                     // the updated residual goes back (HM: into the hi column, lo column zero) for the sums of squares below
                     if (HM) { res[r >> 4][r & 15][s] = v; res[r >> 4][r & 15][s + 4] = 0.f; }
                     else res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] = v;
@@ -383,7 +379,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 const float gt = val(mt, rr, s) * s_rn[s];
                 const float up = val(mt, rr + 8, s) * s_rn[s];
                 const float act = gt / (1.0f + expf(-gt)) * up;
-                a.out_bf[(size_t)s * a.ldob + (n >> 1) + rr] = to_f16(act);
+                xf_store1(a.out_bf, a.ldob, s, (n >> 1) + rr, act);
             }
         }
     } else if (EPI == EPI_QKV) {

@@ -10,18 +10,23 @@
 #include "common.cuh"
 #include "gemv.cuh"
 
-// a projection input leaves its producer as fp16 (common.cuh)
-__device__ __forceinline__ void store_act4(f16* base, size_t idx, const float (&y)[4]) {
-    uint2 o;
-    o.x = pack_f16(y[0], y[1]); o.y = pack_f16(y[2], y[3]);
-    *reinterpret_cast<uint2*>(base + idx) = o;
+// a projection input leaves its producer as fp16 (prefill: row-major [rows][K] for the tcgen05 GEMMs) or, for the decode
+// projection kernel, as the bf16 hi + lo of that fp16 value in the XF layout (common.cuh); xf != 0 selects the latter
+__device__ __forceinline__ void store_act4(void* base, int xf, int K, int row, int k, const float (&y)[4]) {
+    if (xf) {
+        xf_store4(reinterpret_cast<bf16*>(base), K, row, k, y);
+    } else {
+        uint2 o;
+        o.x = pack_f16(y[0], y[1]); o.y = pack_f16(y[2], y[3]);
+        *reinterpret_cast<uint2*>(reinterpret_cast<f16*>(base) + (size_t)row * K + k) = o;
+    }
 }
 // Rows of a prefill activation buffer -> slots of the decode buffer, with their RMSNorm scale: how the last prompt tokens
 // reach the decode lm_head kernel.  One CTA per row.
 struct GatherRowsArgs {
     const f16* src;        // [S][H]
     const float* src_r;    // [S]
-    f16* dst;              // [32][H]
+    bf16* dst;             // XF layout over H columns
     float* dst_r;          // [32]
     int H;
     int rows[32];
@@ -29,19 +34,22 @@ struct GatherRowsArgs {
 static __global__ void __launch_bounds__(256) gather_rows_kernel(const GatherRowsArgs a) {
     const int t = blockIdx.x, r = a.rows[t];
     for (int c = threadIdx.x * 4; c < a.H; c += blockDim.x * 4) {
-        *reinterpret_cast<uint2*>(a.dst + (size_t)t * a.H + c) = *reinterpret_cast<const uint2*>(a.src + (size_t)r * a.H + c);
+        const uint2 v = *reinterpret_cast<const uint2*>(a.src + (size_t)r * a.H + c);
+        const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&v.x)), f1 = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+        const float y[4] = {f0.x, f0.y, f1.x, f1.y};
+        xf_store4(a.dst, a.H, t, c, y);
     }
     if (threadIdx.x == 0) a.dst_r[t] = a.src_r[r];
 }
 
 // =================================================================================================
 // Embedding gather from the CM-layout table (gemv.cuh):  x[t][:] = float(E[tok[t]][:]), and the first layer's
-// RMSNorm in its split form (gemv.cuh): xw = fp16(x * w), per-16-element partial sums of x^2 (decode consumers) and
+// RMSNorm in its split form (gemv.cuh): xw = fp16(x * w) (row-major fp16, or XF layout with xf != 0), per-16-element partial sums of x^2 (decode consumers) and
 // r = rsqrt(mean x^2 + eps) (prefill / tensor-parallel consumers).  One CTA per slot, one thread per 16 elements.
 // =================================================================================================
 static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __restrict__ E, const int* __restrict__ tok,
                                                                 float* __restrict__ x, const bf16* __restrict__ norm_w,
-                                                                f16* __restrict__ xw, float* __restrict__ ss_part,
+                                                                void* __restrict__ xw, int xf, float* __restrict__ ss_part,
                                                                 float* __restrict__ inv_rms, int H, int vocab, float eps) {
     griddep_launch();
     griddep_wait();
@@ -67,8 +75,8 @@ static __global__ void __launch_bounds__(256) embed_norm_kernel(const bf16* __re
             o[1] = b;
             const float y0[4] = {a.x * bf16lo(wv.x), a.y * bf16hi(wv.x), a.z * bf16lo(wv.y), a.w * bf16hi(wv.y)};
             const float y1[4] = {b.x * bf16lo(wv.z), b.y * bf16hi(wv.z), b.z * bf16lo(wv.w), b.w * bf16hi(wv.w)};
-            store_act4(xw, (size_t)t * H + k, y0);
-            store_act4(xw, (size_t)t * H + k + 4, y1);
+            store_act4(xw, xf, H, t, k, y0);
+            store_act4(xw, xf, H, t, k + 4, y1);
             ss += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w + b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
         }
         if (ss_part) ss_part[part * 32 + (t & 31)] = ss;
@@ -101,7 +109,7 @@ static __global__ void bf16_to_f16_kernel(const bf16* __restrict__ in, f16* __re
 // Split RMSNorm for the paths that have a whole row in one place (prefill, tensor parallel): x (+= delta) stays fp32,
 // xw = fp16(x * w), inv_rms[t] = rsqrt(mean x^2 + eps).  One CTA per token.
 static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ x, const float* __restrict__ delta,
-                                                            const bf16* __restrict__ w, f16* __restrict__ xw,
+                                                            const bf16* __restrict__ w, void* __restrict__ xw, int xf,
                                                             float* __restrict__ inv_rms, int H, float eps) {
     const int t = blockIdx.x;
     float* xr = x + (size_t)t * H;
@@ -116,7 +124,7 @@ static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ 
         }
         const uint2 wv = *reinterpret_cast<const uint2*>(w + c);
         const float y[4] = {v.x * bf16lo(wv.x), v.y * bf16hi(wv.x), v.z * bf16lo(wv.y), v.w * bf16hi(wv.y)};
-        store_act4(xw, (size_t)t * H + c, y);
+        store_act4(xw, xf, H, t, c, y);
         ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
     __shared__ float red[8];
@@ -515,7 +523,7 @@ struct MergeArgs {
     int max_len;       // > 0: clamp of slot_pos + 1 (see AttnArgs)
     int chunk_keys;    // C
     int n_q, hd;
-    f16* out_bf;       // nullable  [T][ldo]: fp16, the input of the O-projection
+    bf16* out_bf;      // nullable: the input of the O-projection, XF layout over ldo columns
     float* out_f32;    // nullable  [T][ldo]
     int ldo;
 };
@@ -537,7 +545,7 @@ static __global__ void attn_merge_kernel(const MergeArgs a) {
         acc += a.part_o[(base + i) * a.hd + d] * w;
     }
     const float r = acc / L;
-    if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * a.hd + d] = to_f16(r);
+    if (a.out_bf) xf_store1(a.out_bf, a.ldo, t, head * a.hd + d, r);
     if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * a.hd + d] = r;
 }
 
@@ -609,7 +617,7 @@ static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs
     if (threadIdx.x < HD) {
         const float r = (sacc[0][threadIdx.x] + sacc[1][threadIdx.x]) + (sacc[2][threadIdx.x] + sacc[3][threadIdx.x]);
         const float o = r / sL[0];
-        if (a.out_bf) a.out_bf[(size_t)t * a.ldo + head * HD + threadIdx.x] = to_f16(o);
+        if (a.out_bf) xf_store1(a.out_bf, a.ldo, t, head * HD + threadIdx.x, o);
         if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * HD + threadIdx.x] = o;
     }
     RT_TR(64);

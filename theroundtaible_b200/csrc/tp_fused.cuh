@@ -32,7 +32,7 @@ struct TpFusedArgs {
     int rank, tp, H;
     float* x;                        // local residual stream [T][H]
     const bf16* norm_w;
-    f16* xn;                         // local [32][H]: xw = fp16(x * w) (split RMSNorm, gemv.cuh)
+    bf16* xn;                        // local, XF layout over H columns: xw = fp16(x * w) as bf16 hi + lo (gemv.cuh)
     float* ss_part;                  // local [gridDim.x][32]: per-column-block sums of x^2 for the consuming projection
 };
 
@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
         *(reinterpret_cast<float4*>(a.x + (size_t)t * a.H) + c4) = acc;
         ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
         const float y[4] = {acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x), acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y)};
-        store_act4(a.xn, (size_t)t * a.H + c4 * 4, y);
+        xf_store4(a.xn, a.H, t, c4 * 4, y);
     }
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = ss;
