@@ -36,6 +36,7 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("NCCL_DEBUG", "WARN")      # no version banner on stdout: rank 0 prints exactly one JSON line
 
 WORKLOADS = {
     # BASELINE.json configs[1]: 3 knights, Llama-3.2-1B bf16, shared system-prompt prefix, greedy

@@ -1108,7 +1108,7 @@ static void plan_dec5(rt_engine* e, int max_len, int shared, StepOpts& o) {
     // the mma.sync split-KV kernel has enough warps in flight and is 0-3 % faster (config 3: 3.52 vs 3.63 ms per step); with
     // fewer kv heads per GPU (tensor-parallel shards: 70B/TP8 -7 %, 32B/TP4 -5 %), more rows, or no shared prefix (SEQ mode,
     // -3 %) the tensor-memory kernel wins.  RT_DEC5=2 forces it.
-    static const int dec5_mode = env_int("RT_DEC5", 1);
+    const int dec5_mode = env_int("RT_DEC5", 1);       // read per call (tests switch it between engines)
     if (dec5_mode != 2 && shared > 0 && o.T * e->G <= 32 && e->nkv_l >= 8) return;
     const int T = o.T, nkv = e->nkv_l;
     const int sh_tiles = cdiv(shared, P6_KEYS), own_tiles = cdiv(std::max(max_len - shared, 1), P6_KEYS);

@@ -37,6 +37,12 @@ struct TpFusedArgs {
 };
 
 __device__ __forceinline__ void tpf_st_release_sys(int* p, int v) { asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ void tpf_st_relaxed_sys(int* p, int v) { asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ int tpf_ld_relaxed_sys(const int* p) {
+    int v;
+    asm volatile("ld.relaxed.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ int tpf_ld_acquire_sys(const int* p) {
     int v;
     asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -59,17 +65,23 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
         }
         e = __shfl_sync(0xffffffffu, e, 0);
         if ((int)threadIdx.x < a.tp) {
-            __threadfence_system();
-            tpf_st_release_sys(a.flags[threadIdx.x] + cell * TPF_MAX + a.rank, e);
+            // "my partial is ready": it was written by the PREVIOUS kernel on this GPU (complete and visible in this GPU's
+            // L2 once griddepcontrol.wait has returned), and the peers PULL it through that L2 -- so the flag needs no
+            // system-scope release fence in front of it (the fence + release store + acquire polls cost ~4 us of the
+            // 6-8 us this wait took in the in-kernel timeline, profiles/r2_summary.md).  The poll is relaxed; one acquire
+            // load after it orders the pulls below behind the flag.
+            tpf_st_relaxed_sys(a.flags[threadIdx.x] + cell * TPF_MAX + a.rank, e);
+            const int* mine = a.flags[a.rank] + cell * TPF_MAX + threadIdx.x;
             // bounded: a peer that never arrives (a rank that died or left the step) ends this kernel with a trap -- an
-            // error on this rank's stream -- instead of a GPU that spins for ever (2^28 polls ~ a minute)
+            // error on this rank's stream -- instead of a GPU that spins for ever
             long long spins = 0;
-            while (tpf_ld_acquire_sys(a.flags[a.rank] + cell * TPF_MAX + threadIdx.x) < e) {
+            while (tpf_ld_relaxed_sys(mine) < e) {
                 if (++spins > (1ll << 28)) {
                     printf("tp_fused_allreduce_norm: rank %d still waits for rank %d at epoch %d\n", a.rank, (int)threadIdx.x, e);
                     __trap();
                 }
             }
+            (void)tpf_ld_acquire_sys(mine);
         }
     }
     __syncthreads();
