@@ -657,7 +657,7 @@ void engine_init(rt_engine* e) {
     e->pf_q = zalloc_b((size_t)e->pf_cap * e->nq_l * e->hd);
     e->pf_attn = zalloc_h((size_t)e->pf_cap * e->nq_l * e->hd);
     e->pf_act = zalloc_h((size_t)e->pf_cap * e->F_l);
-    if (c.tp_size > 1) e->pf_delta = zalloc_f((size_t)e->pf_cap * e->H);
+    if (c.tp_size > 1) e->pf_delta = zalloc_h((size_t)e->pf_cap * e->H);
     e->pf_inv_rms = zalloc_f(e->pf_cap);
     e->pf_tok = dalloc<int>(e, e->pf_cap);
     e->pf_seq = dalloc<int>(e, e->pf_cap);
@@ -882,7 +882,7 @@ static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, c
         g.out = e->delta; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
         tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
-        rms_xw_kernel<<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, 1, e->inv_rms, H, e->cfg.rms_eps);
+        rms_xw_kernel<float><<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, 1, e->inv_rms, H, e->cfg.rms_eps);
         e->launches += 2;
     }
 }
@@ -1244,10 +1244,12 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
 
             Gemm5Args go{};
             go.ab_f16 = 1; go.S = S; go.N = H; go.K = e->nq_l * hd; go.ldo = H;
-            go.out = e->tp ? e->pf_delta : e->pf_x;
-            pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
-            if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
-            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, w.norm2, e->pf_xn, 0, e->pf_inv_rms, H, e->cfg.rms_eps);
+            // tensor parallel: the partial sums cross NVLink as fp16 (half the bytes of the [S][H] all-reduce; the rounding
+            // is that of every other projection input) and are added to the fp32 residual stream by the norm kernel
+            go.out = e->pf_x; go.out_bf = e->pf_delta; go.ldob = H;
+            pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE16 : G5_EPI_RESID, e->map_attn, e->map_w[4 * l + 1], go);
+            if (e->tp) tp_allreduce_sum_f16(e->tp, e->pf_delta, (size_t)S * H, e->st);
+            rms_xw_kernel<f16><<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, w.norm2, e->pf_xn, 0, e->pf_inv_rms, H, e->cfg.rms_eps);
             e->launches += 2;
 
             Gemm5Args gu{};
@@ -1255,11 +1257,11 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
             pf_gemm(e->st, pdl, G5_EPI_SWIGLU, e->map_xn, e->map_w[4 * l + 2], gu);
             Gemm5Args gd{};
             gd.ab_f16 = 1; gd.S = S; gd.N = H; gd.K = e->F_l; gd.ldo = H;
-            gd.out = e->tp ? e->pf_delta : e->pf_x;
-            pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE : G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
-            if (e->tp) tp_allreduce_sum_f32(e->tp, e->pf_delta, (size_t)S * H, e->st);
+            gd.out = e->pf_x; gd.out_bf = e->pf_delta; gd.ldob = H;
+            pf_gemm(e->st, pdl, e->tp ? G5_EPI_STORE16 : G5_EPI_RESID, e->map_act, e->map_w[4 * l + 3], gd);
+            if (e->tp) tp_allreduce_sum_f16(e->tp, e->pf_delta, (size_t)S * H, e->st);
             const bf16* nw = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;
-            rms_xw_kernel<<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, nw, e->pf_xn, 0, e->pf_inv_rms, H, e->cfg.rms_eps);
+            rms_xw_kernel<f16><<<S, 256, 0, e->st>>>(e->pf_x, e->tp ? e->pf_delta : nullptr, nw, e->pf_xn, 0, e->pf_inv_rms, H, e->cfg.rms_eps);
             e->launches += 3;
         }
         RT_CUDA(cudaGetLastError());

@@ -132,7 +132,7 @@ struct rt_engine {
     float* all_best = nullptr;     // [tp][64 words]
     float* logits_full = nullptr;  // [32][vocab]: all ranks' logits shards, gathered for top-k / top-p sampling
     float* tp_stop = nullptr;      // [1] the ranks' collective "deadline passed" flag
-    float* pf_delta = nullptr;     // [pf_cap][H] partial sums of the row-parallel prefill GEMMs
+    f16* pf_delta = nullptr;       // [pf_cap][H] partial sums of the row-parallel prefill GEMMs, fp16 (what crosses NVLink)
     // fused peer-memory all-reduce (tp_fused.cuh): two partial buffers (O-proj / down-proj call sites), flags, epochs
     bool tpf_on = false;
     float* tpf_delta[2] = {nullptr, nullptr};

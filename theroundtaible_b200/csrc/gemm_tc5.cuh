@@ -221,6 +221,15 @@ __global__ void __launch_bounds__(192, 1) gemm_tc5_kernel(const __grid_constant_
                     }
                     o[i] = x;
                 }
+            } else if (EPI == G5_EPI_STORE16) {
+                uint4* o = reinterpret_cast<uint4*>(a.out_bf + (size_t)m * a.ldob + n0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 p;
+                    p.x = pack_f16(v[8 * i], v[8 * i + 1]); p.y = pack_f16(v[8 * i + 2], v[8 * i + 3]);
+                    p.z = pack_f16(v[8 * i + 4], v[8 * i + 5]); p.w = pack_f16(v[8 * i + 6], v[8 * i + 7]);
+                    o[i] = p;
+                }
             } else if (EPI == G5_EPI_SWIGLU) {
 #pragma unroll
                 for (int t = 0; t < 2; ++t) {

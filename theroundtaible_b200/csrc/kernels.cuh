@@ -108,17 +108,25 @@ static __global__ void bf16_to_f16_kernel(const bf16* __restrict__ in, f16* __re
 
 // Split RMSNorm for the paths that have a whole row in one place (prefill, tensor parallel): x (+= delta) stays fp32,
 // xw = fp16(x * w), inv_rms[t] = rsqrt(mean x^2 + eps).  One CTA per token.
-static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ x, const float* __restrict__ delta,
+template <typename TD>
+static __global__ void __launch_bounds__(256) rms_xw_kernel(float* __restrict__ x, const TD* __restrict__ delta,
                                                             const bf16* __restrict__ w, void* __restrict__ xw, int xf,
                                                             float* __restrict__ inv_rms, int H, float eps) {
     const int t = blockIdx.x;
     float* xr = x + (size_t)t * H;
-    const float* dr = delta ? delta + (size_t)t * H : nullptr;
+    const TD* dr = delta ? delta + (size_t)t * H : nullptr;
     float ss = 0.f;
     for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
         float4 v = *reinterpret_cast<const float4*>(xr + c);
         if (dr) {
-            const float4 d = *reinterpret_cast<const float4*>(dr + c);
+            float4 d;
+            if (sizeof(TD) == 4) {
+                d = *reinterpret_cast<const float4*>(dr + c);
+            } else {                                    // fp16 partial sums (tensor-parallel prefill)
+                const uint2 dh = *reinterpret_cast<const uint2*>(dr + c);
+                const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&dh.x)), d1 = __half22float2(*reinterpret_cast<const __half2*>(&dh.y));
+                d = make_float4(d0.x, d0.y, d1.x, d1.y);
+            }
             v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
             *reinterpret_cast<float4*>(xr + c) = v;
         }

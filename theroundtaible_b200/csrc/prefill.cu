@@ -90,6 +90,7 @@ void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const Pf
         case G5_EPI_QKV: launch_gemm5<PF_BN, G5_EPI_QKV>(st, pdl, A, W, a); break;
         case G5_EPI_RESID: launch_gemm5<PF_BN, G5_EPI_RESID>(st, pdl, A, W, a); break;
         case G5_EPI_SWIGLU: launch_gemm5<PF_BN, G5_EPI_SWIGLU>(st, pdl, A, W, a); break;
+        case G5_EPI_STORE16: launch_gemm5<PF_BN, G5_EPI_STORE16>(st, pdl, A, W, a); break;
         default: launch_gemm5<PF_BN, G5_EPI_STORE>(st, pdl, A, W, a); break;
     }
 }

@@ -10,7 +10,7 @@ struct alignas(64) PfTensorMap {
     unsigned long long opaque[16];
 };
 
-enum { G5_EPI_QKV = 0, G5_EPI_RESID = 1, G5_EPI_SWIGLU = 2, G5_EPI_STORE = 3 };
+enum { G5_EPI_QKV = 0, G5_EPI_RESID = 1, G5_EPI_SWIGLU = 2, G5_EPI_STORE = 3, G5_EPI_STORE16 = 4 };
 
 struct Gemm5Args {
     int S, N, K;
@@ -19,7 +19,7 @@ struct Gemm5Args {
     // RESID: out[m*ldo + n] += acc ; STORE: out[m*ldo + n] = acc
     float* out;
     int ldo;
-    // SWIGLU
+    // SWIGLU: out_bf[m*ldob + n/2] ; STORE16 (tensor parallel: the partial sums that cross NVLink): out_bf[m*ldob + n] = fp16(acc)
     f16* out_bf;              // fp16
     int ldob;
     // QKV

@@ -11,7 +11,7 @@ namespace {
 typedef struct { char internal[128]; } ncclUniqueId_t;
 typedef void* ncclComm_t_;
 typedef int ncclResult_t_;
-enum { NCCL_FLOAT32 = 7, NCCL_INT8 = 0, NCCL_SUM = 0 };
+enum { NCCL_FLOAT32 = 7, NCCL_FLOAT16 = 6, NCCL_INT8 = 0, NCCL_SUM = 0 };
 
 struct Api {
     ncclResult_t_ (*GetUniqueId)(ncclUniqueId_t*) = nullptr;
@@ -89,6 +89,10 @@ void tp_destroy(TpComm* c) {
 
 void tp_allreduce_sum_f32(TpComm* c, float* buf, size_t count, cudaStream_t st) {
     check(api().AllReduce(buf, buf, count, NCCL_FLOAT32, NCCL_SUM, c->comm, st), "ncclAllReduce");
+}
+
+void tp_allreduce_sum_f16(TpComm* c, void* buf, size_t count, cudaStream_t st) {
+    check(api().AllReduce(buf, buf, count, NCCL_FLOAT16, NCCL_SUM, c->comm, st), "ncclAllReduce");
 }
 
 void tp_allgather_bytes(TpComm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st) {

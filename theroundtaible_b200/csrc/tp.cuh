@@ -10,6 +10,7 @@ void tp_unique_id(void* out128);
 TpComm* tp_init(int rank, int size, const void* id128);
 void tp_destroy(TpComm* c);
 void tp_allreduce_sum_f32(TpComm* c, float* buf, size_t count, cudaStream_t st);
+void tp_allreduce_sum_f16(TpComm* c, void* buf, size_t count, cudaStream_t st);
 void tp_allgather_bytes(TpComm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
 // `rows` all-gathers as ONE grouped NCCL launch: row r gathers bytes_per_rank from send + r*send_stride into recv + r*recv_stride
 void tp_allgather_rows(TpComm* c, const void* send, size_t send_stride, void* recv, size_t recv_stride, size_t bytes_per_rank, int rows,
