@@ -543,11 +543,15 @@ def run_b200(args, w):
             except Exception as ex:  # noqa: BLE001
                 extra["discuss"] = {"failed": repr(ex)}
         # DRAM traffic of one decode step as ncu saw it: a committed capture of the same workload, NOT measured in this run
-        traffic, traffic_src = None, None
+        traffic, traffic_src, dom_traffic, dom_traffic_src = None, None, None, None
         try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{args.workload}_tp{tp}")
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            tr = tj.get(f"{args.workload}_tp{tp}")
             if tr and not args.layers:
                 traffic, traffic_src = tr["dram_bytes_per_step"], tr["source"]
+            dk = tj.get(f"dominant_kernel_{args.workload}")
+            if dk and tp == 1 and not args.layers:
+                dom_traffic, dom_traffic_src = dk["dram_bytes_per_launch"], dk["source"]
         except Exception:  # noqa: BLE001
             pass
         par = f"tp{tp}" if tp > 1 else (f"replicas x{world}" if world > 1 else "single GPU")
@@ -565,7 +569,9 @@ def run_b200(args, w):
                          "algorithmic_bytes_per_launch": h["bytes_step"],
                          "dominant_kernel": {"name": f"gemv_kernel<1,MT,EPI_SWIGLU,{nw}> (gate/up projection of one layer)",
                                              "timed": "alone, CUDA events, weights rotated through > 3x L2", "ms": gu_ms,
-                                             "achieved": gu_gbs, "frac": gu_gbs / hbm}},
+                                             "algorithmic_bytes_per_launch": 2 * (cfg.ffn // tp) * cfg.hidden * 2,
+                                             "achieved": gu_gbs, "frac": gu_gbs / hbm, "traffic": dom_traffic,
+                                             "traffic_source": dom_traffic_src}},
             "cpu_baseline": cpu, "e2e": h["e2e"], "gpu_launches": h["launches"], "clocks": h.get("clocks"),
             "prefill": h["prefill"], "extra": extra,
         }

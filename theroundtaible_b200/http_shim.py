@@ -133,8 +133,9 @@ def main():
                     "without it the model has seeded random weights")
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--port", type=int, default=11435)
-    # default window: the "LM Studio" route's fixed 37,152-char source budget + prompt overhead + the reply, in BYTE tokens
-    ap.add_argument("--max-ctx", type=int, default=LMSTUDIO_SOURCE_CHARS + PROMPT_OVERHEAD_TOKENS + 512 + 1024,
+    # default window: the "LM Studio" route's fixed 37,152-char source budget + 12,000 chars of prompt overhead + the reply,
+    # in BYTE tokens (50,688), rounded up
+    ap.add_argument("--max-ctx", type=int, default=51200,
                     help="context window in byte-level tokens (1 per UTF-8 byte).  The unmodified adapter sends up to 37,152 chars "
                          "of source with source='LM Studio', (N-7096)*4 chars with source='Ollama' (N = what /api/show reports, "
                          "scaled down here to fit), and up to 200,000 chars with no source: size this for the route in use")
