@@ -1112,7 +1112,7 @@ static void plan_dec5(rt_engine* e, int max_len, int shared, StepOpts& o) {
     if (dec5_mode != 2 && shared > 0 && o.T * e->G <= 32 && e->nkv_l >= 8) return;
     const int T = o.T, nkv = e->nkv_l;
     const int sh_tiles = cdiv(shared, P6_KEYS), own_tiles = cdiv(std::max(max_len - shared, 1), P6_KEYS);
-    int L = 1;                                             // tiles per item: the smallest that fits one wave
+    int L = std::max(1, env_int("RT_DEC5_MINL", 1));        // tiles per item: the smallest that fits one wave
     auto count = [&](int l) { return nkv * cdiv(sh_tiles, l) + T * nkv * cdiv(own_tiles, l); };
     while (count(L) > e->sm_count && L < 4096) ++L;
     const int n_sh = sh_tiles ? cdiv(sh_tiles, L) : 0, n_own = cdiv(own_tiles, L);

@@ -7,6 +7,8 @@
 // KV pages are read once with 16-byte coalesced loads, reductions are warp shuffles / fixed-order
 // shared-memory sums (deterministic: no atomics anywhere on the data path).
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 #include "gemv.cuh"
 
@@ -597,13 +599,18 @@ static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs
 #pragma unroll
     for (int v = 0; v < VD; ++v) acc[v] = 0.f;
     const float* src = a.part_o + base * HD + lane * VD;
+    // one vector load per lane and partial (a partial row is HD contiguous floats, 16-byte aligned: HD * 4 bytes per row)
+    using VecT = typename std::conditional<VD == 4, float4, typename std::conditional<VD == 2, float2, float>::type>::type;
     for (int i0 = warp; i0 < n; i0 += 64) {
         float pv[16][VD];
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
             const int i = i0 + 4 * j;
+            VecT t{};
+            if (i < n) t = *reinterpret_cast<const VecT*>(src + (size_t)i * HD);
+            const float* tf = reinterpret_cast<const float*>(&t);
 #pragma unroll
-            for (int v = 0; v < VD; ++v) pv[j][v] = i < n ? src[(size_t)i * HD + v] : 0.f;
+            for (int v = 0; v < VD; ++v) pv[j][v] = tf[v];
         }
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
