@@ -41,6 +41,11 @@ T* dalloc(rt_engine* e, size_t n) {
     return reinterpret_cast<T*>(p);
 }
 
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
 double now_ms() {
     using namespace std::chrono;
     return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
@@ -388,16 +393,29 @@ void launch_pdl(rt_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, siz
     e->launches++;
 }
 
+// cluster pair that splits K (gemv.cuh CL = 2): cluster dimension + PDL on the same launch
+template <int EPI, int NW, int HM>
+void gemv_launch_pair(rt_engine* e, const GemvArgs& a, int groups) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * groups);
+    cfg.blockDim = dim3(NW * 32);
+    cfg.stream = e->st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = e->use_pdl ? 2 : 1;
+    RT_CUDA(cudaLaunchKernelEx(&cfg, gemv_kernel<1, 1, EPI, NW, HM, 2>, a));
+    e->launches++;
+}
+
 template <int EPI, int NT, int MT, int NW>
 void gemv_launch(rt_engine* e, const GemvArgs& a, int grid) {
     // <= 4 slots: the hi and lo parts of the activations share one MMA (gemv.cuh HM)
     if (NT == 1 && a.T <= 4) launch_pdl(e, gemv_kernel<1, MT, EPI, NW, 1>, dim3(grid), dim3(NW * 32), 0, a);
     else launch_pdl(e, gemv_kernel<NT, MT, EPI, NW, 0>, dim3(grid), dim3(NW * 32), 0, a);
-}
-
-int env_int(const char* name, int dflt) {
-    const char* v = getenv(name);
-    return v ? atoi(v) : dflt;
 }
 
 // 16 warps only for very long rows (down-projection, K = FFN >= 8192): measured on B200 (scripts/gemv_tune*.py)
@@ -417,6 +435,17 @@ void gemv_pick_warps(rt_engine* e, const GemvArgs& a, int grid) {
 
 template <int EPI>
 int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
+    // few row tiles (the QKV projection of a tensor-parallel shard): a cluster pair of 8-warp CTAs per 16-row tile splits K,
+    // as long as all pairs are resident at once (two such CTAs per SM)
+    static const int pair_on = env_int("RT_GEMV_PAIR", 1);
+    // measured on one GPU with the shards of tensor-parallel models (profiles/r2_summary.md): 32B/TP4 5.42 -> 5.06 ms/step,
+    // 8B/TP4 1.79 -> 1.73, 8B/TP8 1.41 -> 1.38; NOT where a tile already has 16 warps (K >= 8192: 70B/TP8 5.47 -> 5.71)
+    if (EPI == EPI_QKV && pair_on && a.T <= 8 && a.N / 16 <= e->sm_count && (a.K / 32) % 2 == 0 && a.K / 64 >= 8 &&
+        gemv_warps(a.K, a.N / 16) == 8) {
+        if (a.T <= 4) gemv_launch_pair<EPI_QKV, 8, 1>(e, a, a.N / 16);
+        else gemv_launch_pair<EPI_QKV, 8, 0>(e, a, a.N / 16);
+        return a.N / 16;
+    }
     static const int force_mt = env_int("RT_GEMV_MT", 0);
     const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);
     // rows per CTA: the smallest 16*MT that fits the whole matrix into ONE wave of resident CTAs (2 per SM with 8 warps,

@@ -108,9 +108,14 @@ __device__ __forceinline__ float gumbel_noise(unsigned long long seed, int step,
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;"); }
 
-template <int NT, int MT, int EPI, int NW, int HM = 0>
+// CL = 2: a CLUSTER PAIR shares a row group and splits K between its two CTAs; the second CTA adds its reduced tile into the
+// first one's shared memory (distributed shared memory) and the first runs the epilogue.  For matrices with fewer 16-row
+// tiles than half the SMs -- the QKV projection of a tensor-parallel shard: 70B / TP=8 has 80 tiles, 21 MB on 80 of 148 SMs,
+// 10 us in the in-kernel timeline -- it doubles the CTAs that stream the weights.
+template <int NT, int MT, int EPI, int NW, int HM = 0, int CL = 1>
 __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     static_assert(HM == 0 || NT == 1, "the shared-MMA mode serves <= 4 slots");
+    static_assert(CL == 1 || CL == 2, "cluster pair or none");
     static_assert(NT * MT <= 4, "shared-memory reduction sized for NT*MT <= 4");
     // NT = groups of 8 B-operand columns (slots).  HM: one group whose columns 0..3 are the hi part of slots 0..3 and
     // columns 4..7 their lo part.
@@ -121,6 +126,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     constexpr int NTHR = NW * 32;
     __shared__ float4 red[NW][MT * NT][32];
     __shared__ float res[MT * NT][16][8];
+    __shared__ float res_peer[CL > 1 ? MT * NT : 1][16][8];       // CL = 2: written by the pair's second CTA
     __shared__ float s_rn[SL];
     __shared__ int s_last;
 
@@ -129,11 +135,14 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     // single-wave case; several for the matrices with more tiles than two CTAs per SM can hold at once -- lm_head, the
     // 8B+ gate/up -- where the host launches a persistent grid and the first weights of the NEXT group are requested
     // before this group's reduction and epilogue, so the weight stream never pauses at a group boundary).
-    int tile0 = blockIdx.x * MT;
+    const int crank = CL > 1 ? (int)cl_rank() : 0;
+    const int n_groups_grid = (int)gridDim.x / CL;        // row groups the grid covers at once
+    int tile0 = ((int)blockIdx.x / CL) * MT;
     int row0 = tile0 * 16;
     const int n_tiles = a.N >> 4;
     const int nkb = a.K >> 5;
-    const int kb0 = (warp * nkb) / NW, kb1 = ((warp + 1) * nkb) / NW;
+    const int nkb_r = nkb / CL;                            // this CTA's share of K (host: nkb % CL == 0)
+    const int kb0 = crank * nkb_r + (warp * nkb_r) / NW, kb1 = crank * nkb_r + ((warp + 1) * nkb_r) / NW;
 
     // lane's byte offset inside a 512-byte half: piece (q*8 + g)
     const bf16* wbase[MT];
@@ -296,7 +305,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 
     // this CTA's own weights are in: ask for its slice of a later kernel's (the reduction, the epilogue and the gap
     // before the next launch then overlap with HBM traffic instead of leaving it idle)
-    const int next_tile0 = tile0 + (int)gridDim.x * MT;
+    const int next_tile0 = tile0 + n_groups_grid * MT;
     const bool more = next_tile0 < n_tiles;          // block-uniform
     if (more) first_batch(next_tile0);               // in flight during this group's reduction and epilogue
     else if (threadIdx.x == 0) l2_prefetch_slice(a.pf, blockIdx.x, gridDim.x);
@@ -326,8 +335,22 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     }
     __syncthreads();
     RT_TR(EPI * 10 + 3);
+    if (CL > 1) {
+        // the second CTA of the pair hands its half-K sums to the first through distributed shared memory
+        if (crank == 1) {
+            const uint32_t dst = cl_mapa(smem_u32(&res_peer[0][0][0]), 0);
+            for (int e = threadIdx.x; e < MT * NT * 128; e += NTHR) cl_st_f32(dst + 4 * e, (&res[0][0][0])[e]);
+        }
+        cl_sync();
+        if (crank == 0) {
+            for (int e = threadIdx.x; e < MT * NT * 128; e += NTHR) (&res[0][0][0])[e] += (&res_peer[0][0][0])[e];
+        }
+        __syncthreads();
+    }
 
-    if (EPI == EPI_STORE) {
+    if (CL > 1 && crank != 0) {
+        // nothing to write: only the pair's first CTA runs the epilogue
+    } else if (EPI == EPI_STORE) {
         for (int e = threadIdx.x; e < MT * 16 * SL; e += NTHR) {
             const int r = e % (MT * 16), s = e / (MT * 16);
             const int n = row0 + r;
@@ -451,6 +474,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     if (!more) break;
     tile0 = next_tile0;
     row0 = tile0 * 16;
+    if (CL > 1) cl_sync();                           // the first CTA has read res_peer before the second refills it
     __syncthreads();                                 // red / res are reused by the next group
     }
 
