@@ -41,6 +41,7 @@ struct Attn3Args {
     bf16* out;                  // normalised output = the O-projection's input: XF layout over ldo columns (common.cuh)
     int ldo;
     int early;                  // index setup and old KV pages before the PDL wait (see AttnArgs.early)
+    int raw;                    // 1: `out` in the XF16 form (common.cuh xf_store4)
 };
 
 template <int HD>
@@ -299,6 +300,6 @@ __global__ void __launch_bounds__(A3_WARPS * 32, 1) attn_decode3_kernel(const At
         }
         const float inv = 1.0f / L;
         const float y[4] = {acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv};
-        xf_store4(a.out, a.ldo, slot, (h * G + row) * HD + d4, y);
+        xf_store4(a.out, a.ldo, slot, (h * G + row) * HD + d4, y, a.raw);
     }
 }

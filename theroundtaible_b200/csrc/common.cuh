@@ -70,18 +70,28 @@ __device__ __forceinline__ void split_f16x2(float a, float b, uint32_t& hi, uint
     hi = pack_bf16(ha, hb);
     lo = pack_bf16(ha - bf16lo(hi), hb - bf16hi(hi));
 }
-__device__ __forceinline__ void xf_store1(bf16* base, int K, int slot, int k, float v) {
+// `raw` (XF16 form): the fp16 value itself goes into the hi position and the lo position is not written -- what the
+// projections read when their weights are the fp16 twins (gemv.cuh mode 2: one f16 x f16 MMA per fragment)
+__device__ __forceinline__ void xf_store1(bf16* base, int K, int slot, int k, float v, int raw = 0) {
+    const size_t i = xf_index(slot, k, K);
+    if (raw) {
+        reinterpret_cast<f16*>(base)[i] = to_f16(v);
+        return;
+    }
     const float h = __half2float(__float2half_rn(sat_f16(v)));
     const bf16 hi = __float2bfloat16_rn(h);
-    const size_t i = xf_index(slot, k, K);
     base[i] = hi;
     base[i + 256] = __float2bfloat16_rn(h - __bfloat162float(hi));
 }
-__device__ __forceinline__ void xf_store4(bf16* base, int K, int slot, int k, const float (&y)[4]) {   // k % 4 == 0
+__device__ __forceinline__ void xf_store4(bf16* base, int K, int slot, int k, const float (&y)[4], int raw = 0) {   // k % 4 == 0
+    const size_t i = xf_index(slot, k, K);
+    if (raw) {
+        *reinterpret_cast<uint2*>(base + i) = make_uint2(pack_f16(y[0], y[1]), pack_f16(y[2], y[3]));
+        return;
+    }
     uint2 h, l;
     split_f16x2(y[0], y[1], h.x, l.x);
     split_f16x2(y[2], y[3], h.y, l.y);
-    const size_t i = xf_index(slot, k, K);
     *reinterpret_cast<uint2*>(base + i) = h;
     *reinterpret_cast<uint2*>(base + i + 256) = l;
 }
@@ -156,6 +166,15 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint3
                                                uint32_t b0, uint32_t b1) {
     asm volatile(
         "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// the same shape with fp16 operands (decode projections over the fp16 weight twins)
+__device__ __forceinline__ void mma_f16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                              uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
         : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }

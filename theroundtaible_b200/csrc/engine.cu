@@ -394,7 +394,7 @@ void launch_pdl(rt_engine* e, void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 }
 
 // cluster pair that splits K (gemv.cuh CL = 2): cluster dimension + PDL on the same launch
-template <int EPI, int NW, int HM>
+template <int EPI, int NW, int XM>
 void gemv_launch_pair(rt_engine* e, const GemvArgs& a, int groups) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(2 * groups);
@@ -407,14 +407,15 @@ void gemv_launch_pair(rt_engine* e, const GemvArgs& a, int groups) {
     at[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = e->use_pdl ? 2 : 1;
-    RT_CUDA(cudaLaunchKernelEx(&cfg, gemv_kernel<1, 1, EPI, NW, HM, 2>, a));
+    RT_CUDA(cudaLaunchKernelEx(&cfg, gemv_kernel<1, 1, EPI, NW, XM, 2>, a));
     e->launches++;
 }
 
 template <int EPI, int NT, int MT, int NW>
 void gemv_launch(rt_engine* e, const GemvArgs& a, int grid) {
-    // <= 4 slots: the hi and lo parts of the activations share one MMA (gemv.cuh HM)
-    if (NT == 1 && a.T <= 4) launch_pdl(e, gemv_kernel<1, MT, EPI, NW, 1>, dim3(grid), dim3(NW * 32), 0, a);
+    // fp16 twins (gemv.cuh mode 2); otherwise, with <= 4 slots, the hi and lo parts of the activations share one MMA (mode 1)
+    if (NT == 1 && a.f16) launch_pdl(e, gemv_kernel<1, MT, EPI, NW, 2>, dim3(grid), dim3(NW * 32), 0, a);
+    else if (NT == 1 && a.T <= 4) launch_pdl(e, gemv_kernel<1, MT, EPI, NW, 1>, dim3(grid), dim3(NW * 32), 0, a);
     else launch_pdl(e, gemv_kernel<NT, MT, EPI, NW, 0>, dim3(grid), dim3(NW * 32), 0, a);
 }
 
@@ -442,11 +443,13 @@ int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
     // 8B/TP4 1.79 -> 1.73, 8B/TP8 1.41 -> 1.38; NOT where a tile already has 16 warps (K >= 8192: 70B/TP8 5.47 -> 5.71)
     if (EPI == EPI_QKV && pair_on && a.T <= 8 && a.N / 16 <= e->sm_count && (a.K / 32) % 2 == 0 && a.K / 64 >= 8 &&
         gemv_warps(a.K, a.N / 16) == 8) {
-        if (a.T <= 4) gemv_launch_pair<EPI_QKV, 8, 1>(e, a, a.N / 16);
+        if (a.f16) gemv_launch_pair<EPI_QKV, 8, 2>(e, a, a.N / 16);
+        else if (a.T <= 4) gemv_launch_pair<EPI_QKV, 8, 1>(e, a, a.N / 16);
         else gemv_launch_pair<EPI_QKV, 8, 0>(e, a, a.N / 16);
         return a.N / 16;
     }
     static const int force_mt = env_int("RT_GEMV_MT", 0);
+    RT_REQUIRE(!a.f16 || a.T <= 8, "the fp16-twin projection mode serves <= 8 slots");
     const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);
     // rows per CTA: the smallest 16*MT that fits the whole matrix into ONE wave of resident CTAs (2 per SM with 8 warps,
     // 1 per SM with 16 warps); matrices that need several waves anyway take 32-row CTAs, the lm_head 64-row CTAs
@@ -716,6 +719,12 @@ void engine_init(rt_engine* e) {
             pf_make_map_w(&e->map_w[4 * l + 2], w.wgu16, 2 * e->F_l, e->H, PF_BN);
             pf_make_map_w(&e->map_w[4 * l + 3], w.wdown16, e->H, e->F_l, PF_BN);
         }
+        // the decode projections read the twins too when a step has 5..8 slots (gemv.cuh mode 2): the lm_head then needs one
+        e->dec_f16 = env_int("RT_DEC_F16", 1) != 0;
+        if (e->dec_f16) {
+            e->lm_head16 = dalloc<f16>(e, (size_t)e->vocab_l * e->H);
+            bf16_to_f16_kernel<<<e->sm_count * 4, 256, 0, e->st>>>(e->lm_head, e->lm_head16, (size_t)e->vocab_l * e->H / 8);
+        }
         RT_CUDA(cudaGetLastError());
         // tcgen05 prefill attention (attn_prefill_tc5.cuh): head_dim 128, a q-head group that fits 128 rows
         // head_dim 64 also runs (RT_PFA_TC5=2) but gains nothing measurable: the kernel is softmax-paced and a 64-dim head
@@ -892,6 +901,10 @@ void engine_set_slots(rt_engine* e, const int* tok, const int* seq, const int* p
     RT_CUDA(cudaMemcpyAsync(e->d_pos, e->h_stage + 2 * MAX_SLOTS, T * sizeof(int), cudaMemcpyHostToDevice, e->st));
 }
 
+// 5..8 token slots: the decode projections read the fp16 twins of the weights and the activations travel in the XF16 form
+// (gemv.cuh mode 2); <= 4 slots keep the bf16 weights (hi and lo share one MMA there, nothing to gain)
+static inline int xf_mode(const rt_engine* e, int T) { return (e->dec_f16 && T > 4 && T <= 8) ? 2 : 1; }
+
 // row-parallel projection under tensor parallelism: partial sums -> all-reduce -> residual add -> RMSNorm.
 // Fused path: ONE kernel pulls every rank's partial over NVLink peer memory (tp_fused.cuh); otherwise NCCL + rmsnorm.
 static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, const bf16* norm_w) {
@@ -905,13 +918,13 @@ static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, c
             a.flags[p] = reinterpret_cast<int*>(e->tpf_peer_flags[p]);
         }
         a.epoch = e->tpf_epoch; a.rank = e->cfg.tp_rank; a.tp = e->cfg.tp_size; a.H = H;
-        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.ss_part = e->ss_part;
+        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.ss_part = e->ss_part; a.raw = g.f16;
         launch_pdl(e, tp_fused_allreduce_norm_kernel, dim3(cdiv(H / 4, TPF_THREADS), T), dim3(TPF_THREADS), 0, a);
     } else {
         g.out = e->delta; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
         tp_allreduce_sum_f32(e->tp, e->delta, (size_t)T * H, e->st);
-        rms_xw_kernel<float><<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, 1, e->inv_rms, H, e->cfg.rms_eps);
+        rms_xw_kernel<float><<<T, 256, 0, e->st>>>(e->x, e->delta, norm_w, e->xn, g.f16 ? 2 : 1, e->inv_rms, H, e->cfg.rms_eps);
         e->launches += 2;
     }
 }
@@ -950,7 +963,8 @@ static void lm_head_and_sample(rt_engine* e, int T, bool sample, bool advance, b
         return;
     }
     GemvArgs gl{};
-    gl.W = e->lm_head; gl.N = e->vocab_l; gl.K = e->H; gl.T = T; gl.X = e->xn; gl.ldx = e->H;
+    gl.f16 = xf_mode(e, T) == 2;
+    gl.W = gl.f16 ? reinterpret_cast<const bf16*>(e->lm_head16) : e->lm_head; gl.N = e->vocab_l; gl.K = e->H; gl.T = T; gl.X = e->xn; gl.ldx = e->H;
     set_norm_scale(e, gl, direct_scale);
     gl.logits = store_logits ? e->logits : nullptr; gl.ld_logits = e->vocab_l;
     gl.cta_max = e->cta_max; gl.cta_idx = e->cta_idx; gl.row_offset = e->cfg.tp_rank * e->vocab_l;
@@ -990,17 +1004,21 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
     static const int skip = env_int("RT_SKIP_MASK", 0);
 
     launch_pdl(e, embed_norm_kernel, dim3(T), dim3(256), 0, (const bf16*)e->embed, (const int*)e->d_tok, e->x,
-               (const bf16*)e->layers[0].norm1, (void*)e->xn, 1, e->ss_part, e->inv_rms, H, e->vocab, e->cfg.rms_eps);
+               (const bf16*)e->layers[0].norm1, (void*)e->xn, xf_mode(e, T), e->ss_part, e->inv_rms, H, e->vocab, e->cfg.rms_eps);
+    const int raw = xf_mode(e, T) == 2;
+    // the matrix a projection streams (and the one a kernel before it pulls into L2): the bf16 original or its fp16 twin
+    auto wsel = [raw](const bf16* w, const f16* w16) { return raw ? reinterpret_cast<const bf16*>(w16) : w; };
 
     for (int l = 0; l < e->L; ++l) {
         const LayerW& w = e->layers[l];
+        const bf16 *Wqkv = wsel(w.wqkv, w.wqkv16), *Wo = wsel(w.wo, w.wo16), *Wgu = wsel(w.wgu, w.wgu16), *Wdown = wsel(w.wdown, w.wdown16);
         bf16* kp = e->kpool + (size_t)l * e->layer_pool_elems;
         bf16* vp = e->vpool + (size_t)l * e->layer_pool_elems;
 
         static const int late = env_int("RT_QKV_LATE_LAUNCH", 0);
         GemvArgs g{};
         set_norm_scale(e, g, /*direct=*/l == 0 && e->tp != nullptr);     // tensor parallel: layer 0 takes r from the embed kernel
-        g.W = w.wqkv; g.N = e->qkv_rows; g.K = H; g.T = T; g.X = e->xn; g.ldx = H;
+        g.W = Wqkv; g.f16 = raw; g.N = e->qkv_rows; g.K = H; g.T = T; g.X = e->xn; g.ldx = H;
         g.bias = w.bqkv; g.cos_t = e->cos_t; g.sin_t = e->sin_t; g.slot_seq = e->d_seq; g.slot_pos = e->d_pos;
         g.page_table = e->d_page_table; g.pt_stride = e->max_pages_per_seq; g.Q = e->qb; g.Kp = kp; g.Vp = vp;
         g.n_q = e->nq_l; g.n_kv = e->nkv_l; g.hd = hd;
@@ -1023,14 +1041,14 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         // sampler advanced slot_pos, has completed), or after a QKV projection that releases it late (gemv.cuh).
         static const int attn_early = env_int("RT_ATTN_EARLY", 1);
         a.early = attn_early && !(skip & 2) && (o.in_graph || late);
-        a.pf[0] = {w.wo, pf_wo};
-        a.pf[1] = {w.wgu, pf_wgu};
+        a.pf[0] = {Wo, pf_wo};
+        a.pf[1] = {Wgu, pf_wgu};
         if (!(skip & 4)) {
             if (o.attn3_cs > 0 && T <= 8) {
                 Attn3Args a3{};
                 a3.Q = a.Q; a3.ldq = a.ldq; a3.Kp = kp; a3.Vp = vp; a3.page_table = a.page_table; a3.pt_stride = a.pt_stride;
                 a3.slot_seq = a.slot_seq; a3.slot_pos = a.slot_pos; a3.T = T; a3.n_q = a.n_q; a3.n_kv = a.n_kv;
-                a3.scale_log2 = a.scale_log2; a3.out = e->attn_bf; a3.ldo = e->nq_l * hd; a3.early = a.early;
+                a3.scale_log2 = a.scale_log2; a3.out = e->attn_bf; a3.ldo = e->nq_l * hd; a3.early = a.early; a3.raw = raw;
                 rt_attn3_host_launch(e, a3, hd, o.attn3_cs);
             } else {
             MergeArgs m{};
@@ -1051,7 +1069,7 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
             }
             m.part_o = e->part_o; m.part_ml = e->part_ml; m.max_chunks = MAX_CHUNKS; m.slot_pos = e->d_pos;
             m.shared_len_ptr = e->d_shared_len;
-            m.n_q = e->nq_l; m.hd = hd; m.out_bf = e->attn_bf; m.out_f32 = nullptr; m.ldo = e->nq_l * hd;
+            m.n_q = e->nq_l; m.hd = hd; m.out_bf = e->attn_bf; m.out_f32 = nullptr; m.ldo = e->nq_l * hd; m.raw = raw;
             const dim3 mg(e->nq_l, T);
             if (hd == 128) launch_pdl(e, attn_merge2_kernel<128>, mg, dim3(128), 0, m);
             else if (hd == 64) launch_pdl(e, attn_merge2_kernel<64>, mg, dim3(128), 0, m);
@@ -1060,8 +1078,8 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         }
 
         GemvArgs go{};
-        go.W = w.wo; go.X = e->attn_bf; go.N = H; go.K = e->nq_l * hd; go.ldx = e->nq_l * hd; go.T = T;
-        if (pf_wgu < wgu_bytes) go.pf = {reinterpret_cast<const char*>(w.wgu) + pf_wgu, std::min(tail, wgu_bytes - pf_wgu)};
+        go.W = Wo; go.f16 = raw; go.X = e->attn_bf; go.N = H; go.K = e->nq_l * hd; go.ldx = e->nq_l * hd; go.T = T;
+        if (pf_wgu < wgu_bytes) go.pf = {reinterpret_cast<const char*>(Wgu) + pf_wgu, std::min(tail, wgu_bytes - pf_wgu)};
         if (!e->tp) {
             go.out = e->x; go.ldo = H;
             go.norm_w = w.norm2; go.xn_out = e->xn; go.ss_out = e->ss_part;
@@ -1071,17 +1089,17 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
         }
 
         GemvArgs gu{};
-        gu.W = w.wgu; gu.N = 2 * e->F_l; gu.K = H; gu.T = T; gu.X = e->xn; gu.ldx = H;
+        gu.W = Wgu; gu.f16 = raw; gu.N = 2 * e->F_l; gu.K = H; gu.T = T; gu.X = e->xn; gu.ldx = H;
         set_norm_scale(e, gu, false);
         gu.out_bf = e->act_bf; gu.ldob = e->F_l;
-        gu.pf = {w.wdown, std::min(tail, wd_bytes)};
+        gu.pf = {Wdown, std::min(tail, wd_bytes)};
         if (!(skip & 16)) gemv_dispatch<EPI_SWIGLU>(e, gu);
 
         GemvArgs gd{};
-        gd.W = w.wdown; gd.X = e->act_bf; gd.N = H; gd.K = e->F_l; gd.ldx = e->F_l; gd.T = T;
+        gd.W = Wdown; gd.f16 = raw; gd.X = e->act_bf; gd.N = H; gd.K = e->F_l; gd.ldx = e->F_l; gd.T = T;
         const bf16* next_norm = (l + 1 < e->L) ? e->layers[l + 1].norm1 : e->final_norm;   // feeds the next layer's QKV, or the lm_head
-        if (l + 1 < e->L) gd.pf = {e->layers[l + 1].wqkv, std::min(tail, wqkv_bytes)};
-        else gd.pf = {e->lm_head, std::min(tail, (size_t)e->vocab_l * H * sizeof(bf16))};
+        if (l + 1 < e->L) gd.pf = {wsel(e->layers[l + 1].wqkv, e->layers[l + 1].wqkv16), std::min(tail, wqkv_bytes)};
+        else gd.pf = {wsel(e->lm_head, e->lm_head16), std::min(tail, (size_t)e->vocab_l * H * sizeof(bf16))};
         if (!e->tp) {
             gd.out = e->x; gd.ldo = H;
             gd.norm_w = next_norm; gd.xn_out = e->xn; gd.ss_out = e->ss_part;
@@ -1299,7 +1317,7 @@ static void prefill_tensor(rt_engine* e, const std::vector<int>& tok, const std:
         auto lm_head_rows = [&](const std::vector<int>& rows, bool sample, bool store) {
             const int T = (int)rows.size();
             GatherRowsArgs ga{};
-            ga.src = e->pf_xn; ga.src_r = e->pf_inv_rms; ga.dst = e->xn; ga.dst_r = e->inv_rms; ga.H = H;
+            ga.src = e->pf_xn; ga.src_r = e->pf_inv_rms; ga.dst = e->xn; ga.dst_r = e->inv_rms; ga.H = H; ga.raw = xf_mode(e, T) == 2;
             for (int j = 0; j < T; ++j) ga.rows[j] = rows[j];
             gather_rows_kernel<<<T, 256, 0, e->st>>>(ga);
             e->launches++;

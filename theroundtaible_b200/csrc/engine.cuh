@@ -60,6 +60,8 @@ struct rt_engine {
     int nq_l = 0, nkv_l = 0, F_l = 0, vocab_l = 0, G = 1, qkv_rows = 0;
 
     bf16 *embed = nullptr, *lm_head = nullptr, *final_norm = nullptr;
+    f16* lm_head16 = nullptr;      // fp16 twin of the lm_head (decode steps with 5..8 slots, gemv.cuh mode 2)
+    bool dec_f16 = false;          // twins exist and RT_DEC_F16 != 0
     std::vector<LayerW> layers;
     std::vector<void*> allocs;     // everything to cudaFree
     float *cos_t = nullptr, *sin_t = nullptr;

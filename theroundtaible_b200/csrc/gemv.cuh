@@ -38,10 +38,11 @@ enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4
 constexpr int KV_PAGE = 16;
 
 struct GemvArgs {
-    const bf16* W;            // CM layout
+    const bf16* W;            // CM layout (mode 2: the fp16 twin, same layout)
     int N, K, T;
     // B operand
     const bf16* X;            // activations of the K input columns in the XF layout (common.cuh): bf16 hi + lo of fp16 values
+    int f16;                  // host side only: 1 = W is the fp16 twin and X / the XF outputs are in the XF16 form (mode 2)
     int ldx;                  // (unused: the XF layout is fixed by K)
     // RMSNorm is split around the projections ("scale after the matmul"): the PRODUCER of the residual stream (RESID
     // epilogue, embed kernel) writes xw = bf16(x * norm_w) per element plus the per-16-row-tile partial sums of x^2; the
@@ -112,8 +113,16 @@ __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.
 // first one's shared memory (distributed shared memory) and the first runs the epilogue.  For matrices with fewer 16-row
 // tiles than half the SMs -- the QKV projection of a tensor-parallel shard: 70B / TP=8 has 80 tiles, 21 MB on 80 of 148 SMs,
 // 10 us in the in-kernel timeline -- it doubles the CTAs that stream the weights.
-template <int NT, int MT, int EPI, int NW, int HM = 0, int CL = 1>
+//
+// XM (activation mode): 0 = bf16 weights, activations as bf16 hi + lo, two MMAs per weight fragment;
+//                       1 = the same with <= 4 slots: hi and lo share one MMA (see the header);
+//                       2 = the fp16 TWINS of the weights (engine.cu: the exact fp16 image of the bf16 matrices, which the prefill
+//                           GEMMs read anyway) x the fp16 activations themselves (XF16 form, common.cuh xf_store*): one f16 MMA
+//                           and one activation load per fragment, the same products.  5..8 slots cost 5-8 % per projection
+//                           in mode 0 (profiles/r2_summary.md); mode 2 takes that back.
+template <int NT, int MT, int EPI, int NW, int XM = 0, int CL = 1>
 __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
+    constexpr int HM = XM == 1, F16 = XM == 2;
     static_assert(HM == 0 || NT == 1, "the shared-MMA mode serves <= 4 slots");
     static_assert(CL == 1 || CL == 2, "cluster pair or none");
     static_assert(NT * MT <= 4, "shared-memory reduction sized for NT*MT <= 4");
@@ -121,8 +130,8 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     // columns 4..7 their lo part.
     constexpr int SL = HM ? 4 : NT * 8;               // slots this instantiation serves
     // k-blocks of weights a warp keeps in flight (registers): W takes 8*U*MT registers, X 4*U*NT
-    constexpr int XP = HM ? 1 : 2;                    // activation loads per (k-block, slot group): HM lanes pick their part
-    constexpr int U = HM ? 8 / MT : (NT == 1 ? (MT == 1 ? 6 : (MT == 2 ? 4 : 2)) : (NT == 2 && MT == 1 ? 4 : 2));
+    constexpr int XP = (HM || F16) ? 1 : 2;           // activation loads per (k-block, slot group): HM lanes pick their part
+    constexpr int U = (HM || (F16 && NT == 1)) ? 8 / MT : (NT == 1 ? (MT == 1 ? 6 : (MT == 2 ? 4 : 2)) : (NT == 2 && MT == 1 ? 4 : 2));
     constexpr int NTHR = NW * 32;
     __shared__ float4 red[NW][MT * NT][32];
     __shared__ float res[MT * NT][16][8];
@@ -279,10 +288,17 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
                     for (int p = 0; p < XP; ++p) {       // hi part, then lo part, into the same accumulator
-                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
-                                       xv[u][nt][p].x, xv[u][nt][p].y);
-                        mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
-                                       xv[u][nt][p].z, xv[u][nt][p].w);
+                        if (F16) {
+                            mma_f16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
+                                          xv[u][nt][p].x, xv[u][nt][p].y);
+                            mma_f16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
+                                          xv[u][nt][p].z, xv[u][nt][p].w);
+                        } else {
+                            mma_bf16_16816(acc[mt][nt], av[u][mt][0].x, av[u][mt][1].x, av[u][mt][0].y, av[u][mt][1].y,
+                                           xv[u][nt][p].x, xv[u][nt][p].y);
+                            mma_bf16_16816(acc[mt][nt], av[u][mt][0].z, av[u][mt][1].z, av[u][mt][0].w, av[u][mt][1].w,
+                                           xv[u][nt][p].z, xv[u][nt][p].w);
+                        }
                     }
         // next batch of weights
         if (kbb + U < kb1) {
@@ -370,7 +386,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 const float v = (first ? pre_f0 : *o) + val(r >> 4, r & 15, s);
                 *o = v;
                 if (a.norm_w) {
-                    xf_store1(a.xn_out, a.N, s, n, v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])));
+                    xf_store1(a.xn_out, a.N, s, n, v * (first ? pre_f1 : __bfloat162float(a.norm_w[n])), F16);
                     // the updated residual goes back (HM: into the hi column, lo column zero) for the sums of squares below
                     if (HM) { res[r >> 4][r & 15][s] = v; res[r >> 4][r & 15][s + 4] = 0.f; }
                     else res[(r >> 4) * NT + (s >> 3)][r & 15][s & 7] = v;
@@ -402,7 +418,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 const float gt = val(mt, rr, s) * s_rn[s];
                 const float up = val(mt, rr + 8, s) * s_rn[s];
                 const float act = gt / (1.0f + expf(-gt)) * up;
-                xf_store1(a.out_bf, a.ldob, s, (n >> 1) + rr, act);
+                xf_store1(a.out_bf, a.ldob, s, (n >> 1) + rr, act, F16);
             }
         }
     } else if (EPI == EPI_QKV) {

@@ -13,10 +13,11 @@
 #include "gemv.cuh"
 
 // a projection input leaves its producer as fp16 (prefill: row-major [rows][K] for the tcgen05 GEMMs) or, for the decode
-// projection kernel, as the bf16 hi + lo of that fp16 value in the XF layout (common.cuh); xf != 0 selects the latter
+// projection kernel, as the bf16 hi + lo of that fp16 value in the XF layout (common.cuh): xf = 1; xf = 2: the XF layout
+// holding the fp16 value itself (XF16 form, for projections over the fp16 weight twins)
 __device__ __forceinline__ void store_act4(void* base, int xf, int K, int row, int k, const float (&y)[4]) {
     if (xf) {
-        xf_store4(reinterpret_cast<bf16*>(base), K, row, k, y);
+        xf_store4(reinterpret_cast<bf16*>(base), K, row, k, y, xf == 2);
     } else {
         uint2 o;
         o.x = pack_f16(y[0], y[1]); o.y = pack_f16(y[2], y[3]);
@@ -31,6 +32,7 @@ struct GatherRowsArgs {
     bf16* dst;             // XF layout over H columns
     float* dst_r;          // [32]
     int H;
+    int raw;               // 1: XF16 form (common.cuh xf_store4)
     int rows[32];
 };
 static __global__ void __launch_bounds__(256) gather_rows_kernel(const GatherRowsArgs a) {
@@ -39,7 +41,7 @@ static __global__ void __launch_bounds__(256) gather_rows_kernel(const GatherRow
         const uint2 v = *reinterpret_cast<const uint2*>(a.src + (size_t)r * a.H + c);
         const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&v.x)), f1 = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
         const float y[4] = {f0.x, f0.y, f1.x, f1.y};
-        xf_store4(a.dst, a.H, t, c, y);
+        xf_store4(a.dst, a.H, t, c, y, a.raw);
     }
     if (threadIdx.x == 0) a.dst_r[t] = a.src_r[r];
 }
@@ -536,6 +538,7 @@ struct MergeArgs {
     bf16* out_bf;      // nullable: the input of the O-projection, XF layout over ldo columns
     float* out_f32;    // nullable  [T][ldo]
     int ldo;
+    int raw;           // 1: out_bf in the XF16 form (common.cuh xf_store1)
 };
 
 static __global__ void attn_merge_kernel(const MergeArgs a) {
@@ -555,7 +558,7 @@ static __global__ void attn_merge_kernel(const MergeArgs a) {
         acc += a.part_o[(base + i) * a.hd + d] * w;
     }
     const float r = acc / L;
-    if (a.out_bf) xf_store1(a.out_bf, a.ldo, t, head * a.hd + d, r);
+    if (a.out_bf) xf_store1(a.out_bf, a.ldo, t, head * a.hd + d, r, a.raw);
     if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * a.hd + d] = r;
 }
 
@@ -632,7 +635,7 @@ static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs
     if (threadIdx.x < HD) {
         const float r = (sacc[0][threadIdx.x] + sacc[1][threadIdx.x]) + (sacc[2][threadIdx.x] + sacc[3][threadIdx.x]);
         const float o = r / sL[0];
-        if (a.out_bf) xf_store1(a.out_bf, a.ldo, t, head * HD + threadIdx.x, o);
+        if (a.out_bf) xf_store1(a.out_bf, a.ldo, t, head * HD + threadIdx.x, o, a.raw);
         if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * HD + threadIdx.x] = o;
     }
     RT_TR(64);

@@ -34,6 +34,7 @@ struct TpFusedArgs {
     const bf16* norm_w;
     bf16* xn;                        // local, XF layout over H columns: xw = fp16(x * w) as bf16 hi + lo (gemv.cuh)
     float* ss_part;                  // local [gridDim.x][32]: per-column-block sums of x^2 for the consuming projection
+    int raw;                         // 1: xn in the XF16 form (common.cuh xf_store4)
 };
 
 __device__ __forceinline__ void tpf_st_release_sys(int* p, int v) { asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
         *(reinterpret_cast<float4*>(a.x + (size_t)t * a.H) + c4) = acc;
         ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
         const float y[4] = {acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x), acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y)};
-        xf_store4(a.xn, a.H, t, c4 * 4, y);
+        xf_store4(a.xn, a.H, t, c4 * 4, y, a.raw);
     }
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = ss;
