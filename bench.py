@@ -523,6 +523,7 @@ def run_b200(args, w):
         gu_ms = E.k_gemv_bench(2 * cfg.ffn // tp, cfg.hidden, w["knights"], iters=200, device=D.local, epi=2)
         gu_gbs = 2 * (cfg.ffn // tp) * cfg.hidden * 2 / (gu_ms * 1e-3) / 1e9
         nw = 16 if cfg.hidden >= 8192 else 8
+        xm = 2 if 5 <= w["knights"] <= 8 and os.environ.get("RT_DEC_F16", "1") != "0" else (1 if w["knights"] <= 4 else 0)
         cpu = None
         if not args.no_cpu_baseline and world == 1:
             try:
@@ -557,7 +558,8 @@ def run_b200(args, w):
         par = f"tp{tp}" if tp > 1 else (f"replicas x{world}" if world > 1 else "single GPU")
         conf = workload_config(args.workload, w, model, par)
         conf.update({"prefill_ms_per_round": h["prefill_ms"], "decode_ms_per_token_step": h["step_ms"],
-                     "numerics": "bf16 weights / Q / KV, fp16 projection inputs, fp32 accumulate + residual + softmax"})
+                     "numerics": "bf16 weights (the prefill GEMMs and decode steps of 5-8 slots stream their exact fp16 image) / bf16 Q / KV, "
+                                 "fp16 projection inputs, fp32 accumulate + residual + softmax"})
         line = {
             "metric": "decode_tok_per_s", "value": h["value"], "unit": "tok/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": h["ms_per_step"], "higher_is_better": True,
@@ -567,7 +569,8 @@ def run_b200(args, w):
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": h["peak_src"],
                          "of": "decode step on one GPU (one CUDA-graph launch), algorithmic bytes / CUDA-event time",
                          "algorithmic_bytes_per_launch": h["bytes_step"],
-                         "dominant_kernel": {"name": f"gemv_kernel<1,MT,EPI_SWIGLU,{nw}> (gate/up projection of one layer)",
+                         "dominant_kernel": {"name": f"gemv_kernel<1,MT,EPI_SWIGLU,{nw},{xm}> (gate/up projection of one layer; "
+                                                     f"{'fp16 weight twins x fp16 inputs' if xm == 2 else 'bf16 weights x bf16 hi + lo of the fp16 inputs'})",
                                              "timed": "alone, CUDA events, weights rotated through > 3x L2", "ms": gu_ms,
                                              "algorithmic_bytes_per_launch": 2 * (cfg.ffn // tp) * cfg.hidden * 2,
                                              "achieved": gu_gbs, "frac": gu_gbs / hbm, "traffic": dom_traffic,

@@ -193,7 +193,10 @@ RT_API int rt_nccl_unique_id(void* out128);
 RT_API int rt_weights_export(rt_engine* e, int32_t tensor_id, uint16_t* out, int64_t n_elems);
 
 /* y[t][n] = sum_k W[n][k] * x[t][k]; W bf16 bits [N][K], x FP16 bits [T][K] (projection inputs are fp16 in this engine:
- * DESIGN.md 3 "numerics"), y fp32 [T][N]; T <= 32.  The product is exact in both operands, the sum is fp32. */
+ * DESIGN.md 3 "numerics"), y fp32 [T][N]; T <= 32.  The product is exact in both operands, the sum is fp32.
+ * The hook runs the form of the kernel the engine runs for a step of T slots: T = 5..8 streams the fp16 twin of W against
+ * the fp16 inputs themselves, every other T streams the bf16 matrix against the inputs' bf16 hi + lo parts (RT_DEC_F16=0
+ * forces the latter, as in the engine). */
 RT_API int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t K, int32_t T, int32_t device);
 /* y = rmsnorm(x) * w, rounded to bf16: x fp32 [T][H], w bf16 bits [H], y bf16 bits [T][H]. */
 RT_API int rt_k_rmsnorm(const float* x, const uint16_t* w, uint16_t* y, int32_t T, int32_t H, float eps, int32_t device);
@@ -214,7 +217,8 @@ RT_API int rt_k_attention(const uint16_t* q, const uint16_t* k, const uint16_t* 
 RT_API int rt_k_gemm_tc5(const uint16_t* a, const uint16_t* w, float* c, int32_t S, int32_t N, int32_t K, int32_t device);
 /* Time `iters` back-to-back launches of the decode projection kernel on an [N][K] bf16 matrix that is re-streamed
  * from HBM (rotating over enough copies to exceed L2); epi 0 = plain store, 2 = the fused SwiGLU epilogue of the
- * gate/up projection (the dominant kernel of a decode step); returns mean ms per launch. */
+ * gate/up projection (the dominant kernel of a decode step); returns mean ms per launch.  Same choice of kernel form by
+ * T as rt_k_gemv. */
 RT_API int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t epi, int32_t device, double* ms_out);
 
 /* Paged GQA decode attention for callers that must not allocate.  It has no counterpart in the

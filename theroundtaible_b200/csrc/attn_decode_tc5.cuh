@@ -84,6 +84,7 @@ struct Dec5Args {
     float* part_o;          // [T][n_q][max_chunks][hd]
     float* part_ml;         // [T][n_q][max_chunks][2]
     int max_chunks;
+    int early;              // key ranges and old K/V tiles before the PDL wait (see AttnArgs.early)
 };
 
 template <int HD>
@@ -132,59 +133,81 @@ __global__ void __launch_bounds__(D5_THREADS, 1) attn_decode_tc5_kernel(const __
 
     griddep_launch();
     RT_TR(85);
+
+    // The key range of the item.  `early` (the caller says: inside the decode graph, where the positions only change between
+    // steps): worked out BEFORE the PDL wait, and the K/V tiles that cannot hold the key this step appends -- all of a shared
+    // item, all but the last tile of the own item that reaches the current position -- are requested there too, so that
+    // only Q (and that one tile) is fetched behind the QKV projection.
+    int shared = 0, seq = 0, key0 = 0, key1 = 0, n_safe = 0;
+    auto ranges = [&]() {
+        shared = a.shared_len_ptr ? *a.shared_len_ptr : 0;
+        if (it.slot < 0) {
+            seq = a.slot_seq[0];
+            key0 = it.key0;
+            key1 = min(key0 + it.span, shared);
+            n_safe = 1 << 30;
+        } else {
+            const int pos = a.slot_pos[it.slot];
+            seq = a.slot_seq[it.slot];
+            key0 = shared + it.key0;
+            key1 = min(key0 + it.span, pos + 1);
+            n_safe = key0 + it.span > pos ? (max(key1 - key0, 0) + P6_KEYS - 1) / P6_KEYS - 1 : 1 << 30;
+        }
+    };
+    if (a.early) ranges();
+    constexpr int PPT = P6_KEYS / KV_PAGE;
+    int* spt = reinterpret_cast<int*>(gen + (xchg - sbase) + D5_PARTS * 512);
+    // tile j of the item -> its ring stage (one K/V box per lane: 16 boxes of a tile issued by 16 lanes at once.  Issued one
+    // after the other by a single lane they took ~1.2 us per tile in the in-kernel trace and paced the whole pipeline)
+    auto issue_tile = [&](int j, int n_pages, const int* pt) {
+        if ((j & 31) == 0) {
+            // the page ids of the next 32 tiles are fetched by the whole warp at once into shared memory: read one by one by
+            // the issuing lane, every id is a dependent global load in front of its TMA (four per tile, ~2 us a tile)
+            __syncwarp();
+            for (int i = lane; i < 32 * PPT; i += 32) spt[i] = (j * PPT + i < n_pages) ? pt[j * PPT + i] : 0;
+            __syncwarp();
+        }
+        const int s = j % P6_STAGES;
+        if (lane == 0) {
+            p5_wait(b_kve + 8 * s, ((j / P6_STAGES) & 1) ^ 1);
+            mbar_expect_tx(b_kvf + 8 * s, (uint32_t)min(PPT, n_pages - j * PPT) * (uint32_t)(NH * 4096));
+            RT_TR1(82);
+        }
+        __syncwarp();
+        const int npg = min(PPT, n_pages - j * PPT);
+        const uint32_t st = s_kv + s * STAGE;
+        if (lane < npg * 2 * NH) {
+            const int p = lane / (2 * NH), c = (lane % (2 * NH)) >> 1, is_v = lane & 1;
+            const int page = spt[(j & 31) * PPT + p];
+            const int row = ((a.layer * a.n_pages_pool + page) * a.n_kv + it.h) * KV_PAGE;
+            tma_load_2d(st + (is_v * NH + c) * P6_TILE_BYTES + p * (KV_PAGE * 128), is_v ? &map_v : &map_k, b_kvf + 8 * s, c * 64, row);
+        }
+    };
+    int n_pre = 0;
+    if (a.early && warp == 0) {
+        const int nk = max(key1 - key0, 0), npg = (nk + KV_PAGE - 1) / KV_PAGE, nt = (nk + P6_KEYS - 1) / P6_KEYS;
+        const int* pt = a.page_table + (size_t)seq * a.pt_stride + key0 / KV_PAGE;
+        n_pre = max(min(min(nt, n_safe), P6_STAGES), 0);
+        for (int j = 0; j < n_pre; ++j) issue_tile(j, npg, pt);
+    }
     griddep_wait();                                   // Q and the newest K/V come from the QKV projection of this layer
     RT_TR(81);
+    if (!a.early) ranges();
 
-    const int shared = a.shared_len_ptr ? *a.shared_len_ptr : 0;
-    int seq, key0, key1;
-    if (it.slot < 0) {
-        seq = a.slot_seq[0];
-        key0 = it.key0;
-        key1 = min(key0 + it.span, shared);
-    } else {
-        seq = a.slot_seq[it.slot];
-        key0 = shared + it.key0;
-        key1 = min(key0 + it.span, a.slot_pos[it.slot] + 1);
-    }
     const int n_keys = max(key1 - key0, 0);           // 0: nothing to do (the sequence has not reached this range)
     const int n_pages = (n_keys + KV_PAGE - 1) / KV_PAGE;
     const int n_tiles = (n_keys + P6_KEYS - 1) / P6_KEYS;
-    constexpr int PPT = P6_KEYS / KV_PAGE;
     const int page0 = key0 / KV_PAGE;                 // key0 is page aligned (the shared length and the spans are)
 
     if (warp == 0) {
         if (n_tiles > 0) {
             const int* pt = a.page_table + (size_t)seq * a.pt_stride + page0;
-            // the page ids of the next 32 tiles are fetched by the whole warp at once into shared memory: read one by one by
-            // the issuing lane, every id is a dependent global load in front of its TMA (four per tile, ~2 us a tile)
-            int* spt = reinterpret_cast<int*>(gen + (xchg - sbase) + D5_PARTS * 512);
             if (lane == 0) {
                 mbar_expect_tx(b_q, (uint32_t)NH * 64u * (uint32_t)a.G * (uint32_t)a.BT * 2u);
                 for (int c = 0; c < NH; ++c) p5_tma_3d(s_q + c * P5_HALF_BYTES, &map_q, b_q, c * 64, it.h * a.G, 0);
             }
-            for (int j = 0; j < n_tiles; ++j) {
-                if ((j & 31) == 0) {
-                    __syncwarp();
-                    for (int i = lane; i < 32 * PPT; i += 32) spt[i] = (j * PPT + i < n_pages) ? pt[j * PPT + i] : 0;
-                    __syncwarp();
-                }
-                // one box per lane: 16 K/V boxes of a tile issued by 16 lanes at once.  Issued one after the other by a single
-                // lane they took ~1.2 us per tile (in-kernel trace) and paced the whole pipeline
-                const int s = j % P6_STAGES;
-                if (lane == 0) {
-                    p5_wait(b_kve + 8 * s, ((j / P6_STAGES) & 1) ^ 1);
-                    mbar_expect_tx(b_kvf + 8 * s, (uint32_t)min(PPT, n_pages - j * PPT) * (uint32_t)(NH * 4096));
-                    RT_TR1(82);
-                }
-                __syncwarp();
-                const int npg = min(PPT, n_pages - j * PPT);
-                const uint32_t st = s_kv + s * STAGE;
-                if (lane < npg * 2 * NH) {
-                    const int p = lane / (2 * NH), c = (lane % (2 * NH)) >> 1, is_v = lane & 1;
-                    const int page = spt[(j & 31) * PPT + p];
-                    const int row = ((a.layer * a.n_pages_pool + page) * a.n_kv + it.h) * KV_PAGE;
-                    tma_load_2d(st + (is_v * NH + c) * P6_TILE_BYTES + p * (KV_PAGE * 128), is_v ? &map_v : &map_k, b_kvf + 8 * s, c * 64, row);
-                }
+            for (int j = n_pre; j < n_tiles; ++j) {
+                issue_tile(j, n_pages, pt);
             }
         }
     } else if (warp == 1) {

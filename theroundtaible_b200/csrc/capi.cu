@@ -272,6 +272,12 @@ struct Scratch {
 
 extern "C" {
 
+// the projection hooks follow the engine's rule for which form of the kernel a step of T slots runs (engine.cu xf_mode)
+static bool gemv_hook_twin(int T) {
+    const char* v = getenv("RT_DEC_F16");
+    return T > 4 && T <= 8 && !(v && atoi(v) == 0);
+}
+
 int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t K, int32_t T, int32_t device) {
     return guard(nullptr, [&] {
         RT_REQUIRE(w && x && y, "null argument");
@@ -282,10 +288,18 @@ int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t
         float* dy = s.alloc<float>((size_t)MAX_SLOTS * N);
         std::vector<uint16_t> cm((size_t)N * K);
         wgen::rowmajor_to_cm(w, cm.data(), N, K);     // the kernel streams the core-matrix-major layout (gemv.cuh)
-        // the fp16 inputs as the engine's producers store them: bf16 hi + lo in the XF layout (common.cuh)
+        // the engine's own rule (engine.cu xf_mode): 5..8 slots stream the fp16 twin of the matrix against the fp16 inputs
+        // themselves (gemv.cuh mode 2), otherwise the bf16 matrix against their bf16 hi + lo parts; XF layout either way
+        const bool twin = gemv_hook_twin(T);
+        if (twin)
+            for (auto& v : cm) v = __half_as_ushort(__float2half_rn(__bfloat162float(__ushort_as_bfloat16(v))));
         std::vector<bf16> xf(xf_elems(K), __float2bfloat16_rn(0.f));
         for (int t = 0; t < T; ++t)
             for (int k = 0; k < K; ++k) {
+                if (twin) {
+                    xf[xf_index(t, k, K)] = __ushort_as_bfloat16(x[(size_t)t * K + k]);      // the fp16 bits, as they are
+                    continue;
+                }
                 const float h = __half2float(__ushort_as_half(x[(size_t)t * K + k]));
                 const bf16 hi = __float2bfloat16_rn(h);
                 xf[xf_index(t, k, K)] = hi;
@@ -294,7 +308,7 @@ int rt_k_gemv(const uint16_t* w, const uint16_t* x, float* y, int32_t N, int32_t
         RT_CUDA(cudaMemcpyAsync(dw, cm.data(), (size_t)N * K * 2, cudaMemcpyHostToDevice, s.e.st));
         RT_CUDA(cudaMemcpyAsync(dx, xf.data(), xf.size() * 2, cudaMemcpyHostToDevice, s.e.st));
         GemvArgs a{};
-        a.W = dw; a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N;
+        a.W = dw; a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N; a.f16 = twin;
         rt_gemv_host_dispatch(&s.e, a, EPI_STORE);
         RT_CUDA(cudaGetLastError());
         RT_CUDA(cudaMemcpyAsync(y, dy, (size_t)T * N * 4, cudaMemcpyDeviceToHost, s.e.st));
@@ -492,7 +506,7 @@ int rt_k_gemv_bench(int32_t N, int32_t K, int32_t T, int32_t iters, int32_t epi,
         bf16* dx = s.alloc<bf16>(xf_elems(K));
         float* dy = s.alloc<float>((size_t)MAX_SLOTS * N);
         GemvArgs a{};
-        a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N;
+        a.X = dx; a.N = N; a.K = K; a.ldx = K; a.T = T; a.out = dy; a.ldo = N; a.f16 = gemv_hook_twin(T);
         a.out_bf = s.alloc<bf16>(xf_elems(N / 2)); a.ldob = N / 2;               // SwiGLU: gate/up row pairs -> N/2 outputs (XF layout)
         cudaEvent_t e0, e1;
         RT_CUDA(cudaEventCreate(&e0));

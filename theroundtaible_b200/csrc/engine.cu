@@ -461,6 +461,24 @@ int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
     while (mt < mt_max && (tiles + mt - 1) / mt > capacity) mt <<= 1;
     if ((tiles + mt - 1) / mt > capacity) mt = std::min(mt_max, tiles >= 4096 ? 4 : 2);
     while (mt > 1 && a.N % (16 * mt) != 0) mt >>= 1;
+    // balance: the rule above may leave SMs with very different numbers of 16-row tiles (864 tiles as 216 CTAs of 64 rows
+    // on 148 SMs: 68 SMs stream twice what the other 80 do -- Qwen2.5-32B/TP4 gate/up 28.4 us against 23.7 us as a
+    // persistent grid of 16-row groups, scripts/gemv_shard_tune.py).  Take the rows per CTA whose busiest SM has the fewest
+    // tiles, when that is at least a fifth fewer than under the rule above (32B/TP4 shard 4.75 -> 4.58 ms per step, 32B/TP2
+    // 7.56 -> 7.22; a smaller edge did not survive inside the step: Llama-3.1-8B gate/up, 16 -> 14 tiles on the busiest SM, is
+    // 5 % faster alone and 1 % slower per step).
+    static const int balance = env_int("RT_GEMV_BALANCE", 1);
+    if (balance && tiles < 4096) {
+        const int cpsm = capacity / e->sm_count;
+        auto busiest = [&](int m) {
+            const int groups = (tiles + m - 1) / m;
+            return groups <= capacity ? cdiv(groups, e->sm_count) * m : cpsm * cdiv(groups, capacity) * m;
+        };
+        int best = mt;
+        for (int m = mt_max; m >= 1; m >>= 1)
+            if (a.N % (16 * m) == 0 && busiest(m) < busiest(best) && 5 * busiest(m) <= 4 * busiest(mt)) best = m;
+        mt = best;
+    }
     // experiment: instead of growing the CTA until one wave covers the matrix, keep small row groups and walk them
     static const int pmode = env_int("RT_GEMV_PMODE", 0);
     if (pmode && tiles > capacity && pmode * NT <= 4 && a.N % (16 * pmode) == 0) mt = pmode;
@@ -1061,6 +1079,8 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
                 d.shared_len_ptr = e->d_shared_len; d.items = reinterpret_cast<const Dec5Item*>(e->dec5_items_dev);
                 d.T = T; d.n_q = e->nq_l; d.n_kv = e->nkv_l; d.G = e->G; d.BT = e->dec5_bt; d.n_pages_pool = e->n_pages; d.layer = l;
                 d.scale_log2 = a.scale_log2; d.part_o = e->part_o; d.part_ml = e->part_ml; d.max_chunks = MAX_CHUNKS;
+                static const int dec5_early = env_int("RT_DEC5_EARLY", 1);
+                d.early = a.early && dec5_early;
                 pf_attention_dec5(e->st, e->use_pdl, o.dec5_items, e->map_qdec, e->map_kpool, e->map_vpool, d, hd);
                 e->launches++;
                 m.n_sh_parts = o.dec5_nsh; m.chunk_keys = o.dec5_own_span; m.cascade = 1;
@@ -1071,9 +1091,22 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
             m.shared_len_ptr = e->d_shared_len;
             m.n_q = e->nq_l; m.hd = hd; m.out_bf = e->attn_bf; m.out_f32 = nullptr; m.ldo = e->nq_l * hd; m.raw = raw;
             const dim3 mg(e->nq_l, T);
-            if (hd == 128) launch_pdl(e, attn_merge2_kernel<128>, mg, dim3(128), 0, m);
-            else if (hd == 64) launch_pdl(e, attn_merge2_kernel<64>, mg, dim3(128), 0, m);
-            else launch_pdl(e, attn_merge2_kernel<32>, mg, dim3(128), 0, m);
+            m.early = a.early;
+            // many partials per row (long contexts): 16 warps hold all of them in flight at once
+            static const int wide_from = env_int("RT_MERGE_WIDE", 24);
+            const int n_parts = o.dec5_items > 0 ? o.dec5_nsh + o.dec5_nown : o.n_partials_max;
+            // ... when the merge has few CTAs: a wide merge on most SMs keeps the NEXT projection's CTAs from becoming resident
+            // and requesting their first weights early (config 3, 160 CTAs: 3.19 -> 3.30 ms per step with 8 or 16 warps)
+            static const int wide_ctas = env_int("RT_MERGE_WIDE_CTAS", 64);
+            if (n_parts >= wide_from && e->nq_l * T <= wide_ctas) {
+                if (hd == 128) launch_pdl(e, attn_merge2_kernel<128, 16>, mg, dim3(512), 0, m);
+                else if (hd == 64) launch_pdl(e, attn_merge2_kernel<64, 16>, mg, dim3(512), 0, m);
+                else launch_pdl(e, attn_merge2_kernel<32, 16>, mg, dim3(512), 0, m);
+            } else {
+                if (hd == 128) launch_pdl(e, attn_merge2_kernel<128, 4>, mg, dim3(128), 0, m);
+                else if (hd == 64) launch_pdl(e, attn_merge2_kernel<64, 4>, mg, dim3(128), 0, m);
+                else launch_pdl(e, attn_merge2_kernel<32, 4>, mg, dim3(128), 0, m);
+            }
             }
         }
 
@@ -1177,6 +1210,7 @@ static void plan_dec5(rt_engine* e, int max_len, int shared, StepOpts& o) {
     o.dec5_items = n;
     o.dec5_nsh = n_sh;
     o.dec5_own_span = L * P6_KEYS;
+    o.dec5_nown = n_own;
 }
 
 static void check_deadline(rt_engine* e, double t0, uint64_t deadline_ms) {
@@ -1374,7 +1408,7 @@ static cudaGraphExec_t capture_steps(rt_engine* e, const StepOpts& o, int steps,
 
 static void ensure_graph(rt_engine* e, const StepOpts& o) {
     const StepOpts& g = e->graph_opts;
-    if (e->graph_exec && g.dec5_items == o.dec5_items && g.dec5_nsh == o.dec5_nsh && g.dec5_own_span == o.dec5_own_span && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks && g.n_sh == o.n_sh && g.n_own == o.n_own &&
+    if (e->graph_exec && g.dec5_items == o.dec5_items && g.dec5_nsh == o.dec5_nsh && g.dec5_own_span == o.dec5_own_span && g.dec5_nown == o.dec5_nown && g.T == o.T && g.chunk_pages == o.chunk_pages && g.n_chunk_blocks == o.n_chunk_blocks && g.n_sh == o.n_sh && g.n_own == o.n_own &&
         g.n_shared_tiles == o.n_shared_tiles && g.attn3_cs == o.attn3_cs && g.inv_temp == o.inv_temp && g.seed == o.seed && g.top_k == o.top_k && g.top_p == o.top_p)
         return;
     if (e->graph_exec) { cudaGraphExecDestroy(e->graph_exec); e->graph_exec = nullptr; }

@@ -42,7 +42,7 @@ struct StepOpts {
     bool in_graph = false;     // the step is being captured into the decode graph (consecutive steps fully serialised)
     int top_k = 0;             // sampler.cuh; only with inv_temp > 0
     // tcgen05 decode attention for long contexts (attn_decode_tc5.cuh): work items of the call, 0 = not used
-    int dec5_items = 0, dec5_nsh = 0, dec5_own_span = 0;
+    int dec5_items = 0, dec5_nsh = 0, dec5_own_span = 0, dec5_nown = 0;
     float top_p = 0.f;
 };
 

@@ -539,6 +539,7 @@ struct MergeArgs {
     float* out_f32;    // nullable  [T][ldo]
     int ldo;
     int raw;           // 1: out_bf in the XF16 form (common.cuh xf_store1)
+    int early;         // slot_pos / shared_len read before the PDL wait (see AttnArgs.early)
 };
 
 static __global__ void attn_merge_kernel(const MergeArgs a) {
@@ -562,79 +563,95 @@ static __global__ void attn_merge_kernel(const MergeArgs a) {
     if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * a.hd + d] = r;
 }
 
-// Merge for the engine's decode step: one CTA of 4 warps per (slot, q head).  Every warp reads all (m, l) pairs
-// (one round trip), derives the global max and its weights, then accumulates the partial outputs of chunks
-// i = warp, warp+4, ... in batches of 16 independent loads; the 4 warp sums are added in fixed order.
-template <int HD>
-static __global__ void __launch_bounds__(128) attn_merge2_kernel(const MergeArgs a) {
+// Merge for the engine's decode step: one CTA of NWM warps per (slot, q head).  The stage is a chain of dependent round trips
+// on a few KB (index -> (m, l) pairs -> partial outputs), so it is laid out to have as few of them as possible after the
+// PDL wait: the number of partials comes from values that do not change within a step and is read BEFORE the wait when the
+// caller says so (`early`: inside the decode graph); after it every warp requests its partial outputs (chunks i = warp,
+// warp + NWM, ...: with 16 warps ALL <= 136 partials of a row are in flight at once, 9 per warp) and, right behind them, all
+// (m, l) pairs; it derives the global max and the weights while the outputs travel, accumulates, and the warp sums are added
+// in fixed order.  Measured in the in-kernel timeline of tensor-parallel shards (profiles/r2_summary.md): 4 warps walking
+// 130 partials in three dependent batches of 16 took 5.8 us per layer.
+template <int HD, int NWM>
+static __global__ void __launch_bounds__(NWM * 32) attn_merge2_kernel(const MergeArgs a) {
     RT_TR(60);
     griddep_launch();
+    constexpr int VD = HD / 32;
+    constexpr int MAXC = 136;               // MAX_CHUNKS (engine.cuh)
+    constexpr int MAXB = (MAXC + 31) / 32;
+    constexpr int PW = (MAXC + NWM - 1) / NWM > 16 ? 16 : (MAXC + NWM - 1) / NWM;     // partials a warp requests at once
+    __shared__ float sacc[NWM][HD];
+    __shared__ float sL;
+    const int t = blockIdx.y, head = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int len = 0, sh = 0;
+    if (a.early) {
+        len = a.slot_pos[t] + 1;
+        sh = (a.cascade && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
+    }
     griddep_wait();
     RT_TR(61);
-    constexpr int VD = HD / 32;
-    __shared__ float sacc[4][HD];
-    __shared__ float sL[4];
-    const int t = blockIdx.y, head = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int len = a.slot_pos[t] + 1;
-    const int sh = (a.cascade && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
+    if (!a.early) {
+        len = a.slot_pos[t] + 1;
+        sh = (a.cascade && a.shared_len_ptr) ? *a.shared_len_ptr : 0;
+    }
+    if (a.max_len > 0) len = min(len, a.max_len);
     const int C = a.chunk_keys;
-    const int n = (a.n_sh_parts >= 0 ? a.n_sh_parts : (sh + C - 1) / C) + (len - sh + C - 1) / C;
+    const int n = min((a.n_sh_parts >= 0 ? a.n_sh_parts : (sh + C - 1) / C) + (len - sh + C - 1) / C, a.max_chunks);
     const size_t base = ((size_t)t * a.n_q + head) * a.max_chunks;
-    constexpr int MAXB = (136 + 31) / 32;   // MAX_CHUNKS / 32
-    float2 ml[MAXB];
-    float M = -INFINITY;
-#pragma unroll
-    for (int b = 0; b < MAXB; ++b) {
-        const int i = b * 32 + lane;
-        ml[b] = i < n ? *reinterpret_cast<const float2*>(a.part_ml + (base + i) * 2) : make_float2(-INFINITY, 0.f);
-        M = fmaxf(M, ml[b].x);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
-    float L = 0.f;
-#pragma unroll
-    for (int b = 0; b < MAXB; ++b) {
-        ml[b].x = exp2f(ml[b].x - M);   // weight of chunk b*32+lane (0 for absent chunks)
-        L += ml[b].y * ml[b].x;
-    }
-    L = warp_sum(L);
-    float acc[VD];
-#pragma unroll
-    for (int v = 0; v < VD; ++v) acc[v] = 0.f;
     const float* src = a.part_o + base * HD + lane * VD;
     // one vector load per lane and partial (a partial row is HD contiguous floats, 16-byte aligned: HD * 4 bytes per row)
     using VecT = typename std::conditional<VD == 4, float4, typename std::conditional<VD == 2, float2, float>::type>::type;
-    for (int i0 = warp; i0 < n; i0 += 64) {
-        float pv[16][VD];
+    float acc[VD];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const int i = i0 + 4 * j;
-            VecT t{};
-            if (i < n) t = *reinterpret_cast<const VecT*>(src + (size_t)i * HD);
-            const float* tf = reinterpret_cast<const float*>(&t);
+    for (int v = 0; v < VD; ++v) acc[v] = 0.f;
+    float2 ml[MAXB];
+    float M = -INFINITY, L = 0.f;
+    for (int i0 = warp; i0 < n; i0 += NWM * PW) {
+        VecT pv[PW];
 #pragma unroll
-            for (int v = 0; v < VD; ++v) pv[j][v] = tf[v];
+        for (int j = 0; j < PW; ++j) {
+            const int i = i0 + NWM * j;
+            pv[j] = VecT{};
+            if (i < n) pv[j] = *reinterpret_cast<const VecT*>(src + (size_t)i * HD);
+        }
+        if (i0 == warp) {                   // first (usually only) round: the (m, l) pairs travel together with the outputs
+#pragma unroll
+            for (int b = 0; b < MAXB; ++b) {
+                const int i = b * 32 + lane;
+                ml[b] = i < n ? *reinterpret_cast<const float2*>(a.part_ml + (base + i) * 2) : make_float2(-INFINITY, 0.f);
+                M = fmaxf(M, ml[b].x);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+#pragma unroll
+            for (int b = 0; b < MAXB; ++b) {
+                ml[b].x = exp2f(ml[b].x - M);   // weight of chunk b*32+lane (0 for absent chunks)
+                L += ml[b].y * ml[b].x;
+            }
+            L = warp_sum(L);
         }
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const int i = i0 + 4 * j;
+        for (int j = 0; j < PW; ++j) {
+            const int i = i0 + NWM * j;
             float w = 0.f;
 #pragma unroll
             for (int b = 0; b < MAXB; ++b) {
                 const float wb = __shfl_sync(0xffffffffu, ml[b].x, i & 31);
                 if ((i >> 5) == b) w = wb;
             }
+            const float* tf = reinterpret_cast<const float*>(&pv[j]);
 #pragma unroll
-            for (int v = 0; v < VD; ++v) acc[v] += pv[j][v] * w;
+            for (int v = 0; v < VD; ++v) acc[v] += tf[v] * w;
         }
     }
 #pragma unroll
     for (int v = 0; v < VD; ++v) sacc[warp][lane * VD + v] = acc[v];
-    if (lane == 0) sL[warp] = L;
+    if (threadIdx.x == 0) sL = L;           // warp 0 always has a partial (n >= 1)
     __syncthreads();
     if (threadIdx.x < HD) {
-        const float r = (sacc[0][threadIdx.x] + sacc[1][threadIdx.x]) + (sacc[2][threadIdx.x] + sacc[3][threadIdx.x]);
-        const float o = r / sL[0];
+        float r = 0.f;
+#pragma unroll
+        for (int w = 0; w < NWM; ++w) r += sacc[w][threadIdx.x];
+        const float o = r / sL;
         if (a.out_bf) xf_store1(a.out_bf, a.ldo, t, head * HD + threadIdx.x, o, a.raw);
         if (a.out_f32) a.out_f32[(size_t)t * a.ldo + head * HD + threadIdx.x] = o;
     }
