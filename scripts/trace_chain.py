@@ -1,14 +1,14 @@
 """Per-kernel timeline of a stretch of the decode step from the in-kernel trace (build.py --trace, RT_LIB=..., RT_TRACE_FILE=...):
 for every launch -- first CTA start, last release from the PDL wait, last "inputs consumed" mark, last end -- in microseconds
 from the first launch shown.  Kernel kinds (tag / 10): 0 store, 1 resid, 2 swiglu, 3 logits, 4 qkv, 5 attention (mma.sync),
-6 merge, 7 tensor-parallel exchange (72 = every peer's flag seen), 8 attention (tcgen05 decode).
+6 merge, 7 tensor-parallel exchange (72 = every peer's flag / packet seen), 8 attention (tcgen05 decode), 9 push projection.
 usage: trace_chain.py dump.bin [n_launches]"""
 import sys
 import numpy as np
 
 rec = np.fromfile(sys.argv[1], dtype=np.dtype([("t", "<u8"), ("tag", "<i4"), ("cta", "<i4")]))
 rec = rec[np.argsort(rec["t"], kind="stable")]
-names = {0: "store", 1: "resid", 2: "swiglu", 3: "logits", 4: "qkv", 5: "attn", 6: "merge", 7: "tp-xchg", 8: "attn-tc5"}
+names = {0: "store", 1: "resid", 2: "swiglu", 3: "logits", 4: "qkv", 5: "attn", 6: "merge", 7: "tp-xchg", 8: "attn-tc5", 9: "push"}
 kind, ev = rec["tag"] // 10, rec["tag"] % 10
 launches = []
 for k in np.unique(kind):

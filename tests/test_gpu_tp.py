@@ -30,8 +30,10 @@ def _rank_main(rank, tp, nccl_id, name, seed, prompts, n_new, mode, q, env=None)
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 # tiny-qwen has 7 q heads x 32 dims per rank: not a multiple of 64, so its prompts take the slab path (mode 0)
-# third case: the NCCL all-reduce path instead of the fused peer-memory exchange (RT_TP_FUSED=0)
-@pytest.mark.parametrize("name,mode,env", [("tiny-llama", 1, None), ("tiny-qwen", 0, None), ("tiny-llama", 1, {"RT_TP_FUSED": "0"})])
+# third case: the NCCL all-reduce path instead of the fused peer-memory exchange (RT_TP_FUSED=0); fourth: the pull form of the
+# fused exchange for decode steps too (RT_TP_PUSH=0; by default steps of <= 8 slots take the push form, larger ones the pull form)
+@pytest.mark.parametrize("name,mode,env", [("tiny-llama", 1, None), ("tiny-qwen", 0, None), ("tiny-llama", 1, {"RT_TP_FUSED": "0"}),
+                                           ("tiny-qwen", 0, {"RT_TP_PUSH": "0"})])
 def test_tp2_generation_and_logits_match_oracle(name, mode, env):
     a = ARCHS[name]
     rng = np.random.default_rng(11)

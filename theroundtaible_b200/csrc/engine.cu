@@ -692,6 +692,20 @@ void engine_init(rt_engine* e) {
             RT_CUDA(cudaStreamSynchronize(e->st));
             for (int j = 0; j < 2; ++j) tp_ipc_exchange(e->tp, e->tpf_delta[j], e->tpf_peer_delta[j], e->st);
             tp_ipc_exchange(e->tp, e->tpf_flags, e->tpf_peer_flags, e->st);
+            e->tpl_on = env_int("RT_TP_PUSH", 1) != 0;
+            if (e->tpl_on) {
+                for (int j = 0; j < 2; ++j) {
+                    e->tpl_recv[j] = zalloc_f((size_t)c.tp_size * MAX_SLOTS * e->H);          // zero = parity 0 = "no packet yet"
+                    e->tpl_cell_epoch[j] = dalloc<int>(e, MAX_SLOTS * TPF_CMAX);
+                    e->tpl_send_epoch[j] = dalloc<int>(e, MAX_SLOTS);
+                    RT_CUDA(cudaMemsetAsync(e->tpl_cell_epoch[j], 0, MAX_SLOTS * TPF_CMAX * sizeof(int), e->st));
+                    int init[MAX_SLOTS];
+                    for (int t = 0; t < MAX_SLOTS; ++t) init[t] = j == 0 ? 1 : 0;      // site 1 is advanced to 1 before its first use
+                    RT_CUDA(cudaMemcpyAsync(e->tpl_send_epoch[j], init, sizeof(init), cudaMemcpyHostToDevice, e->st));
+                    RT_CUDA(cudaStreamSynchronize(e->st));
+                    tp_ipc_exchange(e->tp, e->tpl_recv[j], e->tpl_peer_recv[j], e->st);
+                }
+            }
             // nobody may raise a flag before every rank has cleared its own: one more collective as a barrier
             tp_allreduce_sum_f32(e->tp, e->loc_best, 64, e->st);
             RT_CUDA(cudaStreamSynchronize(e->st));
@@ -775,6 +789,7 @@ void engine_free(rt_engine* e) {
     if (e->graph_exec_multi) cudaGraphExecDestroy(e->graph_exec_multi);
     if (e->tp && e->tpf_on) {
         for (int j = 0; j < 2; ++j) tp_ipc_close(e->tp, e->tpf_peer_delta[j]);
+        if (e->tpl_on) for (int j = 0; j < 2; ++j) tp_ipc_close(e->tp, e->tpl_peer_recv[j]);
         tp_ipc_close(e->tp, e->tpf_peer_flags);
     }
     tp_destroy(e->tp);
@@ -927,7 +942,17 @@ static inline int xf_mode(const rt_engine* e, int T) { return (e->dec_f16 && T >
 // Fused path: ONE kernel pulls every rank's partial over NVLink peer memory (tp_fused.cuh); otherwise NCCL + rmsnorm.
 static void tp_reduce_residual_norm(rt_engine* e, GemvArgs g, int site, int T, const bf16* norm_w) {
     const int H = e->H;
-    if (e->tpf_on) {
+    if (e->tpl_on && T <= 8 && !g.bias) {
+        // push form: the projection delivers its partial sums into every rank's receive buffer, the receiver does not wait for it
+        g.push_tp = e->cfg.tp_size; g.push_rank = e->cfg.tp_rank; g.push_epoch = e->tpl_send_epoch[site];
+        for (int p = 0; p < e->cfg.tp_size; ++p) g.push_dst[p] = reinterpret_cast<float*>(e->tpl_peer_recv[site][p]);
+        gemv_dispatch<EPI_PUSH>(e, g);
+        TpLLArgs a{};
+        a.recv = e->tpl_recv[site]; a.cell_epoch = e->tpl_cell_epoch[site]; a.next_site_epoch = e->tpl_send_epoch[1 - site];
+        a.rank = e->cfg.tp_rank; a.tp = e->cfg.tp_size; a.H = H;
+        a.x = e->x; a.norm_w = norm_w; a.xn = e->xn; a.ss_part = e->ss_part; a.raw = g.f16;
+        launch_pdl(e, tp_ll_reduce_norm_kernel, dim3(cdiv(H / 4, TPF_THREADS), T), dim3(TPF_THREADS), 0, a);
+    } else if (e->tpf_on) {
         g.out = e->tpf_delta[site]; g.ldo = H;
         gemv_dispatch<EPI_STORE>(e, g);
         TpFusedArgs a{};

@@ -141,6 +141,13 @@ struct rt_engine {
     int *tpf_flags = nullptr, *tpf_epoch = nullptr;
     void* tpf_peer_delta[2][8] = {};
     void* tpf_peer_flags[8] = {};
+    // push form of the exchange (tp_fused.cuh tp_ll_reduce_norm_kernel, <= 8 slots): per call site a receive buffer
+    // [tp][32][H], the receiver CTAs' private run counters, the senders' per-slot epochs
+    bool tpl_on = false;
+    float* tpl_recv[2] = {nullptr, nullptr};
+    void* tpl_peer_recv[2][8] = {};
+    int* tpl_cell_epoch[2] = {nullptr, nullptr};
+    int* tpl_send_epoch[2] = {nullptr, nullptr};
 
     // cached decode graph
     cudaGraphExec_t graph_exec = nullptr;       // one decode step

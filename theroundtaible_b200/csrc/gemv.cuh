@@ -29,11 +29,13 @@
 // Fusions: EPI_QKV    -> + bias, RoPE, q -> bf16 Q buffer, k/v -> bf16 into their KV page;
 //          EPI_RESID  -> x += acc, xw = fp16(x * w_next) (XF layout) and per-tile partial sums of x^2: the next projection applies
 //                        the RMSNorm scale to its accumulators (no RMSNorm launch, no tail);
-//          EPI_SWIGLU -> fp16(silu(gate) * up);   EPI_LOGITS -> logits and per-CTA arg-max candidates.
+//          EPI_SWIGLU -> fp16(silu(gate) * up);   EPI_LOGITS -> logits and per-CTA arg-max candidates;
+//          EPI_PUSH   -> tensor parallel: the partial sums go straight into EVERY rank's receive buffer (peer memory over
+//                        NVLink) as self-validating 16-byte packets (tp_fused.cuh tp_ll_reduce_norm_kernel).
 #pragma once
 #include "common.cuh"
 
-enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4 };
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_LOGITS = 3, EPI_QKV = 4, EPI_PUSH = 5 };
 
 constexpr int KV_PAGE = 16;
 
@@ -43,6 +45,11 @@ struct GemvArgs {
     // B operand
     const bf16* X;            // activations of the K input columns in the XF layout (common.cuh): bf16 hi + lo of fp16 values
     int f16;                  // host side only: 1 = W is the fp16 twin and X / the XF outputs are in the XF16 form (mode 2)
+    // PUSH (tensor parallel, <= 8 slots): every rank's receive buffer of this call site [tp][32][N] (peer-mapped; [rank] = local),
+    // this rank's index, and the per-slot packet epochs of the site [32] (tp_fused.cuh)
+    float* push_dst[8];
+    int push_tp, push_rank;
+    const int* push_epoch;
     int ldx;                  // (unused: the XF layout is fixed by K)
     // RMSNorm is split around the projections ("scale after the matmul"): the PRODUCER of the residual stream (RESID
     // epilogue, embed kernel) writes xw = bf16(x * norm_w) per element plus the per-16-row-tile partial sums of x^2; the
@@ -123,6 +130,7 @@ __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.
 template <int NT, int MT, int EPI, int NW, int XM = 0, int CL = 1>
 __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     constexpr int HM = XM == 1, F16 = XM == 2;
+    constexpr int TRK = EPI == EPI_PUSH ? 9 : EPI;    // trace kind (5 is the mma.sync attention kernel's)
     static_assert(HM == 0 || NT == 1, "the shared-MMA mode serves <= 4 slots");
     static_assert(CL == 1 || CL == 2, "cluster pair or none");
     static_assert(NT * MT <= 4, "shared-memory reduction sized for NT*MT <= 4");
@@ -181,7 +189,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
 
     float acc[MT][NT][4];
 
-    RT_TR(EPI * 10 + 0);
+    RT_TR(TRK * 10 + 0);
     // ---- first batch of weight loads: independent of the previous kernel, issued before the PDL wait ----
     first_batch(tile0);
     // The QKV projection releases its dependent (the attention kernel) only AFTER its own wait: whatever that kernel
@@ -189,7 +197,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     if (!(EPI == EPI_QKV && a.late_launch)) griddep_launch();
     griddep_wait();
     if (EPI == EPI_QKV && a.late_launch) griddep_launch();
-    RT_TR(EPI * 10 + 1);
+    RT_TR(TRK * 10 + 1);
 
     // RMSNorm scale of every slot (used in the epilogue only: these loads overlap the weight stream)
     if (a.ss_in || a.inv_rms) {
@@ -325,7 +333,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     const bool more = next_tile0 < n_tiles;          // block-uniform
     if (more) first_batch(next_tile0);               // in flight during this group's reduction and epilogue
     else if (threadIdx.x == 0) l2_prefetch_slice(a.pf, blockIdx.x, gridDim.x);
-    RT_TR(EPI * 10 + 2);
+    RT_TR(TRK * 10 + 2);
 
 #pragma unroll
     for (int mt = 0; mt < MT; ++mt)
@@ -350,7 +358,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
         res[tile][rr + 8][cc + 1] = s.w;
     }
     __syncthreads();
-    RT_TR(EPI * 10 + 3);
+    RT_TR(TRK * 10 + 3);
     if (CL > 1) {
         // the second CTA of the pair hands its half-K sums to the first through distributed shared memory
         if (crank == 1) {
@@ -374,6 +382,26 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
                 float v = val(r >> 4, r & 15, s) * s_rn[s];
                 if (a.bias) v += a.bias[n];
                 a.out[(size_t)s * a.ldo + n] = v;
+            }
+        }
+    } else if (EPI == EPI_PUSH) {
+        // four consecutive rows of one slot per thread = one 16-byte packet; the lowest mantissa bit of each of its words
+        // carries the parity of the slot's epoch, so a receiver can tell a packet of this exchange from the one that lay there
+        // before without a flag, a fence or a second round trip (every exchange rewrites every word of the rows it uses)
+        for (int e = threadIdx.x; e < MT * 4 * SL; e += NTHR) {
+            const int r4 = e % (MT * 4), s = e / (MT * 4);
+            const int r = r4 * 4, n = row0 + r;
+            if (s < a.T && n < a.N) {
+                const uint32_t par = (uint32_t)a.push_epoch[s] & 1u;
+                uint32_t w[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) w[i] = (__float_as_uint(val(r >> 4, (r & 15) + i, s) * s_rn[s]) & ~1u) | par;
+                const size_t off = ((size_t)(a.push_rank * 32 + s)) * a.N + n;
+#pragma unroll
+                for (int p = 0; p < 8; ++p)
+                    if (p < a.push_tp)
+                        asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(a.push_dst[p] + off), "r"(w[0]), "r"(w[1]),
+                                     "r"(w[2]), "r"(w[3]) : "memory");
             }
         }
     } else if (EPI == EPI_RESID) {
@@ -555,5 +583,5 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
             }
         }
     }
-    RT_TR(EPI * 10 + 4);
+    RT_TR(TRK * 10 + 4);
 }

@@ -116,3 +116,110 @@ __global__ void __launch_bounds__(TPF_THREADS) tp_fused_allreduce_norm_kernel(co
     }
     RT_TR(74);
 }
+
+// =====================================================================================================================
+// Push form of the same exchange (<= 8 slots): no flag, no pull.
+//
+// The row-parallel projection (gemv.cuh EPI_PUSH) stores its partial sums straight into EVERY rank's receive buffer
+// recv[src rank][slot][H] -- remote stores over NVLink, fire and forget -- as 16-byte packets whose four fp32 words carry
+// the parity of the slot's epoch in their lowest mantissa bit (a relative error of 2^-24, far below the fp16 rounding of the
+// next projection's input).  The receiver reads only its OWN GPU's memory and takes a packet the moment its four parities
+// match: behind the slowest rank's last tile there is one one-way NVLink flight and a local read, instead of a flag flight
+// plus a pull round trip.
+//
+// Epochs.  A receiver CTA counts its own runs (private cell, like the pull kernel).  The SENDER's epoch of site s and slot t
+// is advanced by CTA (0, t) of the OTHER site's receiver at its end: every kernel of the step waits for its predecessor
+// (griddepcontrol.wait), so by then all CTAs of site s's last projection have read the old value, and site s's next projection
+// reads the new one behind its own wait.  The two sites alternate strictly (one O-projection and one down-projection per
+// layer with the same slots), which keeps both counts in step; site 0 starts at 1, site 1 at 0 (advanced to 1 before its
+// first use); the buffers start zeroed = parity 0 = "not yet".
+// Reuse: a rank can be ahead of a peer by less than one exchange of the same site (it needs the peer's packets of the site in
+// between), so a packet is never overwritten before it was read -- the argument of the pull kernel.
+// The receiver does wait for its own projection: a receiver that started early and spun beside it would also have to be
+// ordered against the previous receiver of the same site, which nothing guarantees once the kernels of several layers fit on
+// the GPU at once (seen with the 2-layer test models: both instances read the same run count).
+// A rank that never delivers ends the spin with a trap.
+struct TpLLArgs {
+    const float* recv;               // this rank's receive buffer of the site: [tp][32][H]
+    int* cell_epoch;                 // private [32][TPF_CMAX] run counters of this site's receiver CTAs
+    int* next_site_epoch;            // the OTHER site's sender epochs [32]: CTA (0, t) advances entry t at its end
+    int rank, tp, H;
+    float* x;
+    const bf16* norm_w;
+    bf16* xn;
+    float* ss_part;
+    int raw;
+};
+
+__device__ __forceinline__ uint4 tpf_ld_relaxed_sys_v4(const float* p) {
+    uint4 v;
+    asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(TPF_THREADS) tp_ll_reduce_norm_kernel(const TpLLArgs a) {
+    __shared__ float sred[TPF_THREADS / 32];
+    __shared__ int s_par;
+    RT_TR(70);
+    griddep_launch();
+    griddep_wait();
+    const int c = blockIdx.x, t = blockIdx.y;
+    const int cell = t * TPF_CMAX + c;
+    if (threadIdx.x == 0) {
+        const int e = a.cell_epoch[cell] + 1;
+        a.cell_epoch[cell] = e;
+        s_par = e & 1;
+    }
+    __syncthreads();
+    const uint32_t par = (uint32_t)s_par;
+    const int n4 = a.H >> 2;
+    const int c4 = c * TPF_THREADS + threadIdx.x;
+    const bool active = c4 < n4;
+    const float* mine = a.recv + (size_t)t * a.H + (size_t)c4 * 4;        // + src * 32 * H
+    const size_t src_stride = (size_t)32 * a.H;
+    auto ok = [par](const uint4& v) { return ((v.x & 1u) == par) & ((v.y & 1u) == par) & ((v.z & 1u) == par) & ((v.w & 1u) == par); };
+
+    RT_TR(71);
+
+    float ss = 0.f;
+    if (active) {
+        uint4 d[TPF_MAX];
+        uint32_t pending = (1u << a.tp) - 1u;
+        long long spins = 0;
+        while (pending) {
+#pragma unroll
+            for (int p = 0; p < TPF_MAX; ++p)          // all loads of a round in flight together
+                if (p < a.tp && (pending >> p & 1u)) d[p] = tpf_ld_relaxed_sys_v4(mine + (size_t)p * src_stride);
+#pragma unroll
+            for (int p = 0; p < TPF_MAX; ++p)
+                if (p < a.tp && (pending >> p & 1u) && ok(d[p])) pending &= ~(1u << p);
+            if (pending && ++spins > (1ll << 28)) {
+                printf("tp_ll_reduce_norm: rank %d misses packets (mask %x, slot %d, block %d)\n", a.rank, pending, t, c);
+                __trap();
+            }
+        }
+        float4 acc = *(reinterpret_cast<const float4*>(a.x + (size_t)t * a.H) + c4);
+        const uint2 wv = *reinterpret_cast<const uint2*>(a.norm_w + c4 * 4);
+#pragma unroll
+        for (int p = 0; p < TPF_MAX; ++p)          // rank order: identical sums on every rank
+            if (p < a.tp) {
+                acc.x += __uint_as_float(d[p].x); acc.y += __uint_as_float(d[p].y);
+                acc.z += __uint_as_float(d[p].z); acc.w += __uint_as_float(d[p].w);
+            }
+        *(reinterpret_cast<float4*>(a.x + (size_t)t * a.H) + c4) = acc;
+        ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
+        const float y[4] = {acc.x * bf16lo(wv.x), acc.y * bf16hi(wv.x), acc.z * bf16lo(wv.y), acc.w * bf16hi(wv.y)};
+        xf_store4(a.xn, a.H, t, c4 * 4, y, a.raw);
+    }
+    RT_TR(72);
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float tot = 0.f;
+        for (int w = 0; w < TPF_THREADS / 32; ++w) tot += sred[w];
+        a.ss_part[c * 32 + t] = tot;
+        if (c == 0) a.next_site_epoch[t] += 1;      // the other site's senders read it behind their own wait
+    }
+    RT_TR(74);
+}
