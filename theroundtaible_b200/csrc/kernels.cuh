@@ -578,7 +578,9 @@ static __global__ void __launch_bounds__(NWM * 32) attn_merge2_kernel(const Merg
     constexpr int VD = HD / 32;
     constexpr int MAXC = 136;               // MAX_CHUNKS (engine.cuh)
     constexpr int MAXB = (MAXC + 31) / 32;
-    constexpr int PW = (MAXC + NWM - 1) / NWM > 16 ? 16 : (MAXC + NWM - 1) / NWM;     // partials a warp requests at once
+    // partials a warp requests at once: 4 warps x 18 cover the 69 partials of a row of config 3 (64 shared + 5 own chunks) in
+    // ONE round of loads; 16 warps x 9 cover all 136
+    constexpr int PW = (MAXC + NWM - 1) / NWM > 18 ? 18 : (MAXC + NWM - 1) / NWM;
     __shared__ float sacc[NWM][HD];
     __shared__ float sL;
     const int t = blockIdx.y, head = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
