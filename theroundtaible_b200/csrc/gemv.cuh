@@ -23,8 +23,9 @@
 // parts go through the MMAs, so the product is exact in the fp16 input.  Measured alternatives (profiles/r2_summary.md): the
 // split done in registers by the consumer costs ~36 ALU instructions per k-block and lane (+6-8 % per step); hi / lo as two
 // ROW-MAJOR planes double the half-line requests to the few L2 lines every CTA reads (+18 % per kernel).
-// With T <= 4 slots (template HM) hi and lo share ONE MMA: columns 0..3 carry hi of slots 0..3, columns 4..7 their lo,
-// and the epilogue adds the two columns of a slot.
+// With T <= 4 slots (template XM = 1) hi and lo share ONE MMA: columns 0..3 carry hi of slots 0..3, columns 4..7 their lo,
+// and the epilogue adds the two columns of a slot.  With 5..8 slots (XM = 2) the kernel streams the fp16 twin of the matrix
+// against the fp16 activations themselves: see the template's comment.
 //
 // Fusions: EPI_QKV    -> + bias, RoPE, q -> bf16 Q buffer, k/v -> bf16 into their KV page;
 //          EPI_RESID  -> x += acc, xw = fp16(x * w_next) (XF layout) and per-tile partial sums of x^2: the next projection applies
