@@ -67,7 +67,16 @@ struct Dec5Item {
     int key0;      // SHARED: first key; OWN: first key RELATIVE to the shared length
     int span;      // keys (multiple of 64)
     int pidx;      // partial index of this item within its rows: shared items 0 .. n_sh-1, own items n_sh + chunk
-    int pad[3];
+    int seq;       // sequence whose page table the item walks (decode slot t of a generate call is sequence t; shared items: 0)
+    int pad[2];
+};
+// The work items travel as a kernel PARAMETER (constant bank): the first thing every CTA does is read its item, and as a
+// global load that was a whole L2 round trip in front of everything else (the prologue only hides under the QKV projection for
+// the CTAs that find a free SM early, profiles/r2_summary.md 7).  They are a function of the plan alone, so a captured graph
+// may keep them.
+constexpr int D5_MAX_ITEMS = 296;
+struct Dec5ItemList {
+    Dec5Item it[D5_MAX_ITEMS];
 };
 
 struct Dec5Args {
@@ -76,7 +85,6 @@ struct Dec5Args {
     const int* slot_seq;
     const int* slot_pos;
     const int* shared_len_ptr;
-    const Dec5Item* items;
     int T, n_q, n_kv, G, BT;
     int n_pages_pool;       // pages per layer in the pool
     int layer;
@@ -90,7 +98,8 @@ struct Dec5Args {
 template <int HD>
 __global__ void __launch_bounds__(D5_THREADS, 1) attn_decode_tc5_kernel(const __grid_constant__ CUtensorMap map_q,
                                                                         const __grid_constant__ CUtensorMap map_k,
-                                                                        const __grid_constant__ CUtensorMap map_v, const Dec5Args a) {
+                                                                        const __grid_constant__ CUtensorMap map_v, const Dec5Args a,
+                                                                        const __grid_constant__ Dec5ItemList items) {
     extern __shared__ __align__(1024) unsigned char smem[];
     constexpr int NH = HD / 64;
     constexpr int Q_BYTES = NH * P5_HALF_BYTES, STAGE = 2 * NH * P6_TILE_BYTES;
@@ -105,7 +114,7 @@ __global__ void __launch_bounds__(D5_THREADS, 1) attn_decode_tc5_kernel(const __
     volatile uint32_t* tmem_slot_p = reinterpret_cast<volatile uint32_t*>(gen + (tmem_slot - sbase));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const Dec5Item it = a.items[blockIdx.x];
+    const Dec5Item it = items.it[blockIdx.x];
     RT_TR(80);
 
     if (threadIdx.x == 0) {
@@ -117,10 +126,13 @@ __global__ void __launch_bounds__(D5_THREADS, 1) attn_decode_tc5_kernel(const __
         mbar_init(b_of, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    // stale shared memory must never reach the PV product as NaN: pages a tile does not load, and the P rows of warps
-    // without valid rows, stay zero
-    for (int i = threadIdx.x; i < (Q_BYTES + P6_STAGES * STAGE + 2 * P6_PBUF) / 16; i += D5_THREADS)
-        reinterpret_cast<uint4*>(gen)[i] = make_uint4(0u, 0u, 0u, 0u);
+    // Stale shared memory must never reach the PV product as NaN through a page a tile does not load: the V half of every
+    // stage starts zeroed (its P is zero there, and 0 x NaN is NaN).  Nothing else needs it: scores of keys beyond the range
+    // are REPLACED by -inf, Q is written whole by its TMA box, and the rows of a product depend on their own P row only
+    // (rows without a valid query are never stored).
+    for (int s = 0; s < P6_STAGES; ++s)
+        for (int i = threadIdx.x; i < NH * P6_TILE_BYTES / 16; i += D5_THREADS)
+            reinterpret_cast<uint4*>(gen + Q_BYTES + s * STAGE + NH * P6_TILE_BYTES)[i] = make_uint4(0u, 0u, 0u, 0u);
     p5_fence_async_smem();
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(256));
@@ -141,26 +153,41 @@ __global__ void __launch_bounds__(D5_THREADS, 1) attn_decode_tc5_kernel(const __
     int shared = 0, seq = 0, key0 = 0, key1 = 0, n_safe = 0;
     auto ranges = [&]() {
         shared = a.shared_len_ptr ? *a.shared_len_ptr : 0;
+        seq = it.seq;
         if (it.slot < 0) {
-            seq = a.slot_seq[0];
             key0 = it.key0;
             key1 = min(key0 + it.span, shared);
             n_safe = 1 << 30;
         } else {
             const int pos = a.slot_pos[it.slot];
-            seq = a.slot_seq[it.slot];
             key0 = shared + it.key0;
             key1 = min(key0 + it.span, pos + 1);
             n_safe = key0 + it.span > pos ? (max(key1 - key0, 0) + P6_KEYS - 1) / P6_KEYS - 1 : 1 << 30;
         }
     };
-    if (a.early) ranges();
     constexpr int PPT = P6_KEYS / KV_PAGE;
     int* spt = reinterpret_cast<int*>(gen + (xchg - sbase) + D5_PARTS * 512);
+    // a shared item's pages are known from the item alone: their ids are requested together with the positions (one round
+    // trip instead of two in front of the first K/V tile)
+    bool spt_ready = false;
+    if (a.early && warp == 0 && it.slot < 0) {
+        const int* pt0 = a.page_table + (size_t)it.seq * a.pt_stride + it.key0 / KV_PAGE;
+        const int np_max = it.span / KV_PAGE;
+        int ids[PPT];
+#pragma unroll
+        for (int i = 0; i < PPT; ++i) ids[i] = (lane + 32 * i < np_max) ? pt0[lane + 32 * i] : 0;
+        ranges();
+#pragma unroll
+        for (int i = 0; i < PPT; ++i) spt[lane + 32 * i] = ids[i];
+        __syncwarp();
+        spt_ready = true;
+    } else if (a.early) {
+        ranges();
+    }
     // tile j of the item -> its ring stage (one K/V box per lane: 16 boxes of a tile issued by 16 lanes at once.  Issued one
     // after the other by a single lane they took ~1.2 us per tile in the in-kernel trace and paced the whole pipeline)
     auto issue_tile = [&](int j, int n_pages, const int* pt) {
-        if ((j & 31) == 0) {
+        if ((j & 31) == 0 && !(j == 0 && spt_ready)) {
             // the page ids of the next 32 tiles are fetched by the whole warp at once into shared memory: read one by one by
             // the issuing lane, every id is a dependent global load in front of its TMA (four per tile, ~2 us a tile)
             __syncwarp();

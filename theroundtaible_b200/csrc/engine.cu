@@ -774,8 +774,7 @@ void engine_init(rt_engine* e) {
         if (e->dec5_ok) {
             e->dec5_bt = std::min(128 / e->G, MAX_SLOTS);
             pf_make_map_q3(&e->map_qdec, e->qb, MAX_SLOTS, e->nq_l, e->G, e->dec5_bt, e->hd);
-            e->dec5_cap = 2 * e->sm_count;
-            e->dec5_items_dev = dalloc<Dec5Item>(e, e->dec5_cap);
+            e->dec5_cap = std::min(2 * e->sm_count, D5_MAX_ITEMS);
             RT_CUDA(cudaMallocHost(&e->dec5_items_host, (size_t)e->dec5_cap * sizeof(Dec5Item)));
         }
     }
@@ -1101,12 +1100,13 @@ void engine_forward(rt_engine* e, const StepOpts& o) {
             if (o.dec5_items > 0) {
                 Dec5Args d{};
                 d.page_table = e->d_page_table; d.pt_stride = e->max_pages_per_seq; d.slot_seq = e->d_seq; d.slot_pos = e->d_pos;
-                d.shared_len_ptr = e->d_shared_len; d.items = reinterpret_cast<const Dec5Item*>(e->dec5_items_dev);
+                d.shared_len_ptr = e->d_shared_len;
                 d.T = T; d.n_q = e->nq_l; d.n_kv = e->nkv_l; d.G = e->G; d.BT = e->dec5_bt; d.n_pages_pool = e->n_pages; d.layer = l;
                 d.scale_log2 = a.scale_log2; d.part_o = e->part_o; d.part_ml = e->part_ml; d.max_chunks = MAX_CHUNKS;
                 static const int dec5_early = env_int("RT_DEC5_EARLY", 1);
                 d.early = a.early && dec5_early;
-                pf_attention_dec5(e->st, e->use_pdl, o.dec5_items, e->map_qdec, e->map_kpool, e->map_vpool, d, hd);
+                pf_attention_dec5(e->st, e->use_pdl, o.dec5_items, e->map_qdec, e->map_kpool, e->map_vpool, d,
+                                  reinterpret_cast<const Dec5Item*>(e->dec5_items_host), hd);
                 e->launches++;
                 m.n_sh_parts = o.dec5_nsh; m.chunk_keys = o.dec5_own_span; m.cascade = 1;
             } else {
@@ -1227,11 +1227,11 @@ static void plan_dec5(rt_engine* e, int max_len, int shared, StepOpts& o) {
     // own items first: they are the ones that may end early, the shared ranges are always full
     for (int t = 0; t < T; ++t)
         for (int h = 0; h < nkv; ++h)
-            for (int c = 0; c < n_own; ++c) it[n++] = Dec5Item{t, h, c * L * P6_KEYS, L * P6_KEYS, n_sh + c, {0, 0, 0}};
+            for (int c = 0; c < n_own; ++c) it[n++] = Dec5Item{t, h, c * L * P6_KEYS, L * P6_KEYS, n_sh + c, t, {0, 0}};
     for (int h = 0; h < nkv; ++h)
-        for (int c = 0; c < n_sh; ++c) it[n++] = Dec5Item{-1, h, c * L * P6_KEYS, L * P6_KEYS, c, {0, 0, 0}};
-    RT_CUDA(cudaStreamSynchronize(e->st));                 // the staging buffer of the previous call has been consumed
-    RT_CUDA(cudaMemcpyAsync(e->dec5_items_dev, it, (size_t)n * sizeof(Dec5Item), cudaMemcpyHostToDevice, e->st));
+        for (int c = 0; c < n_sh; ++c) it[n++] = Dec5Item{-1, h, c * L * P6_KEYS, L * P6_KEYS, c, 0, {0, 0}};
+    // (the items go to the kernel as a parameter: prefill.cu pf_attention_dec5 copies them from this host list at launch /
+    // capture; a generate call's decode slot t IS sequence t, and slot 0's sequence holds the shared pages)
     o.dec5_items = n;
     o.dec5_nsh = n_sh;
     o.dec5_own_span = L * P6_KEYS;

@@ -122,8 +122,7 @@ struct rt_engine {
     PfTensorMap map_qdec{};           // the decode queries qb as (dims, heads, slots) for attn_decode_tc5.cuh
     bool dec5_ok = false;
     int dec5_bt = 0;
-    void* dec5_items_dev = nullptr;   // Dec5Item[dec5_cap]
-    void* dec5_items_host = nullptr;  // pinned
+    void* dec5_items_host = nullptr;  // Dec5Item[dec5_cap]: the work items of the current plan (a kernel parameter at launch)
     int dec5_cap = 0;
     bool pfa_tc5 = false;
     std::vector<PfTensorMap> map_w;   // per layer: qkv, o, gate/up, down

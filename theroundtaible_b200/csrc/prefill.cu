@@ -171,8 +171,11 @@ void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap&
 }
 
 void pf_attention_dec5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
-                       const Dec5Args& a, int hd) {
+                       const Dec5Args& a, const Dec5Item* host_items, int hd) {
     if (n_items <= 0) return;
+    RT_REQUIRE(n_items <= D5_MAX_ITEMS, "too many work items for the decode attention kernel");
+    static thread_local Dec5ItemList list;            // kernel parameter: copied at launch (or into the graph node at capture)
+    memcpy(list.it, host_items, (size_t)n_items * sizeof(Dec5Item));
     const size_t smem = p6_smem_bytes(hd) + (D5_PARTS - 2) * 512;   // the exchange area holds D5_PARTS values per row
     auto kern = hd == 128 ? attn_decode_tc5_kernel<128> : attn_decode_tc5_kernel<64>;
     RT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -187,7 +190,7 @@ void pf_attention_dec5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
     RT_CUDA(cudaLaunchKernelEx(&cfg, kern, reinterpret_cast<const CUtensorMap&>(mq), reinterpret_cast<const CUtensorMap&>(mk),
-                               reinterpret_cast<const CUtensorMap&>(mv), a));
+                               reinterpret_cast<const CUtensorMap&>(mv), a, list));
 }
 
 #ifdef RT_TRACE

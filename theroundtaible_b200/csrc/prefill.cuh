@@ -60,8 +60,9 @@ void pf_attention_tc5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap&
                       int n_pages_pool, int layer, float scale_log2, f16* out, int hd);
 // tcgen05 decode attention for long contexts (attn_decode_tc5.cuh): query rows = (slot, q-head) pairs, work items = key ranges
 struct Dec5Args;
+struct Dec5Item;
 void pf_attention_dec5(cudaStream_t st, bool pdl, int n_items, const PfTensorMap& mq, const PfTensorMap& mk, const PfTensorMap& mv,
-                       const Dec5Args& a, int hd);
+                       const Dec5Args& a, const Dec5Item* host_items, int hd);
 void pf_make_map_a(PfTensorMap* out, const void* base, int rows, int K);
 void pf_make_map_w(PfTensorMap* out, const void* base, int N, int K, int BN);
 void pf_gemm(cudaStream_t st, bool pdl, int epi, const PfTensorMap& ma, const PfTensorMap& mw, const Gemm5Args& a);
