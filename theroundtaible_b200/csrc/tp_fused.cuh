@@ -1,4 +1,6 @@
-// Fused tensor-parallel all-reduce + residual add + RMSNorm over NVLink peer memory (decode path).
+// Fused tensor-parallel all-reduce + residual add + RMSNorm over NVLink peer memory (decode path).  Two forms: the PULL form
+// below (any slot count; used for steps of more than 8 slots and with RT_TP_PUSH=0) and the PUSH form at the end of this
+// file (steps of <= 8 slots: the projection delivers its partial sums itself, the receiver reads local memory only).
 //
 // No reference counterpart (no collective exists in /root/reference); SURVEY.md 8(a-K) last row: the two
 // per-layer all-reduces of [T][H] are LATENCY-bound (128-256 KB), so they are done one-shot inside the kernel that also
