@@ -448,6 +448,18 @@ int gemv_dispatch(rt_engine* e, const GemvArgs& a) {
         else gemv_launch_pair<EPI_QKV, 8, 0>(e, a, a.N / 16);
         return a.N / 16;
     }
+    // more tiles than two 8-warp CTAs per SM hold, no more than three do (Llama-3.1-8B QKV: 384 tiles; Qwen2.5-32B/TP4 down: 320):
+    // 16-row CTAs at three per SM, all resident at once, instead of 32-row CTAs that put 4 tiles on some SMs and 2 on others
+    // (gemv.cuh OC; config 3 -1.0..-1.8 % per step, 3 knights on the 8B model -4.8 %)
+    static const int oc3 = env_int("RT_GEMV_OC3", 1);
+    if constexpr (EPI == EPI_QKV || EPI == EPI_RESID || EPI == EPI_PUSH) {
+        if (oc3 && a.T <= 8 && (a.f16 || a.T <= 4) && gemv_warps(a.K, a.N / 16) == 8 && a.N / 16 > 2 * e->sm_count &&
+            a.N / 16 <= 3 * e->sm_count) {
+            if (a.f16) launch_pdl(e, gemv_kernel<1, 1, EPI, 8, 2, 1, 3>, dim3(a.N / 16), dim3(256), 0, a);
+            else launch_pdl(e, gemv_kernel<1, 1, EPI, 8, 1, 1, 3>, dim3(a.N / 16), dim3(256), 0, a);
+            return a.N / 16;
+        }
+    }
     static const int force_mt = env_int("RT_GEMV_MT", 0);
     RT_REQUIRE(!a.f16 || a.T <= 8, "the fp16-twin projection mode serves <= 8 slots");
     const int NT = a.T <= 8 ? 1 : (a.T <= 16 ? 2 : 4);

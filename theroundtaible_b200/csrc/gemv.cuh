@@ -128,8 +128,11 @@ __device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.
 //                           GEMMs read anyway) x the fp16 activations themselves (XF16 form, common.cuh xf_store*): one f16 MMA
 //                           and one activation load per fragment, the same products.  5..8 slots cost 5-8 % per projection
 //                           in mode 0 (profiles/r2_summary.md); mode 2 takes that back.
-template <int NT, int MT, int EPI, int NW, int XM = 0, int CL = 1>
-__global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
+// OC = 3: three CTAs per SM (<= 85 registers: half the weight batch in flight per warp) for matrices with more 16-row tiles
+// than two CTAs per SM hold but no more than three do -- every tile is then resident at once and the busiest SM carries 3
+// tiles instead of 4 (Llama-3.1-8B QKV: 384 tiles on 148 SMs).
+template <int NT, int MT, int EPI, int NW, int XM = 0, int CL = 1, int OC = 1>
+__global__ void __launch_bounds__(NW * 32, OC == 3 ? 3 : (NW == 8 ? 2 : 1)) gemv_kernel(const GemvArgs a) {   // <= 128 / 85 registers
     constexpr int HM = XM == 1, F16 = XM == 2;
     constexpr int TRK = EPI == EPI_PUSH ? 9 : EPI;    // trace kind (5 is the mma.sync attention kernel's)
     static_assert(HM == 0 || NT == 1, "the shared-MMA mode serves <= 4 slots");
@@ -140,7 +143,7 @@ __global__ void __launch_bounds__(NW * 32) gemv_kernel(const GemvArgs a) {
     constexpr int SL = HM ? 4 : NT * 8;               // slots this instantiation serves
     // k-blocks of weights a warp keeps in flight (registers): W takes 8*U*MT registers, X 4*U*NT
     constexpr int XP = (HM || F16) ? 1 : 2;           // activation loads per (k-block, slot group): HM lanes pick their part
-    constexpr int U = (HM || (F16 && NT == 1)) ? 8 / MT : (NT == 1 ? (MT == 1 ? 6 : (MT == 2 ? 4 : 2)) : (NT == 2 && MT == 1 ? 4 : 2));
+    constexpr int U = OC == 3 ? 4 : (HM || (F16 && NT == 1)) ? 8 / MT : (NT == 1 ? (MT == 1 ? 6 : (MT == 2 ? 4 : 2)) : (NT == 2 && MT == 1 ? 4 : 2));
     constexpr int NTHR = NW * 32;
     __shared__ float4 red[NW][MT * NT][32];
     __shared__ float res[MT * NT][16][8];
